@@ -1,0 +1,158 @@
+"""ctypes binding of liblg_b200.so (C ABI declared in include/lg_b200.h).
+
+PyTorch is only plumbing here: it owns device memory and the stream; every wrapper passes raw
+device pointers + sizes + the current CUDA stream handle.  There is NO fallback: if the shared
+library is missing or a call returns non-zero, a RuntimeError is raised.
+"""
+import ctypes
+import os
+import subprocess
+
+import torch
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(_HERE, "liblg_b200.so")
+TILE = 128
+TILE_BYTES = 16384
+
+_c = ctypes
+_P, _I, _F, _L = _c.c_void_p, _c.c_int, _c.c_float, _c.c_int64
+
+# name -> (restype, argtypes); must list every symbol include/lg_b200.h declares
+SIGNATURES = {
+    "lg_version": (_I, []),
+    "lg_posenc": (_I, [_P, _P, _P, _P, _P, _F, _P, _P, _I, _I, _P]),
+    "lg_keypoint_extent": (_I, [_P, _P, _I, _I, _P]),
+    "lg_pack_self_qkv": (_I, [_P, _P, _P, _P, _P, _P, _P, _I, _I, _I, _I, _P]),
+    "lg_pack_cross_qkv": (_I, [_P, _P, _P, _P, _P, _I, _I, _I, _I, _P]),
+    "lg_attention": (_I, [_P, _P, _P, _P, _P, _P, _I, _I, _I, _I, _I, _I, _F, _P]),
+    "lg_filter_ws_bytes": (_c.c_size_t, [_I, _I, _I]),
+    "lg_filter_matches": (_I, [_P, _L, _P, _P, _F, _P, _P, _P, _P, _P, _I, _I, _I, _P]),
+}
+
+_lib = None
+
+
+def build(verbose: bool = False) -> str:
+    """Compile csrc/*.cu for sm_100a into liblg_b200.so (nvcc cross-compiles without a GPU)."""
+    r = subprocess.run(["make", "-C", os.path.join(_HERE, "csrc"), "-j8"], capture_output=True, text=True)
+    if r.returncode != 0:
+        raise RuntimeError("building liblg_b200.so failed:\n" + r.stdout + r.stderr)
+    if verbose:
+        print(r.stdout)
+    return LIB_PATH
+
+
+def lib():
+    global _lib
+    if _lib is None:
+        if not os.path.isfile(LIB_PATH):
+            raise RuntimeError(
+                f"{LIB_PATH} not found: the CUDA extension is required (no CPU / PyTorch fallback). "
+                "Run `python -c 'import __graft_entry__ as g; g.build()'` or `make -C cs566-project-lightglue_b200/csrc`."
+            )
+        l = ctypes.CDLL(LIB_PATH)
+        for name, (res, args) in SIGNATURES.items():
+            fn = getattr(l, name)
+            fn.restype, fn.argtypes = res, args
+        _lib = l
+    return _lib
+
+
+def _check(code: int, what: str):
+    if code != 0:
+        kind = {-1: "null pointer", -2: "bad shape", -3: "misaligned pointer"}.get(code, f"cudaError {code}")
+        raise RuntimeError(f"{what} failed: {kind}")
+
+
+def _ptr(t):
+    return None if t is None else t.data_ptr()
+
+
+def _stream():
+    return torch.cuda.current_stream().cuda_stream
+
+
+def _f32c(t, name):
+    assert t.is_cuda and t.dtype == torch.float32 and t.is_contiguous(), f"{name}: want contiguous cuda float32"
+    return t
+
+
+def _i32(t):
+    if t is None:
+        return None
+    assert t.is_cuda and t.dtype == torch.int32 and t.is_contiguous()
+    return t
+
+
+def tiles_pad(n: int) -> int:
+    t = (n + TILE - 1) // TILE
+    return t + (t & 1)
+
+
+def version() -> int:
+    return lib().lg_version()
+
+
+def posenc(kpts, size, wr, wc, bc, cond: float):
+    """-> (cos, sin) compact tables (B,N,32). size (B,2) f32 or None (extent of the points)."""
+    B, N, _ = kpts.shape
+    _f32c(kpts, "kpts")
+    if size is None:
+        size = torch.empty(B, 2, device=kpts.device, dtype=torch.float32)
+        _check(lib().lg_keypoint_extent(_ptr(kpts), _ptr(size), B, N, _stream()), "lg_keypoint_extent")
+    cos = torch.empty(B, N, 32, device=kpts.device, dtype=torch.float32)
+    sin = torch.empty_like(cos)
+    _check(lib().lg_posenc(_ptr(kpts), _ptr(_f32c(size, "size")), _ptr(_f32c(wr, "wr")), _ptr(_f32c(wc, "wc")),
+                           _ptr(_f32c(bc, "bc")), float(cond), _ptr(cos), _ptr(sin), B, N, _stream()), "lg_posenc")
+    return cos, sin
+
+
+def alloc_tiles(B, H, N, device):
+    return torch.empty(B, H, tiles_pad(N), TILE_BYTES, device=device, dtype=torch.uint8)
+
+
+def pack_self_qkv(qkv, cos, sin, lens=None, H=4):
+    B, N, F = qkv.shape
+    assert F == H * 192
+    q, k, v = (alloc_tiles(B, H, N, qkv.device) for _ in range(3))
+    _check(lib().lg_pack_self_qkv(_ptr(_f32c(qkv, "qkv")), _ptr(cos), _ptr(sin), _ptr(_i32(lens)), _ptr(q), _ptr(k),
+                                  _ptr(v), B, N, H, tiles_pad(N), _stream()), "lg_pack_self_qkv")
+    return q, k, v
+
+
+def pack_cross_qkv(qk, v, lens=None, H=4):
+    B, N, F = qk.shape
+    assert F == H * 64 and v.shape == qk.shape
+    qt, vt = alloc_tiles(B, H, N, qk.device), alloc_tiles(B, H, N, qk.device)
+    _check(lib().lg_pack_cross_qkv(_ptr(_f32c(qk, "qk")), _ptr(_f32c(v, "v")), _ptr(_i32(lens)), _ptr(qt), _ptr(vt),
+                                   B, N, H, tiles_pad(N), _stream()), "lg_pack_cross_qkv")
+    return qt, vt
+
+
+def attention(q_tiles, k_tiles, v_tiles, nq, nk, q_len=None, k_len=None, scale=0.125):
+    """-> context (B, nq, H*64) f32."""
+    B, H = q_tiles.shape[:2]
+    out = torch.empty(B, nq, H * 64, device=q_tiles.device, dtype=torch.float32)
+    _check(lib().lg_attention(_ptr(q_tiles), _ptr(k_tiles), _ptr(v_tiles), _ptr(out), _ptr(_i32(q_len)),
+                              _ptr(_i32(k_len)), B, H, nq, nk, q_tiles.shape[2], k_tiles.shape[2], float(scale),
+                              _stream()), "lg_attention")
+    return out
+
+
+def filter_matches(scores, th: float, m_len=None, n_len=None):
+    """scores (B, M+1, N+1) f32 contiguous -> m0 (B,M) i64, m1 (B,N) i64, ms0, ms1 f32."""
+    _f32c(scores, "scores")
+    B, M1, N1 = scores.shape
+    M, N = M1 - 1, N1 - 1
+    dev = scores.device
+    m0 = torch.empty(B, M, device=dev, dtype=torch.int64)
+    m1 = torch.empty(B, N, device=dev, dtype=torch.int64)
+    ms0 = torch.empty(B, M, device=dev, dtype=torch.float32)
+    ms1 = torch.empty(B, N, device=dev, dtype=torch.float32)
+    if M == 0 or N == 0:
+        raise RuntimeError("filter_matches: empty inner matrix (the reference's max() raises too)")
+    ws = torch.empty(lib().lg_filter_ws_bytes(B, M, N), device=dev, dtype=torch.uint8)
+    _check(lib().lg_filter_matches(_ptr(scores), N1, _ptr(_i32(m_len)), _ptr(_i32(n_len)), float(th), _ptr(m0),
+                                   _ptr(m1), _ptr(ms0), _ptr(ms1), _ptr(ws), B, M, N, _stream()), "lg_filter_matches")
+    return m0, m1, ms0, ms1

@@ -1,0 +1,274 @@
+// lg_attention : tcgen05 / TMEM flash attention for LightGlue's SelfBlock and CrossBlock.
+//
+// Replaces Attention.forward (reference gluefactory/models/matchers/lightglue.py:139-156),
+// i.e. softmax(q k^T * dh^-0.5 [+ key-padding mask]) v, without materialising the (N x N)
+// score matrix.  For CrossBlock (lightglue.py:229-244) it is called once per direction on
+// the shared to_qk projection (qk0 against qk1/v1, then qk1 against qk0/v0).
+//
+// Shape of one CTA (320 threads, 1 CTA / SM):
+//   * 256 query rows = two 128-row tiles, one per softmax warpgroup (warps 0-3, 4-7);
+//     both tiles share every staged K / V^T tile.
+//   * warp 8 (one lane): bulk (TMA engine) copies of the pre-swizzled bf16 operand tiles
+//     into a 3-stage shared-memory ring, mbarrier complete_tx signalling.
+//   * warp 9 (one lane): tcgen05.mma issue.  S_t = Q_t K^T (128x128x64) and
+//     O_t += P_t V (128x64x128) with accumulators in TMEM: S0 S1 O0 O1 = 384 columns.
+//   * softmax warpgroups: thread == row.  tcgen05.ld S from TMEM, fp32 online softmax in the
+//     exp2 domain with lazy (thresholded) rescaling of O, P written as bf16 into a
+//     SWIZZLE_128B shared tile that feeds the second MMA.
+// The MMA order  PV0_j, QK0_{j+1}, PV1_j, QK1_{j+1}  lets each warpgroup's softmax overlap the
+// other tile's tensor work.
+#include "lg_common.cuh"
+#include "lg_b200.h"
+
+namespace lg {
+
+constexpr int kStages = 3;
+constexpr int kTileBytes = 16384;
+constexpr int kAttnThreads = 320;
+constexpr uint32_t kColS = 0, kColO = 256;  // TMEM column map: S_t at t*128, O_t at 256 + t*64
+constexpr float kRescaleThreshold = 8.0f;   // log2 units; P stays <= 2^8
+
+struct AttnParams {
+  const uint8_t* q_tiles;
+  const uint8_t* k_tiles;
+  const uint8_t* v_tiles;
+  float* out;          // (B, nq, H*64) fp32
+  const int* q_len;    // per-image valid query rows, or null
+  const int* k_len;    // per-image valid keys, or null
+  int B, H, nq, nk, tq_pad, tk_pad;
+  float scale_log2;    // dh^-0.5 * log2(e)
+};
+
+struct __align__(8) AttnBarriers {
+  uint64_t q_full;
+  uint64_t kv_full[kStages];
+  uint64_t kv_empty[kStages];
+  uint64_t s_full[2];
+  uint64_t p_full[2];
+  uint64_t o_final;
+  uint32_t tmem_base;
+};
+
+constexpr int kAttnSmem = 1024 /*align slack*/ + 2 * kTileBytes + kStages * 2 * kTileBytes + 2 * 2 * kTileBytes +
+                          static_cast<int>(sizeof(AttnBarriers));
+
+__global__ void __launch_bounds__(kAttnThreads, 1) attention_kernel(const AttnParams p) {
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* base = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+  uint8_t* sQ = base;                               // 2 x 16 KB
+  uint8_t* sKV = sQ + 2 * kTileBytes;               // kStages x (K 16 KB | V^T 16 KB)
+  uint8_t* sP = sKV + kStages * 2 * kTileBytes;     // 2 x 32 KB
+  AttnBarriers* bar = reinterpret_cast<AttnBarriers*>(sP + 4 * kTileBytes);
+
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int b = blockIdx.z, h = blockIdx.y, qt0 = blockIdx.x * 2;
+  const int q_len = p.q_len ? min(p.q_len[b], p.nq) : p.nq;
+  const int k_len = p.k_len ? min(p.k_len[b], p.nk) : p.nk;
+  const int nkt = (k_len + kTile - 1) / kTile;
+  const int row_stride = p.H * kHeadDim;
+
+  if (qt0 * kTile >= q_len || nkt == 0) {
+    // nothing to attend from / to: rows are zero (reference: nan_to_num of an all-masked softmax)
+    const int r0 = qt0 * kTile, r1 = min(p.nq, r0 + 2 * kTile);
+    for (int i = threadIdx.x; i < (r1 - r0) * (kHeadDim / 4); i += kAttnThreads) {
+      const int r = r0 + i / (kHeadDim / 4), c4 = i % (kHeadDim / 4);
+      reinterpret_cast<float4*>(p.out + (static_cast<size_t>(b) * p.nq + r) * row_stride + h * kHeadDim)[c4] =
+          make_float4(0.f, 0.f, 0.f, 0.f);
+    }
+    return;
+  }
+
+  if (threadIdx.x == 0) {
+    mbar_init(&bar->q_full, 1);
+    for (int s = 0; s < kStages; ++s) { mbar_init(&bar->kv_full[s], 1); mbar_init(&bar->kv_empty[s], 1); }
+    for (int t = 0; t < 2; ++t) { mbar_init(&bar->s_full[t], 1); mbar_init(&bar->p_full[t], 128); }
+    mbar_init(&bar->o_final, 1);
+    fence_mbar_init();
+  }
+  if (warp == 9) tmem_alloc<512>(&bar->tmem_base);
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem = bar->tmem_base;
+
+  if (warp == 8) {
+    // ------------------------------------------------------------------ producer
+    if (lane == 0) {
+      const size_t bh = static_cast<size_t>(b) * p.H + h;
+      const uint8_t* gq = p.q_tiles + (bh * p.tq_pad + qt0) * kTileBytes;
+      const uint8_t* gk = p.k_tiles + bh * p.tk_pad * kTileBytes;
+      const uint8_t* gv = p.v_tiles + bh * p.tk_pad * kTileBytes;
+      mbar_arrive_expect_tx(&bar->q_full, 2 * kTileBytes);
+      bulk_g2s(sQ, gq, 2 * kTileBytes, &bar->q_full);  // tiles qt0, qt0+1 are adjacent (tq_pad is even)
+      for (int j = 0; j < nkt; ++j) {
+        const int s = j % kStages;
+        if (j >= kStages) mbar_wait(&bar->kv_empty[s], ((j / kStages) - 1) & 1);
+        mbar_arrive_expect_tx(&bar->kv_full[s], 2 * kTileBytes);
+        bulk_g2s(sKV + s * 2 * kTileBytes, gk + static_cast<size_t>(j) * kTileBytes, kTileBytes, &bar->kv_full[s]);
+        bulk_g2s(sKV + s * 2 * kTileBytes + kTileBytes, gv + static_cast<size_t>(j) * kTileBytes, kTileBytes,
+                 &bar->kv_full[s]);
+      }
+    }
+  } else if (warp == 9) {
+    // ------------------------------------------------------------------ MMA issuer
+    if (lane == 0) {
+      constexpr uint32_t idesc_qk = umma_idesc(kFmtBF16, 128, 128);
+      constexpr uint32_t idesc_pv = umma_idesc(kFmtBF16, 128, 64);
+      const uint32_t aQ = smem_u32(sQ), aKV = smem_u32(sKV), aP = smem_u32(sP);
+      auto issue_qk = [&](int t, int s) {
+        const uint64_t da = umma_desc_kmajor_sw128(aQ + t * kTileBytes);
+        const uint64_t db = umma_desc_kmajor_sw128(aKV + s * 2 * kTileBytes);
+#pragma unroll
+        for (int kk = 0; kk < 4; ++kk)  // K = 64 = 4 x 16, 32 B per step inside the 128 B swizzle row
+          umma_bf16_ss(tmem + kColS + t * 128, da + 2 * kk, db + 2 * kk, idesc_qk, kk > 0);
+        umma_commit(&bar->s_full[t]);
+      };
+      auto issue_pv = [&](int t, int s, int j) {
+#pragma unroll
+        for (int kk = 0; kk < 8; ++kk) {  // K = 128 keys = 2 swizzle atoms x 4 steps
+          const uint32_t offA = (kk >> 2) * kTileBytes + (kk & 3) * 32;
+          const uint32_t offB = kTileBytes + (kk >> 2) * (kTileBytes / 2) + (kk & 3) * 32;
+          umma_bf16_ss(tmem + kColO + t * 64, umma_desc_kmajor_sw128(aP + t * 2 * kTileBytes + offA),
+                       umma_desc_kmajor_sw128(aKV + s * 2 * kTileBytes + offB), idesc_pv, (j > 0 || kk > 0));
+        }
+      };
+      mbar_wait(&bar->q_full, 0);
+      mbar_wait(&bar->kv_full[0], 0);
+      tc_fence_after();
+      issue_qk(0, 0);
+      issue_qk(1, 0);
+      for (int j = 0; j < nkt; ++j) {
+        const int s = j % kStages, sn = (j + 1) % kStages;
+        for (int t = 0; t < 2; ++t) {
+          mbar_wait(&bar->p_full[t], j & 1);
+          tc_fence_after();
+          issue_pv(t, s, j);
+          if (t == 1) umma_commit(&bar->kv_empty[s]);  // K_j and V_j are dead once PV1_j retires
+          if (j + 1 < nkt) {
+            if (t == 0) { mbar_wait(&bar->kv_full[sn], ((j + 1) / kStages) & 1); tc_fence_after(); }
+            issue_qk(t, sn);
+          }
+        }
+      }
+      umma_commit(&bar->o_final);
+    }
+  } else {
+    // ------------------------------------------------------------------ softmax warpgroups
+    const int t = warp >> 2;                       // query tile of this warpgroup
+    const int r = (warp & 3) * 32 + lane;          // row == TMEM lane
+    const uint32_t lane_addr = static_cast<uint32_t>((warp & 3) * 32) << 16;
+    const uint32_t tS = tmem + lane_addr + kColS + t * 128;
+    const uint32_t tO = tmem + lane_addr + kColO + t * 64;
+    uint8_t* myP = sP + t * 2 * kTileBytes;
+    const float c = p.scale_log2;
+    float m_used = -INFINITY, l = 0.f;
+    uint32_t v[32];
+
+    for (int j = 0; j < nkt; ++j) {
+      const int rem = k_len - j * kTile;           // valid keys in this block (>= 1)
+      const bool partial = rem < kTile;
+      mbar_wait(&bar->s_full[t], j & 1);
+      tc_fence_after();
+      // pass 1: block row max
+      float mx = -INFINITY;
+#pragma unroll
+      for (int cb = 0; cb < 4; ++cb) {
+        tmem_ld32(tS + cb * 32, v);
+        tmem_wait_ld();
+        if (!partial) {
+#pragma unroll
+          for (int i = 0; i < 32; ++i) mx = fmaxf(mx, __uint_as_float(v[i]));
+        } else {
+#pragma unroll
+          for (int i = 0; i < 32; ++i) mx = fmaxf(mx, (cb * 32 + i < rem) ? __uint_as_float(v[i]) : -INFINITY);
+        }
+      }
+      // lazy rescale: only move the reference max when it grew by more than the threshold
+      const bool need = (mx - m_used) * c > kRescaleThreshold;  // true on the first block (m_used = -inf)
+      if (__any_sync(0xffffffffu, need)) {
+        float alpha = 1.f;
+        if (need) { alpha = exp2f((m_used - mx) * c); m_used = mx; }
+        l *= alpha;
+        if (j > 0) {  // s_full(j) retiring implies PV_t(j-1) has retired: O_t is quiescent
+#pragma unroll
+          for (int cb = 0; cb < 2; ++cb) {
+            tmem_ld32(tO + cb * 32, v);
+            tmem_wait_ld();
+#pragma unroll
+            for (int i = 0; i < 32; ++i) v[i] = __float_as_uint(__uint_as_float(v[i]) * alpha);
+            tmem_st32(tO + cb * 32, v);
+          }
+          tmem_wait_st();
+        }
+      }
+      const float ms = m_used * c;
+      // pass 2: P = exp2(S*c - ms) -> bf16 -> swizzled smem tile (A operand of the PV MMA)
+#pragma unroll
+      for (int cb = 0; cb < 4; ++cb) {
+        tmem_ld32(tS + cb * 32, v);
+        tmem_wait_ld();
+        float e[32];
+#pragma unroll
+        for (int i = 0; i < 32; ++i) {
+          float x = exp2f(fmaf(__uint_as_float(v[i]), c, -ms));
+          if (partial && cb * 32 + i >= rem) x = 0.f;
+          e[i] = x;
+          l += x;
+        }
+#pragma unroll
+        for (int q = 0; q < 4; ++q) {
+          uint4 o;
+          o.x = pack_bf16x2(e[8 * q], e[8 * q + 1]); o.y = pack_bf16x2(e[8 * q + 2], e[8 * q + 3]);
+          o.z = pack_bf16x2(e[8 * q + 4], e[8 * q + 5]); o.w = pack_bf16x2(e[8 * q + 6], e[8 * q + 7]);
+          const int g = cb * 4 + q;  // 16 B chunk index along the 128 keys
+          *reinterpret_cast<uint4*>(myP + (g >> 3) * kTileBytes + sw128_offset(r, g & 7)) = o;
+        }
+      }
+      fence_proxy_async_smem();
+      tc_fence_before();
+      mbar_arrive(&bar->p_full[t]);
+    }
+    // epilogue: O / l -> fp32 rows of the (B, nq, H*64) context tensor
+    mbar_wait(&bar->o_final, 0);
+    tc_fence_after();
+    const int row = (qt0 + t) * kTile + r;
+    const float inv = (row < q_len) ? 1.f / l : 0.f;  // padded query rows -> 0
+    float4* dst = reinterpret_cast<float4*>(p.out + (static_cast<size_t>(b) * p.nq + row) * row_stride + h * kHeadDim);
+#pragma unroll
+    for (int cb = 0; cb < 2; ++cb) {
+      tmem_ld32(tO + cb * 32, v);
+      tmem_wait_ld();
+      if (row < p.nq) {
+#pragma unroll
+        for (int i = 0; i < 8; ++i)
+          dst[cb * 8 + i] = make_float4(__uint_as_float(v[4 * i]) * inv, __uint_as_float(v[4 * i + 1]) * inv,
+                                        __uint_as_float(v[4 * i + 2]) * inv, __uint_as_float(v[4 * i + 3]) * inv);
+      }
+    }
+  }
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 9) tmem_dealloc<512>(tmem);
+}
+
+}  // namespace lg
+
+extern "C" int lg_attention(const void* q_tiles, const void* k_tiles, const void* v_tiles, float* out,
+                            const int* q_len, const int* k_len, int B, int H, int nq, int nk, int tq_pad, int tk_pad,
+                            float softmax_scale, cudaStream_t stream) {
+  if (!q_tiles || !k_tiles || !v_tiles || !out) return LG_ERR_NULL;
+  if (B <= 0 || H <= 0 || nq <= 0 || nk <= 0) return LG_ERR_SHAPE;
+  if (tq_pad * lg::kTile < nq || tk_pad * lg::kTile < nk || (tq_pad & 1) || (tk_pad & 1)) return LG_ERR_SHAPE;
+  static bool attr_done = false;  // idempotent attribute; a benign race at worst sets it twice
+  if (!attr_done) {
+    cudaError_t e = cudaFuncSetAttribute(lg::attention_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                         lg::kAttnSmem);
+    if (e != cudaSuccess) return static_cast<int>(e);
+    attr_done = true;
+  }
+  lg::AttnParams p{static_cast<const uint8_t*>(q_tiles), static_cast<const uint8_t*>(k_tiles),
+                   static_cast<const uint8_t*>(v_tiles), out, q_len, k_len, B, H, nq, nk, tq_pad, tk_pad,
+                   softmax_scale * 1.4426950408889634f};
+  lg::attention_kernel<<<dim3(tq_pad / 2, H, B), lg::kAttnThreads, lg::kAttnSmem, stream>>>(p);
+  return static_cast<int>(cudaGetLastError());
+}

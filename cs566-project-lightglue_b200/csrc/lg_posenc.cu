@@ -1,0 +1,88 @@
+// lg_posenc : keypoint normalisation + count-conditioned Fourier positional encoding.
+//
+// Replaces normalize_keypoints (reference gluefactory/models/matchers/lightglue.py:21-33) and
+// ConditionalLearnableFourierPositionalEncoding.forward (lightglue.py:63-77) as called at
+// lightglue.py:448-456,490-494.  Writes the compact (B,N,32) cos / sin tables (frequency j is
+// lanes 2j, 2j+1 of the reference's repeat_interleave'd (2,B,1,N,64) tensor); the tables are
+// consumed by lg_pack_self_qkv, which applies the rotary while producing the Q/K tiles.
+// Phases reach ~N radians (condition ~ w*N), so the fp32 rounding sequence of the reference
+// is kept (projection rounded, then + condition rounded) and full-range sincosf is used.
+#include "lg_common.cuh"
+#include "lg_b200.h"
+
+namespace lg {
+
+// per-image (shift, scale) when no image size is given: size = 1 + max - min over the points
+__global__ void posenc_extent_kernel(const float* __restrict__ kpts, float* __restrict__ size_out, int N) {
+  const int b = blockIdx.x;
+  float mnx = INFINITY, mny = INFINITY, mxx = -INFINITY, mxy = -INFINITY;
+  for (int i = threadIdx.x; i < N; i += blockDim.x) {
+    const float2 k = reinterpret_cast<const float2*>(kpts)[static_cast<size_t>(b) * N + i];
+    mnx = fminf(mnx, k.x); mxx = fmaxf(mxx, k.x); mny = fminf(mny, k.y); mxy = fmaxf(mxy, k.y);
+  }
+  __shared__ float red[4][32];
+  mnx = -warp_max(-mnx); mny = -warp_max(-mny); mxx = warp_max(mxx); mxy = warp_max(mxy);
+  const int w = threadIdx.x >> 5, l = threadIdx.x & 31;
+  if (l == 0) { red[0][w] = mnx; red[1][w] = mny; red[2][w] = mxx; red[3][w] = mxy; }
+  __syncthreads();
+  if (w == 0) {
+    const int nw = blockDim.x >> 5;
+    mnx = l < nw ? red[0][l] : INFINITY; mny = l < nw ? red[1][l] : INFINITY;
+    mxx = l < nw ? red[2][l] : -INFINITY; mxy = l < nw ? red[3][l] : -INFINITY;
+    mnx = -warp_max(-mnx); mny = -warp_max(-mny); mxx = warp_max(mxx); mxy = warp_max(mxy);
+    if (l == 0) {
+      size_out[2 * b] = __fsub_rn(__fadd_rn(1.f, mxx), mnx);
+      size_out[2 * b + 1] = __fsub_rn(__fadd_rn(1.f, mxy), mny);
+    }
+  }
+}
+
+// one thread per (b, n, j): 32 consecutive threads write one point's 32 frequencies
+__global__ void posenc_kernel(const float* __restrict__ kpts, const float* __restrict__ size,
+                              const float* __restrict__ wr, const float* __restrict__ wc,
+                              const float* __restrict__ bc, float cond, float* __restrict__ cos_t,
+                              float* __restrict__ sin_t, int B, int N) {
+  const size_t idx = static_cast<size_t>(blockIdx.x) * blockDim.x + threadIdx.x;
+  if (idx >= static_cast<size_t>(B) * N * 32) return;
+  const int j = idx & 31;
+  const size_t pt = idx >> 5;
+  const int b = static_cast<int>(pt / N);
+  const float2 k = reinterpret_cast<const float2*>(kpts)[pt];
+  const float w = size[2 * b], h = size[2 * b + 1];
+  // (kpts - size/2) / (max(size)/2), IEEE division like torch
+  const float scale = __fmul_rn(fmaxf(w, h), 0.5f);
+  const float x = __fdiv_rn(__fsub_rn(k.x, __fmul_rn(w, 0.5f)), scale);
+  const float y = __fdiv_rn(__fsub_rn(k.y, __fmul_rn(h, 0.5f)), scale);
+  // Linear(2->32, no bias): x*w0 + y*w1 accumulated with fma like the CPU GEMV micro-kernel
+  const float proj = __fmaf_rn(y, wr[2 * j + 1], __fmul_rn(x, wr[2 * j]));
+  // Linear(1->32)(relu(count)): count*w + b
+  const float modulated = __fmaf_rn(fmaxf(cond, 0.f), wc[j], bc[j]);
+  const float phase = __fadd_rn(proj, modulated);
+  float s, c;
+  sincosf(phase, &s, &c);
+  cos_t[idx] = c;
+  sin_t[idx] = s;
+}
+
+}  // namespace lg
+
+extern "C" int lg_posenc(const float* kpts, const float* size, const float* wr, const float* wc, const float* bc,
+                         float cond, float* cos_t, float* sin_t, int B, int N, cudaStream_t stream) {
+  if (!kpts || !wr || !wc || !bc || !cos_t || !sin_t) return LG_ERR_NULL;
+  if (B <= 0 || N <= 0) return LG_ERR_SHAPE;
+  if (!size) return LG_ERR_NULL;  // size=None branch: call lg_keypoint_extent first
+  const size_t total = static_cast<size_t>(B) * N * 32;
+  lg::posenc_kernel<<<static_cast<unsigned>((total + 255) / 256), 256, 0, stream>>>(kpts, size, wr, wc, bc, cond,
+                                                                                   cos_t, sin_t, B, N);
+  return static_cast<int>(cudaGetLastError());
+}
+
+// size_out (B,2) f32 = 1 + max - min over each image's keypoints (lightglue.py:25-26)
+extern "C" int lg_keypoint_extent(const float* kpts, float* size_out, int B, int N, cudaStream_t stream) {
+  if (!kpts || !size_out) return LG_ERR_NULL;
+  if (B <= 0 || N <= 0) return LG_ERR_SHAPE;
+  lg::posenc_extent_kernel<<<B, 256, 0, stream>>>(kpts, size_out, N);
+  return static_cast<int>(cudaGetLastError());
+}
+
+extern "C" int lg_version(void) { return 100; }

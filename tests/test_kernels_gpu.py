@@ -1,0 +1,190 @@
+"""GPU parity tests, kernel by kernel, through the C ABI (ctypes) against the oracle
+(oracle/lightglue_oracle.py, the CPU restatement pinned to the reference module)."""
+import numpy as np
+import pytest
+import torch
+
+from conftest import load_golden, pkg
+from oracle import lightglue_oracle as O
+
+pytestmark = pytest.mark.gpu
+
+W = pkg("weights")
+
+
+@pytest.fixture(scope="module")
+def C():
+    assert torch.cuda.is_available(), "gpu tests need a CUDA device"
+    return pkg("_cabi")
+
+
+def _gen(seed):
+    g = torch.Generator().manual_seed(seed)
+    return g
+
+
+# ----------------------------------------------------------------------------- (4) filter_matches
+def test_filter_known_answers(C):
+    """Bit-exact indices on the reference's own score tensors (golden KATs incl. ties, -inf rows)."""
+    meta, g = load_golden("filter_matches_kat")
+    for name, th in meta["thresholds"].items():
+        s = torch.from_numpy(g[name + "_scores"]).cuda().contiguous()
+        m0, m1, ms0, ms1 = C.filter_matches(s, th)
+        np.testing.assert_array_equal(m0.cpu().numpy(), g[name + "_m0"], err_msg=name)
+        np.testing.assert_array_equal(m1.cpu().numpy(), g[name + "_m1"], err_msg=name)
+        # expf (GPU libm) vs SLEEF exp (CPU): <= 2 ulp
+        np.testing.assert_allclose(ms0.cpu().numpy(), g[name + "_ms0"], rtol=3e-7, atol=0, err_msg=name)
+        np.testing.assert_allclose(ms1.cpu().numpy(), g[name + "_ms1"], rtol=3e-7, atol=0, err_msg=name)
+        assert m0.dtype == torch.int64 and ms0.dtype == torch.float32
+
+
+@pytest.mark.parametrize("B,M,N,th", [(1, 1, 1, 0.0), (2, 33, 1000, 0.1), (3, 513, 257, 0.0), (2, 2048, 2048, 0.1),
+                                      (1, 4096, 3000, 0.05)])
+def test_filter_random_vs_oracle(C, B, M, N, th):
+    g = _gen(M * 7 + N)
+    # scores quantised to a coarse grid => many exact ties, exercising the lowest-index rule
+    s = (torch.randn(B, M + 1, N + 1, generator=g) * 3).round() / 2 - 6
+    m0, m1, ms0, ms1 = C.filter_matches(s.cuda(), th)
+    r0, r1, rs0, rs1 = O.filter_matches(s, th)
+    assert torch.equal(m0.cpu(), r0) and torch.equal(m1.cpu(), r1)
+    np.testing.assert_allclose(ms0.cpu().numpy(), rs0.numpy(), rtol=3e-7)
+    np.testing.assert_allclose(ms1.cpu().numpy(), rs1.numpy(), rtol=3e-7)
+
+
+def test_filter_on_reference_log_assignment(C):
+    """filter_matches fed the reference's own log_assignment (golden forward) -> its own matches."""
+    for name in ("sp_b1_192", "sp_b2_160x224", "adaptive_depth_300x400"):
+        meta, g = load_golden("fwd_" + name)
+        s = torch.from_numpy(g["log_assignment"]).cuda()
+        m0, m1, ms0, ms1 = C.filter_matches(s, meta["conf"]["filter_threshold"])
+        np.testing.assert_array_equal(m0.cpu().numpy(), g["matches0"])
+        np.testing.assert_array_equal(m1.cpu().numpy(), g["matches1"])
+        np.testing.assert_allclose(ms0.cpu().numpy(), g["matching_scores0"], rtol=3e-7)
+
+
+def test_filter_varlen(C):
+    g = _gen(5)
+    B, M, N = 3, 300, 260
+    s = torch.randn(B, M + 1, N + 1, generator=g)
+    ml, nl = [300, 17, 129], [260, 260, 1]
+    m0, m1, ms0, ms1 = C.filter_matches(s.cuda(), 0.0, torch.tensor(ml, dtype=torch.int32).cuda(),
+                                        torch.tensor(nl, dtype=torch.int32).cuda())
+    for b in range(B):
+        sub = torch.full((1, ml[b] + 1, nl[b] + 1), 0.0)
+        sub[0, :ml[b], :nl[b]] = s[b, :ml[b], :nl[b]]
+        r0, r1, rs0, rs1 = O.filter_matches(sub, 0.0)
+        assert torch.equal(m0[b, :ml[b]].cpu(), r0[0]) and torch.equal(m1[b, :nl[b]].cpu(), r1[0])
+        assert (m0[b, ml[b]:] == -1).all() and (ms1[b, nl[b]:] == 0).all()
+
+
+# ----------------------------------------------------------------------------- (1) posenc
+@pytest.mark.parametrize("B,N,size", [(2, 1000, (640, 480)), (1, 2048, (1600, 1200)), (3, 77, None)])
+def test_posenc_vs_oracle(C, B, N, size):
+    sd = W.make_state_dict({}, seed=0)
+    data = W.make_inputs(B, N, N, seed=3, image_size=size or (640, 480))
+    k = data["keypoints0"]
+    sz = None if size is None else data["view0"]["image_size"]
+    kn = O.normalize_keypoints(k, sz)
+    cos_r, sin_r = O.posenc_table(sd, kn, float(N))
+    szg = None if sz is None else sz.float().cuda()
+    cos, sin = C.posenc(k.cuda(), szg, sd["posenc.Wr.weight"].cuda(), sd["posenc.condition_modulation.weight"].cuda().reshape(-1).contiguous(),
+                        sd["posenc.condition_modulation.bias"].cuda(), float(N))
+    # phases are O(N) rad: one fp32 ulp of the phase is 2.4e-4 at 2048.  The kernel mirrors the
+    # CPU rounding sequence, so the tables agree to sincosf-vs-SLEEF accuracy.
+    assert (cos.cpu() - cos_r).abs().max() < 2e-6
+    assert (sin.cpu() - sin_r).abs().max() < 2e-6
+
+
+# ----------------------------------------------------------------------------- (2) attention
+def _unswizzle_tiles(t, n):
+    """Inverse of the SWIZZLE_128B tile image: (B,H,T,16384) u8 -> (B,H,T*128,64) bf16 rows."""
+    B, H, T, _ = t.shape
+    x = t.view(B, H, T, 128, 8, 16)  # row, chunk position, 16 bytes
+    r = torch.arange(128, device=t.device) % 8
+    pos = (torch.arange(8, device=t.device)[None, :] ^ r[:, None])  # logical chunk c lives at c ^ (r%8)
+    x = torch.gather(x, 4, pos[None, None, None, :, :, None].expand(B, H, T, 128, 8, 16))
+    return x.reshape(B, H, T * 128, 128).view(torch.bfloat16)[:, :, :n]
+
+
+def test_pack_self_layout(C):
+    B, N, H = 2, 300, 4
+    g = _gen(11)
+    qkv = torch.randn(B, N, H * 192, generator=g)
+    sd = W.make_state_dict({}, seed=0)
+    kn = torch.rand(B, N, 2, generator=g) * 2 - 1
+    cos, sin = O.posenc_table(sd, kn, float(N))
+    q, k, v = O.split_qkv(qkv, H)
+    q, k = O.apply_rotary(q, cos, sin), O.apply_rotary(k, cos, sin)
+    qt, kt, vt = C.pack_self_qkv(qkv.cuda(), cos.cuda(), sin.cuda(), None, H)
+    torch.cuda.synchronize()
+    assert torch.equal(_unswizzle_tiles(qt, N).float().cpu(), q.bfloat16().float())
+    assert torch.equal(_unswizzle_tiles(kt, N).float().cpu(), k.bfloat16().float())
+    # V^T tile: 2 atoms of [64 dh][64 points]
+    T = vt.shape[2]
+    vv = vt.view(B, H, T, 2, 8192)
+    x = vv.view(B, H, T, 2, 64, 8, 16)
+    r = torch.arange(64, device=vt.device) % 8
+    pos = torch.arange(8, device=vt.device)[None, :] ^ r[:, None]
+    x = torch.gather(x, 5, pos[None, None, None, None, :, :, None].expand(B, H, T, 2, 64, 8, 16))
+    x = x.reshape(B, H, T, 2, 64, 128).view(torch.bfloat16)           # (.., atom, dh, 64 points)
+    x = x.permute(0, 1, 2, 3, 5, 4).reshape(B, H, T * 128, 64)[:, :, :N]
+    assert torch.equal(x.float().cpu(), v.bfloat16().float())
+    # padded rows are zero
+    assert _unswizzle_tiles(qt, T * 128)[:, :, N:].float().abs().max() == 0
+
+
+def _attn_case(C, B, H, nq, nk, qlen, klen, seed, scale_mag=1.0):
+    g = _gen(seed)
+    qk_q = torch.randn(B, nq, H * 64, generator=g) * scale_mag
+    v_q = torch.randn(B, nq, H * 64, generator=g)
+    qk_k = torch.randn(B, nk, H * 64, generator=g) * scale_mag
+    v_k = torch.randn(B, nk, H * 64, generator=g)
+    ql = None if qlen is None else torch.tensor(qlen, dtype=torch.int32).cuda()
+    kl = None if klen is None else torch.tensor(klen, dtype=torch.int32).cuda()
+    qt, _ = C.pack_cross_qkv(qk_q.cuda(), v_q.cuda(), ql, H)
+    kt, vt = C.pack_cross_qkv(qk_k.cuda(), v_k.cuda(), kl, H)
+    out = C.attention(qt, kt, vt, nq, nk, ql, kl, 0.125)
+    torch.cuda.synchronize()
+    out = out.cpu()
+
+    def heads(t):
+        return t.unflatten(-1, (H, 64)).transpose(1, 2)
+
+    errs = []
+    for b in range(B):
+        a = nq if qlen is None else qlen[b]
+        c = nk if klen is None else klen[b]
+        if c == 0 or a == 0:
+            assert out[b].abs().max() == 0
+            continue
+        q, k, v = heads(qk_q[b:b + 1, :a]), heads(qk_k[b:b + 1, :c]), heads(v_k[b:b + 1, :c])
+        ref = O.attention(q, k, v).transpose(1, 2).flatten(-2)                     # fp32 oracle
+        refb = O.attention(q.bfloat16().float(), k.bfloat16().float(), v.bfloat16().float()).transpose(1, 2).flatten(-2)
+        got = out[b:b + 1, :a]
+        errs.append(((got - ref).abs().max().item(), (got - refb).abs().max().item()))
+        assert out[b, a:].abs().max() == 0 if a < nq else True
+    return errs
+
+
+@pytest.mark.parametrize("B,nq,nk", [(1, 128, 128), (1, 256, 256), (2, 300, 200), (1, 1024, 1024), (2, 2048, 2048),
+                                     (1, 97, 4096)])
+def test_attention_vs_oracle(C, B, nq, nk):
+    errs = _attn_case(C, B, 4, nq, nk, None, None, seed=nq + nk)
+    for e32, eb in errs:
+        # bf16 operands (Q,K,V,P), fp32 accumulate: vs the fp32 oracle ~1e-2 on O(1) outputs; vs the
+        # oracle fed bf16-rounded operands only the P rounding remains
+        assert e32 < 3e-2 and eb < 1.5e-2, (e32, eb)
+
+
+def test_attention_large_logits(C):
+    """peaked softmax (|logit| ~ 30): exercises the lazy-rescale path."""
+    errs = _attn_case(C, 1, 4, 512, 1024, None, None, seed=5, scale_mag=4.0)
+    for e32, eb in errs:
+        assert eb < 3e-2, (e32, eb)
+
+
+def test_attention_varlen(C):
+    errs = _attn_case(C, 4, 4, 512, 640, [512, 1, 200, 0], [640, 129, 128, 5], seed=9)
+    for e32, eb in errs:
+        assert e32 < 3e-2 and eb < 1.5e-2, (e32, eb)
+    errs = _attn_case(C, 2, 4, 256, 256, [256, 256], [0, 256], seed=10)
