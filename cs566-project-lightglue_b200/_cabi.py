@@ -26,6 +26,8 @@ SIGNATURES = {
     "lg_pack_self_qkv": (_I, [_P, _P, _P, _P, _P, _P, _P, _I, _I, _I, _I, _P]),
     "lg_pack_cross_qkv": (_I, [_P, _P, _P, _P, _P, _I, _I, _I, _I, _P]),
     "lg_attention": (_I, [_P, _P, _P, _P, _P, _P, _I, _I, _I, _I, _I, _I, _F, _P]),
+    "lg_assign_ws_bytes": (_c.c_size_t, [_I, _I, _I]),
+    "lg_assign": (_I, [_P, _P, _P, _P, _P, _P, _F, _P, _P, _I, _I, _I, _P]),
     "lg_filter_ws_bytes": (_c.c_size_t, [_I, _I, _I]),
     "lg_filter_matches": (_I, [_P, _L, _P, _P, _F, _P, _P, _P, _P, _P, _I, _I, _I, _P]),
 }
@@ -138,6 +140,19 @@ def attention(q_tiles, k_tiles, v_tiles, nq, nk, q_len=None, k_len=None, scale=0
                               _ptr(_i32(k_len)), B, H, nq, nk, q_tiles.shape[2], k_tiles.shape[2], float(scale),
                               _stream()), "lg_attention")
     return out
+
+
+def assign(md0, md1, z0, z1, m_len=None, n_len=None, prescale=0.25):
+    """md0 (B,M,256), md1 (B,N,256), z0 (B,M), z1 (B,N) f32 -> log assignment (B,M+1,N+1) f32."""
+    B, M, D = md0.shape
+    N = md1.shape[1]
+    assert D == 256 and md1.shape[2] == 256
+    scores = torch.empty(B, M + 1, N + 1, device=md0.device, dtype=torch.float32)
+    ws = torch.empty(lib().lg_assign_ws_bytes(B, M, N), device=md0.device, dtype=torch.uint8)
+    _check(lib().lg_assign(_ptr(_f32c(md0, "md0")), _ptr(_f32c(md1, "md1")), _ptr(_f32c(z0, "z0")),
+                           _ptr(_f32c(z1, "z1")), _ptr(_i32(m_len)), _ptr(_i32(n_len)), float(prescale),
+                           _ptr(scores), _ptr(ws), B, M, N, _stream()), "lg_assign")
+    return scores
 
 
 def filter_matches(scores, th: float, m_len=None, n_len=None):

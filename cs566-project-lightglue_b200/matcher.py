@@ -1,0 +1,290 @@
+"""B200-native LightGlue matcher forward -- drop-in for the reference's
+gluefactory/models/matchers/lightglue.py:340-579 (class LightGlue, eval-mode forward).
+
+Same constructor (`LightGlue(conf)`, conf = dict or DictConfig merged over `default_conf`,
+lightglue.py:341-361,369), same data dict in (`keypoints0/1`, `descriptors0/1`, optional
+`view0/1.image_size`, lightglue.py:444-456), same pred dict out (lightglue.py:567-577), same
+state_dict names (lightglue.py:380-396), selected through `__main_model__` like the reference
+(lightglue.py:666; gluefactory/models/__init__.py:20-25):  `model.matcher.name: b200glue.matcher`.
+
+The hot subsystems run as hand-written sm_100a kernels behind the C ABI in include/lg_b200.h
+(positional encoding, rotary + operand packing, tcgen05 flash attention, TF32x3 assignment,
+match filter, confidence / pruning).  The per-token linears, LayerNorm and GELU stay on
+cuBLAS / torch in this cut.  There is no CPU path and no fallback: inputs
+must live on a CUDA device and the shared library must be present.
+"""
+import math
+from pathlib import Path
+
+import numpy as np
+import torch
+import torch.nn.functional as F
+from torch import nn
+
+from . import _cabi as C
+
+
+class Conf(dict):
+    """Attribute-access dict standing in for an OmegaConf DictConfig (omegaconf is optional)."""
+
+    def __getattr__(self, k):
+        try:
+            return self[k]
+        except KeyError as e:
+            raise AttributeError(k) from e
+
+    def __setattr__(self, k, v):
+        self[k] = v
+
+
+def _to_plain(c):
+    if c is None:
+        return {}
+    if isinstance(c, dict):
+        return {k: _to_plain(v) if isinstance(v, dict) else v for k, v in c.items()}
+    try:  # DictConfig
+        from omegaconf import OmegaConf
+
+        return OmegaConf.to_container(c, resolve=True)
+    except ImportError:
+        return dict(c)
+
+
+def merge_conf(default: dict, user) -> Conf:
+    out = Conf()
+    user = _to_plain(user)
+    for k, v in default.items():
+        out[k] = merge_conf(v, user.get(k)) if isinstance(v, dict) else user.get(k, v)
+    for k, v in user.items():  # unknown keys are tolerated (no struct mode in the reference)
+        if k not in out:
+            out[k] = Conf(v) if isinstance(v, dict) else v
+    return out
+
+
+class _PosEnc(nn.Module):  # parameter holder: lightglue.py:50-61
+    def __init__(self, m_in, half):
+        super().__init__()
+        self.Wr = nn.Linear(m_in, half, bias=False)
+        nn.init.normal_(self.Wr.weight.data, mean=0, std=1.0)
+        self.condition_modulation = nn.Linear(1, half)
+
+
+def _ffn(d):
+    return nn.Sequential(nn.Linear(2 * d, 2 * d), nn.LayerNorm(2 * d, elementwise_affine=True), nn.GELU(),
+                         nn.Linear(2 * d, d))
+
+
+class _SelfBlock(nn.Module):  # lightglue.py:159-176
+    def __init__(self, d):
+        super().__init__()
+        self.Wqkv = nn.Linear(d, 3 * d)
+        self.out_proj = nn.Linear(d, d)
+        self.ffn = _ffn(d)
+
+
+class _CrossBlock(nn.Module):  # lightglue.py:194-211
+    def __init__(self, d):
+        super().__init__()
+        self.to_qk = nn.Linear(d, d)
+        self.to_v = nn.Linear(d, d)
+        self.to_out = nn.Linear(d, d)
+        self.ffn = _ffn(d)
+
+
+class _Layer(nn.Module):  # lightglue.py:252-256
+    def __init__(self, d):
+        super().__init__()
+        self.self_attn = _SelfBlock(d)
+        self.cross_attn = _CrossBlock(d)
+
+
+class _Assignment(nn.Module):  # lightglue.py:299-304
+    def __init__(self, d):
+        super().__init__()
+        self.matchability = nn.Linear(d, 1)
+        self.final_proj = nn.Linear(d, d)
+
+
+class _TokenConfidence(nn.Module):  # lightglue.py:96-99
+    def __init__(self, d):
+        super().__init__()
+        self.token = nn.Sequential(nn.Linear(d, 1), nn.Sigmoid())
+
+
+def _apply_ffn(ffn, x, msg):
+    """x + Linear(GELU(LayerNorm(Linear(cat[x, msg])))) -- lightglue.py:171-176,191 (cuBLAS/torch, N1)."""
+    h = F.linear(torch.cat([x, msg], -1), ffn[0].weight, ffn[0].bias)
+    h = F.layer_norm(h, (h.shape[-1],), ffn[1].weight, ffn[1].bias, ffn[1].eps)
+    return x + F.linear(F.gelu(h), ffn[3].weight, ffn[3].bias)
+
+
+class LightGlue(nn.Module):
+    default_conf = {
+        "name": "lightglue",
+        "input_dim": 256,
+        "add_scale_ori": False,
+        "descriptor_dim": 256,
+        "n_layers": 9,
+        "num_heads": 4,
+        "flash": False,
+        "mp": False,
+        "depth_confidence": -1,
+        "width_confidence": -1,
+        "filter_threshold": 0.0,
+        "checkpointed": False,
+        "weights": None,
+        "weights_from_version": "v0.1_arxiv",
+        "loss": {"gamma": 1.0, "fn": "nll", "nll_balancing": 0.5},
+        # namespaced additions (existing YAMLs stay valid)
+        "b200": {"precision": "bf16"},
+    }
+    required_data_keys = ["keypoints0", "keypoints1", "descriptors0", "descriptors1"]
+
+    def __init__(self, conf=None) -> None:
+        super().__init__()
+        self.conf = conf = merge_conf(self.default_conf, conf)
+        d, h, L = conf.descriptor_dim, conf.num_heads, conf.n_layers
+        if d != 256 or h != 4:
+            raise ValueError("the sm_100a kernels are built for descriptor_dim=256, num_heads=4 (no fallback)")
+        if conf.add_scale_ori:
+            raise NotImplementedError("add_scale_ori (4-d positional input) is not built; SuperPoint/DISK use 2-d")
+        if conf.b200.precision not in ("bf16",):
+            raise ValueError(f"b200.precision={conf.b200.precision!r}: only 'bf16' attention operands are built")
+        self.input_proj = nn.Linear(conf.input_dim, d, bias=True) if conf.input_dim != d else nn.Identity()
+        self.posenc = _PosEnc(2, (d // h) // 2)
+        self.transformers = nn.ModuleList([_Layer(d) for _ in range(L)])
+        self.log_assignment = nn.ModuleList([_Assignment(d) for _ in range(L)])
+        self.token_confidence = nn.ModuleList([_TokenConfidence(d) for _ in range(L - 1)])
+        # the attribute the fork forgot: thresholds as an fp32 table
+        self.register_buffer(
+            "confidence_thresholds",
+            torch.tensor([self.confidence_threshold(i) for i in range(L)], dtype=torch.float32), persistent=False)
+        if conf.weights is not None:
+            self._load_weights(conf.weights)
+        self.eval()
+
+    # ------------------------------------------------------------------ weights (lightglue.py:400-430)
+    def _load_weights(self, weights):
+        path = Path(weights)
+        if not path.exists():
+            raise FileNotFoundError(f"weights {weights!r}: only local files are supported (no network on the box)")
+        state = torch.load(str(path), map_location="cpu")
+        if "model" in state and isinstance(state["model"], dict):
+            state = state["model"]
+        self.load_state_dict(self.rename_legacy_keys(state, self.conf.n_layers), strict=False)
+
+    @staticmethod
+    def rename_legacy_keys(state, n_layers):
+        for i in range(n_layers):  # lightglue.py:425-429
+            state = {k.replace(f"self_attn.{i}", f"transformers.{i}.self_attn"): v for k, v in state.items()}
+            state = {k.replace(f"cross_attn.{i}", f"transformers.{i}.cross_attn"): v for k, v in state.items()}
+        return state
+
+    def confidence_threshold(self, layer_index: int) -> float:  # lightglue.py:581-584
+        return float(np.clip(0.8 + 0.1 * np.exp(-4.0 * layer_index / self.conf.n_layers), 0, 1))
+
+    # ------------------------------------------------------------------ blocks
+    def _self_block(self, blk, x, cs, lens):
+        H = self.conf.num_heads
+        qkv = F.linear(x, blk.Wqkv.weight, blk.Wqkv.bias)
+        q, k, v = C.pack_self_qkv(qkv, cs[0], cs[1], lens, H)
+        n = x.shape[1]
+        ctx = C.attention(q, k, v, n, n, lens, lens, scale=64 ** -0.5)
+        msg = F.linear(ctx, blk.out_proj.weight, blk.out_proj.bias)
+        return _apply_ffn(blk.ffn, x, msg)
+
+    def _cross_block(self, blk, x0, x1, len0, len1):
+        H = self.conf.num_heads
+        qk0, qk1 = F.linear(x0, blk.to_qk.weight, blk.to_qk.bias), F.linear(x1, blk.to_qk.weight, blk.to_qk.bias)
+        v0, v1 = F.linear(x0, blk.to_v.weight, blk.to_v.bias), F.linear(x1, blk.to_v.weight, blk.to_v.bias)
+        qt0, vt0 = C.pack_cross_qkv(qk0, v0, len0, H)
+        qt1, vt1 = C.pack_cross_qkv(qk1, v1, len1, H)
+        m, n = x0.shape[1], x1.shape[1]
+        # each direction is one flash pass over the shared to_qk projection (why the
+        # similarity tile is not shared between the two softmax directions)
+        m0 = C.attention(qt0, qt1, vt1, m, n, len0, len1, scale=64 ** -0.5)
+        m1 = C.attention(qt1, qt0, vt0, n, m, len1, len0, scale=64 ** -0.5)
+        m0 = F.linear(m0, blk.to_out.weight, blk.to_out.bias)
+        m1 = F.linear(m1, blk.to_out.weight, blk.to_out.bias)
+        return _apply_ffn(blk.ffn, x0, m0), _apply_ffn(blk.ffn, x1, m1)
+
+    def _assign(self, i, d0, d1, len0, len1):
+        head = self.log_assignment[i]
+        md0 = F.linear(d0, head.final_proj.weight, head.final_proj.bias)
+        md1 = F.linear(d1, head.final_proj.weight, head.final_proj.bias)
+        z0 = F.linear(d0, head.matchability.weight, head.matchability.bias).squeeze(-1).contiguous()
+        z1 = F.linear(d1, head.matchability.weight, head.matchability.bias).squeeze(-1).contiguous()
+        return C.assign(md0, md1, z0, z1, len0, len1, prescale=self.conf.descriptor_dim ** -0.25)
+
+    @staticmethod
+    def _image_size(data, view, like):
+        v = data.get(view)
+        size = None if v is None else v.get("image_size")
+        if size is None:
+            return None
+        if not isinstance(size, torch.Tensor):
+            size = torch.tensor(size)
+        size = size.to(device=like.device, dtype=torch.float32)
+        if size.dim() == 1:
+            size = size[None].expand(like.shape[0], 2)
+        return size.contiguous()
+
+    @staticmethod
+    def _lens(data, key, n, device):
+        v = data.get(key)
+        if v is None:
+            return None
+        return torch.as_tensor(v, device=device).to(torch.int32).clamp(0, n).contiguous()
+
+    # ------------------------------------------------------------------ forward (lightglue.py:444-579)
+    @torch.no_grad()
+    def forward(self, data: dict) -> dict:
+        for key in self.required_data_keys:
+            assert key in data, f"Missing key {key} in data"
+        conf = self.conf
+        kpts0, kpts1 = data["keypoints0"], data["keypoints1"]
+        if not kpts0.is_cuda:
+            raise RuntimeError("b200glue LightGlue runs on CUDA (sm_100a) only; move the batch to the GPU")
+        b, m, _ = kpts0.shape
+        _, n, _ = kpts1.shape
+        dev = kpts0.device
+        desc0 = data["descriptors0"].contiguous().float()
+        desc1 = data["descriptors1"].contiguous().float()
+        assert desc0.shape[-1] == conf.input_dim and desc1.shape[-1] == conf.input_dim
+        len0 = self._lens(data, "num_keypoints0", m, dev)
+        len1 = self._lens(data, "num_keypoints1", n, dev)
+        pe = self.posenc
+        wc = pe.condition_modulation.weight.reshape(-1)
+        cs0 = C.posenc(kpts0.float().contiguous(), self._image_size(data, "view0", kpts0), pe.Wr.weight, wc,
+                       pe.condition_modulation.bias, float(m))
+        cs1 = C.posenc(kpts1.float().contiguous(), self._image_size(data, "view1", kpts1), pe.Wr.weight, wc,
+                       pe.condition_modulation.bias, float(n))
+        if conf.input_dim != conf.descriptor_dim:
+            desc0 = F.linear(desc0, self.input_proj.weight, self.input_proj.bias)
+            desc1 = F.linear(desc1, self.input_proj.weight, self.input_proj.bias)
+
+        do_early_stop = conf.depth_confidence > 0
+        do_point_pruning = conf.width_confidence > 0
+        if do_early_stop or do_point_pruning:
+            from .adaptive import forward_adaptive
+
+            return forward_adaptive(self, data, desc0, desc1, cs0, cs1)
+
+        L = conf.n_layers
+        for i in range(L):
+            layer = self.transformers[i]
+            desc0 = self._self_block(layer.self_attn, desc0, cs0, len0)
+            desc1 = self._self_block(layer.self_attn, desc1, cs1, len1)
+            desc0, desc1 = self._cross_block(layer.cross_attn, desc0, desc1, len0, len1)
+        scores = self._assign(L - 1, desc0, desc1, len0, len1)
+        m0, m1, ms0, ms1 = C.filter_matches(scores, conf.filter_threshold, len0, len1)
+        return {
+            "matches0": m0, "matches1": m1,
+            "matching_scores0": ms0, "matching_scores1": ms1,
+            "ref_descriptors0": desc0[:, None], "ref_descriptors1": desc1[:, None],
+            "log_assignment": scores,
+            "prune0": torch.ones_like(ms0) * L, "prune1": torch.ones_like(ms1) * L,
+        }
+
+
+__main_model__ = LightGlue

@@ -59,6 +59,16 @@ int lg_attention(const void* q_tiles, const void* k_tiles, const void* v_tiles, 
                  const int* k_len, int B, int H, int nq, int nk, int tq_pad, int tk_pad, float softmax_scale,
                  cudaStream_t stream);
 
+/* (3) MatchAssignment.forward from the similarity on (lightglue.py:310-315) + sigmoid_log_double_softmax
+ * (lightglue.py:284-296).  md0 (B,M,256), md1 (B,N,256) f32 = final_proj outputs; prescale multiplies
+ * both (d^-1/4 = 0.25, lightglue.py:310); z0 (B,M), z1 (B,N) f32 matchability logits.  Writes scores
+ * (B,M+1,N+1) f32 contiguous.  Similarity GEMM: TF32x3 on tcgen05, fp32 accumulate.  Padded entries
+ * of a variable-count pair (row >= m_len or col >= n_len) are -inf; the dustbin row/column stay at
+ * index M / N.  ws: lg_assign_ws_bytes(B,M,N) bytes of scratch. */
+size_t lg_assign_ws_bytes(int B, int M, int N);
+int lg_assign(const float* md0, const float* md1, const float* z0, const float* z1, const int* m_len,
+              const int* n_len, float prescale, float* scores, void* ws, int B, int M, int N, cudaStream_t stream);
+
 /* (4) filter_matches (lightglue.py:321-337) on scores (B, M+1, N+1) f32, row pitch `pitch` floats
  * (>= N+1), image pitch (M+1)*pitch.  m_len/n_len: per-pair valid M/N (NULL = M,N).
  * Outputs m0 (B,M) i64, m1 (B,N) i64, ms0 (B,M) f32, ms1 (B,N) f32.  ws: lg_filter_ws_bytes(B,M,N)

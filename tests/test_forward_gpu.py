@@ -1,0 +1,103 @@
+"""GPU end-to-end parity: the drop-in matcher against the golden reference outputs and the oracle."""
+import numpy as np
+import pytest
+import torch
+
+from conftest import load_golden, pkg
+from oracle import lightglue_oracle as O
+
+pytestmark = pytest.mark.gpu
+W = pkg("weights")
+
+BF16_TOL = 2e-2  # north_star: bf16 path, abs on log_assignment
+
+
+def _cuda(data):
+    return {k: ({kk: vv.cuda() for kk, vv in v.items()} if isinstance(v, dict) else v.cuda()) for k, v in data.items()}
+
+
+def _model(conf, sd):
+    M = pkg("matcher")
+    model = M.LightGlue(conf)
+    missing, unexpected = model.load_state_dict(sd, strict=True)
+    return model.cuda()
+
+
+def _golden_inputs(meta):
+    conf = meta["conf"]
+    sd = W.make_state_dict(conf, seed=meta["weight_seed"], adaptive_fixture=meta["adaptive_fixture"])
+    data = W.make_inputs(meta["batch"], meta["m"], meta["n"], d_in=conf.get("input_dim", 256),
+                         seed=meta["data_seed"], image_size=tuple(meta["image_size"]), correlated=meta["correlated"])
+    return conf, sd, data
+
+
+@pytest.mark.parametrize("name", ["sp_b1_192", "sp_b2_160x224", "disk_b1_130x97", "sp_b1_1024"])
+def test_forward_vs_golden(name):
+    meta, g = load_golden("fwd_" + name)
+    conf, sd, data = _golden_inputs(meta)
+    pred = _model(conf, sd)(_cuda(data))
+    la = pred["log_assignment"].cpu().numpy()
+    assert list(la.shape) == meta["la_shape"]
+    if "log_assignment" in g:
+        err = np.abs(la - g["log_assignment"]).max()
+    else:
+        err = np.abs(la[:, ::17, ::19] - g["log_assignment_sample"]).max()
+    agree0 = (pred["matches0"].cpu().numpy() == g["matches0"]).mean()
+    agree1 = (pred["matches1"].cpu().numpy() == g["matches1"]).mean()
+    print(f"{name}: max|dlog_assignment|={err:.3e} match agreement {agree0:.4f}/{agree1:.4f}")
+    assert err < BF16_TOL, err
+    assert agree0 > 0.97 and agree1 > 0.97
+    for k in ("matches0", "matches1", "prune0", "prune1"):
+        assert pred[k].cpu().numpy().dtype == g[k].dtype and pred[k].shape == g[k].shape, k
+    assert float(pred["prune0"][0, 0]) == 9.0
+    assert pred["ref_descriptors0"].shape == (meta["batch"], 1, meta["m"], 256)
+
+
+def test_forward_varlen_vs_golden():
+    meta, g = load_golden("varlen_disk_b3_256")
+    conf = meta["conf"]
+    sd = W.make_state_dict(conf, seed=meta["weight_seed"])
+    data = W.make_inputs(meta["batch"], meta["npad"], meta["npad"], d_in=128, seed=meta["data_seed"],
+                         image_size=tuple(meta["image_size"]), correlated=meta["correlated"])
+    data = _cuda(data)
+    data["num_keypoints0"] = torch.tensor(meta["len0"]).cuda()
+    data["num_keypoints1"] = torch.tensor(meta["len1"]).cuda()
+    pred = _model(conf, sd)(data)
+    la = pred["log_assignment"].cpu().numpy()
+    M = N = meta["npad"]
+    for p in range(meta["batch"]):
+        a, c = meta["len0"][p], meta["len1"][p]
+        ref = g[f"log_assignment_{p}"][0]
+        assert np.abs(la[p, :a, :c] - ref[:a, :c]).max() < BF16_TOL
+        assert np.abs(la[p, :a, N] - ref[:a, c]).max() < BF16_TOL
+        assert np.abs(la[p, M, :c] - ref[a, :c]).max() < BF16_TOL
+        m0 = pred["matches0"][p, :a].cpu().numpy()
+        assert (m0 == g[f"matches0_{p}"][0]).mean() > 0.95
+        assert (pred["matches0"][p, a:] == -1).all()
+
+
+def test_forward_2048_vs_oracle():
+    """BASELINE config-2 shape (one pair of it): 2048 keypoints, SuperPoint-shaped."""
+    conf = {"filter_threshold": 0.1}
+    sd = W.make_state_dict(conf, seed=0)
+    data = W.make_inputs(1, 2048, 2048, seed=1, correlated=0.7)
+    ref = O.forward(sd, conf, data)
+    pred = _model(conf, sd)(_cuda(data))
+    err = (pred["log_assignment"].cpu() - ref["log_assignment"]).abs().max().item()
+    agree = (pred["matches0"].cpu() == ref["matches0"]).float().mean().item()
+    print(f"2048: max|dlog_assignment|={err:.3e} match agreement {agree:.4f}")
+    assert err < BF16_TOL and agree > 0.97
+
+
+def test_registry_alias_and_errors():
+    import importlib
+
+    mod = importlib.import_module("b200glue.matcher")
+    assert mod.__main_model__ is pkg("matcher").LightGlue
+    model = mod.__main_model__({"filter_threshold": 0.1, "some_unknown_key": 1})
+    assert model.conf.filter_threshold == 0.1 and model.conf.n_layers == 9
+    with pytest.raises(AssertionError):
+        model({"keypoints0": torch.zeros(1, 4, 2)})
+    with pytest.raises(RuntimeError):  # CPU tensors: no fallback
+        d = W.make_inputs(1, 8, 8)
+        model(d)

@@ -188,3 +188,40 @@ def test_attention_varlen(C):
     for e32, eb in errs:
         assert e32 < 3e-2 and eb < 1.5e-2, (e32, eb)
     errs = _attn_case(C, 2, 4, 256, 256, [256, 256], [0, 256], seed=10)
+
+
+# ----------------------------------------------------------------------------- (3) assignment
+@pytest.mark.parametrize("B,M,N", [(1, 128, 128), (2, 200, 333), (1, 1024, 1024), (2, 2048, 2048), (1, 1, 700)])
+def test_assign_vs_oracle(C, B, M, N):
+    g = _gen(M + 3 * N)
+    md0 = torch.randn(B, M, 256, generator=g) * 1.5
+    md1 = torch.randn(B, N, 256, generator=g) * 1.5
+    z0, z1 = torch.randn(B, M, 1, generator=g) * 2, torch.randn(B, N, 1, generator=g) * 2
+    sim = torch.einsum("bmd,bnd->bmn", (md0 / 4).double(), (md1 / 4).double())
+    ref64 = O.sigmoid_log_double_softmax(sim, z0.double(), z1.double())
+    ref32 = O.sigmoid_log_double_softmax(torch.einsum("bmd,bnd->bmn", md0 / 4, md1 / 4), z0, z1)
+    got = C.assign(md0.cuda(), md1.cuda(), z0[..., 0].contiguous().cuda(), z1[..., 0].contiguous().cuda()).cpu()
+    e64 = (got.double() - ref64).abs().max().item()
+    e32ref = (ref32.double() - ref64).abs().max().item()
+    # TF32x3 must be as good as the fp32 reference itself (north_star: 1e-4 abs end to end)
+    assert e64 < max(3e-5, 3 * e32ref), (e64, e32ref)
+    assert got[:, -1, -1].abs().max() == 0
+
+
+def test_assign_varlen(C):
+    g = _gen(77)
+    B, M, N = 3, 300, 260
+    ml, nl = [300, 17, 129], [260, 260, 1]
+    md0, md1 = torch.randn(B, M, 256, generator=g), torch.randn(B, N, 256, generator=g)
+    z0, z1 = torch.randn(B, M, 1, generator=g), torch.randn(B, N, 1, generator=g)
+    got = C.assign(md0.cuda(), md1.cuda(), z0[..., 0].contiguous().cuda(), z1[..., 0].contiguous().cuda(),
+                   torch.tensor(ml, dtype=torch.int32).cuda(), torch.tensor(nl, dtype=torch.int32).cuda()).cpu()
+    for b in range(B):
+        a, c = ml[b], nl[b]
+        sim = torch.einsum("bmd,bnd->bmn", md0[b:b + 1, :a] / 4, md1[b:b + 1, :c] / 4)
+        ref = O.sigmoid_log_double_softmax(sim, z0[b:b + 1, :a], z1[b:b + 1, :c])[0]
+        assert (got[b, :a, :c] - ref[:a, :c]).abs().max() < 3e-5
+        assert (got[b, :a, N] - ref[:a, c]).abs().max() < 1e-6
+        assert (got[b, M, :c] - ref[a, :c]).abs().max() < 1e-6
+        if a < M:
+            assert torch.isinf(got[b, a:M, :N]).all()
