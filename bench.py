@@ -1,0 +1,258 @@
+#!/usr/bin/env python
+"""Throughput bench for the B200-native LightGlue matcher forward.
+
+  python bench.py --gpus N --steps K --warmup W            # this repo's CUDA path
+  python bench.py --impl reference --gpus N --steps K ...   # the reference's CPU path (oracle port)
+
+Metric (BASELINE.json): image pairs/sec at 2048 keypoints/image.  One step = one forward over
+a batch of 32 synthetic pairs x 2048 SuperPoint-shaped keypoints (BASELINE config 2) per GPU;
+pairs shard across ranks with no data-path collective (weak scaling).  Prints ONE JSON line.
+"""
+import argparse
+import importlib
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+import torch
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+PKG = "cs566-project-lightglue_b200"
+METRIC, UNIT = "image pairs/sec @2048 kp/img", "pairs/s"
+CONF = {"filter_threshold": 0.1}
+
+
+def parse():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=10)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
+    ap.add_argument("--batch", type=int, default=32, help="pairs per GPU per step")
+    ap.add_argument("--kpts", type=int, default=2048)
+    ap.add_argument("--cpu-pairs", type=int, default=4, help="pairs timed for the cpu_baseline sample")
+    return ap.parse_args()
+
+
+def workload_name(a):
+    return f"SuperPoint+LightGlue (9 layers, d=256, 4 heads), {a.batch} pairs x {a.kpts} keypoints per GPU, synthetic"
+
+
+# ----------------------------------------------------------------------------- CPU arm (oracle port)
+def cpu_forward_rate(kpts: int, pairs: int, warm: int = 1):
+    """pairs/s of the reference algorithm on the host cores: the oracle port (torch CPU ops in the
+    reference's op order, bit-identical to the reference module in the build container), B=1 per
+    forward as the reference's eval loop does (utils/export_predictions.py:32)."""
+    from oracle import lightglue_oracle as O
+
+    W = importlib.import_module(PKG + ".weights")
+    cores = os.cpu_count() or 1
+    torch.set_num_threads(cores)
+    sd = W.make_state_dict(CONF, seed=0)
+    data = W.make_inputs(1, kpts, kpts, seed=1)
+    for _ in range(warm):
+        O.forward(sd, CONF, data)
+    t0 = time.perf_counter()
+    for _ in range(pairs):
+        O.forward(sd, CONF, data)
+    dt = time.perf_counter() - t0
+    return pairs / dt, cores, dt
+
+
+def run_reference(a):
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return
+    # each step = a bounded sample of the workload: ONE pair of the 32-pair batch
+    for _ in range(max(a.warmup, 1)):
+        rate, cores, _ = cpu_forward_rate(a.kpts, 1, warm=0)
+    t0 = time.perf_counter()
+    rate, cores, dt = cpu_forward_rate(a.kpts, a.steps, warm=0)
+    sample = f"{a.steps} forwards of 1 pair x {a.kpts} kpts (1/{a.batch} of the step's batch), fp32, {cores} threads"
+    print(json.dumps({
+        "impl": "reference", "metric": METRIC, "value": rate, "unit": UNIT, "n_gpus": a.gpus, "steps": a.steps,
+        "warmup": a.warmup, "ms_per_step": 1e3 * dt / a.steps, "higher_is_better": True, "scaling": "weak",
+        "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+        "config": {"workload": workload_name(a), "note": "CPU arm: oracle port of the reference (Python reference cannot travel)"},
+        "cpu_baseline": {"value": rate, "unit": UNIT, "cores": cores, "kind": "port", "sample": sample},
+        "e2e": {"value": rate, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        "gpu_launches": 0,
+    }), flush=True)
+
+
+# ----------------------------------------------------------------------------- clocks sampler
+class ClockSampler(threading.Thread):
+    Q = "clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown," \
+        "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap"
+
+    def __init__(self, index):
+        super().__init__(daemon=True)
+        self.index, self.samples, self.stop_flag = index, [], False
+
+    def run(self):
+        while not self.stop_flag:
+            try:
+                out = subprocess.run(["nvidia-smi", "-i", str(self.index), f"--query-gpu={self.Q}",
+                                      "--format=csv,noheader,nounits"], capture_output=True, text=True, timeout=5).stdout
+                f = [x.strip() for x in out.strip().split(",")]
+                if len(f) >= 6:
+                    self.samples.append(f)
+            except Exception:
+                pass
+            time.sleep(0.1)
+
+    def summary(self):
+        if not self.samples:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["unsampled"]}
+        mhz = sorted(int(s[0]) for s in self.samples if s[0].isdigit())
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        reasons = [n for i, n in enumerate(names) if any(s[2 + i].lower().startswith("active") for s in self.samples)]
+        return {"sm_mhz": mhz[len(mhz) // 2] if mhz else None,
+                "sm_max_mhz": int(self.samples[0][1]) if self.samples[0][1].isdigit() else None,
+                "reasons": reasons, "samples": len(self.samples)}
+
+
+# ----------------------------------------------------------------------------- GPU arm
+def to_device(data, dev, non_blocking=True):
+    return {k: ({kk: vv.to(dev, non_blocking=non_blocking) for kk, vv in v.items()} if isinstance(v, dict)
+                else v.to(dev, non_blocking=non_blocking)) for k, v in data.items()}
+
+
+def pin(data):
+    return {k: ({kk: vv.pin_memory() for kk, vv in v.items()} if isinstance(v, dict) else v.pin_memory())
+            for k, v in data.items()}
+
+
+def nbytes(data):
+    return sum((sum(vv.numel() * vv.element_size() for vv in v.values()) if isinstance(v, dict)
+                else v.numel() * v.element_size()) for v in data.values())
+
+
+def run_b200(a):
+    import torch.distributed as dist
+
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    if not torch.cuda.is_available():
+        raise RuntimeError("bench.py (impl b200) needs a CUDA device: there is no CPU fallback")
+    torch.cuda.set_device(local)
+    dev = torch.device("cuda", local)
+    distributed = world > 1
+    if distributed:
+        dist.init_process_group("nccl", device_id=dev)
+    C = importlib.import_module(PKG + "._cabi")
+    M = importlib.import_module(PKG + ".matcher")
+    W = importlib.import_module(PKG + ".weights")
+    model = M.LightGlue(CONF)
+    model.load_state_dict(W.make_state_dict(CONF, seed=0), strict=True)
+    model = model.to(dev)
+    host = pin(W.make_inputs(a.batch, a.kpts, a.kpts, seed=1 + rank))  # each rank owns its own pairs
+    data = to_device(host, dev)
+    torch.cuda.synchronize()
+
+    def barrier():
+        if distributed:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    def timed(fn, steps):
+        barrier()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        for _ in range(steps):
+            fn()
+        e1.record()
+        barrier()
+        ms = torch.tensor([e0.elapsed_time(e1)], device=dev)
+        if distributed:
+            dist.all_reduce(ms, op=dist.ReduceOp.MAX)
+        return float(ms.item())
+
+    # ---- device-resident throughput ("value")
+    def step():
+        return model(data)
+
+    for _ in range(max(a.warmup, 3)):
+        step()
+    sampler = ClockSampler(local)
+    sampler.start()
+    l0 = C.LAUNCHES
+    ms = timed(step, a.steps)
+    launches = C.LAUNCHES - l0
+    sampler.stop_flag = True
+    value = world * a.batch * a.steps / (ms / 1e3)
+
+    # ---- end to end through the public API with HOST buffers ("e2e")
+    out_host = {k: torch.empty((a.batch, a.kpts), dtype=dt).pin_memory()
+                for k, dt in (("matches0", torch.int64), ("matches1", torch.int64),
+                              ("matching_scores0", torch.float32), ("matching_scores1", torch.float32))}
+
+    def step_e2e():
+        pred = model(to_device(host, dev))
+        for k, buf in out_host.items():
+            buf.copy_(pred[k], non_blocking=True)
+        torch.cuda.current_stream().synchronize()  # the caller reads the matches (export_predictions.py:68)
+
+    for _ in range(2):
+        step_e2e()
+    ms_e2e = timed(step_e2e, a.steps)
+    e2e = world * a.batch * a.steps / (ms_e2e / 1e3)
+
+    # ---- roofline of the dominant kernel (attention): CUDA events around every launch
+    C.ATTN_EVENTS = []
+    barrier()
+    for _ in range(min(a.steps, 3)):
+        step()
+    torch.cuda.synchronize()
+    ev = C.ATTN_EVENTS
+    C.ATTN_EVENTS = None
+    attn_ms = sum(e0.elapsed_time(e1) for e0, e1, _ in ev)
+    attn_flops = sum(f for _, _, f in ev)
+    peaks = {}
+    try:
+        peaks = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))
+    except Exception:
+        pass
+    peak = float(peaks.get("bf16_tflops_sustained", 1400.0))  # kernel timed inside a long step
+    achieved = attn_flops / (attn_ms / 1e3) / 1e12
+    roofline = {"kernel": "attention_kernel (tcgen05 flash attention, self + cross)", "bound": "tensor",
+                "achieved": achieved, "peak": peak, "unit": "TFLOP/s", "frac": achieved / peak, "traffic": None,
+                "peak_source": "MEASURED_PEAKS.json bf16_tflops_sustained" if peaks else "fallback 1.4 PFLOP/s sustained",
+                "launches_timed": len(ev), "avg_launch_ms": attn_ms / max(len(ev), 1),
+                "share_of_step": attn_ms / max(min(a.steps, 3), 1) / (ms / a.steps)}
+
+    if rank == 0:
+        cpu_rate, cores, cpu_dt = cpu_forward_rate(a.kpts, a.cpu_pairs)
+        line = {
+            "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": a.steps, "warmup": max(a.warmup, 3),
+            "ms_per_step": ms / a.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+            "dtype": "bf16 attention operands / tf32x3 assignment / f32 elsewhere", "data": "synthetic",
+            "config": {"workload": workload_name(a), "pairs_per_gpu": a.batch, "keypoints": a.kpts,
+                       "l2": "inputs+activations per step (>4 GB) exceed the 126 MB L2; no flush needed",
+                       "parallelism": f"pairs sharded over {world} GPU(s), no data-path collective"},
+            "e2e": {"value": e2e, "unit": UNIT, "h2d_bytes_per_step": nbytes(host),
+                    "d2h_bytes_per_step": sum(v.numel() * v.element_size() for v in out_host.values()),
+                    "ms_per_step": ms_e2e / a.steps},
+            "gpu_launches": launches,
+            "roofline": roofline,
+            "cpu_baseline": {"value": cpu_rate, "unit": UNIT, "cores": cores, "kind": "port",
+                             "sample": f"{a.cpu_pairs} forwards of 1 pair x {a.kpts} kpts ({cpu_dt:.1f} s), fp32 torch CPU"},
+            "clocks": sampler.summary(),
+        }
+        print(json.dumps(line), flush=True)
+    if distributed:
+        dist.barrier()
+        dist.destroy_process_group()
+
+
+if __name__ == "__main__":
+    args = parse()
+    if args.impl == "reference":
+        run_reference(args)
+    else:
+        run_b200(args)

@@ -34,6 +34,16 @@ SIGNATURES = {
 
 _lib = None
 
+# kernels launched by this library since import (bench.py reports it as gpu_launches)
+LAUNCHES = 0
+# when a list, attention() appends (start_event, end_event, flops) around every launch
+ATTN_EVENTS = None
+
+
+def _count(n):
+    global LAUNCHES
+    LAUNCHES += n
+
 
 def build(verbose: bool = False) -> str:
     """Compile csrc/*.cu for sm_100a into liblg_b200.so (nvcc cross-compiles without a GPU)."""
@@ -107,6 +117,7 @@ def posenc(kpts, size, wr, wc, bc, cond: float):
     sin = torch.empty_like(cos)
     _check(lib().lg_posenc(_ptr(kpts), _ptr(_f32c(size, "size")), _ptr(_f32c(wr, "wr")), _ptr(_f32c(wc, "wc")),
                            _ptr(_f32c(bc, "bc")), float(cond), _ptr(cos), _ptr(sin), B, N, _stream()), "lg_posenc")
+    _count(1)
     return cos, sin
 
 
@@ -120,6 +131,7 @@ def pack_self_qkv(qkv, cos, sin, lens=None, H=4):
     q, k, v = (alloc_tiles(B, H, N, qkv.device) for _ in range(3))
     _check(lib().lg_pack_self_qkv(_ptr(_f32c(qkv, "qkv")), _ptr(cos), _ptr(sin), _ptr(_i32(lens)), _ptr(q), _ptr(k),
                                   _ptr(v), B, N, H, tiles_pad(N), _stream()), "lg_pack_self_qkv")
+    _count(1)
     return q, k, v
 
 
@@ -129,6 +141,7 @@ def pack_cross_qkv(qk, v, lens=None, H=4):
     qt, vt = alloc_tiles(B, H, N, qk.device), alloc_tiles(B, H, N, qk.device)
     _check(lib().lg_pack_cross_qkv(_ptr(_f32c(qk, "qk")), _ptr(_f32c(v, "v")), _ptr(_i32(lens)), _ptr(qt), _ptr(vt),
                                    B, N, H, tiles_pad(N), _stream()), "lg_pack_cross_qkv")
+    _count(1)
     return qt, vt
 
 
@@ -136,9 +149,16 @@ def attention(q_tiles, k_tiles, v_tiles, nq, nk, q_len=None, k_len=None, scale=0
     """-> context (B, nq, H*64) f32."""
     B, H = q_tiles.shape[:2]
     out = torch.empty(B, nq, H * 64, device=q_tiles.device, dtype=torch.float32)
+    if ATTN_EVENTS is not None:
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
     _check(lib().lg_attention(_ptr(q_tiles), _ptr(k_tiles), _ptr(v_tiles), _ptr(out), _ptr(_i32(q_len)),
                               _ptr(_i32(k_len)), B, H, nq, nk, q_tiles.shape[2], k_tiles.shape[2], float(scale),
                               _stream()), "lg_attention")
+    if ATTN_EVENTS is not None:
+        e1.record()
+        ATTN_EVENTS.append((e0, e1, 4.0 * 64 * nq * nk * B * H))  # algorithmic: QK^T + PV, 2 FLOP/MAC
+    _count(1)
     return out
 
 
@@ -152,6 +172,7 @@ def assign(md0, md1, z0, z1, m_len=None, n_len=None, prescale=0.25):
     _check(lib().lg_assign(_ptr(_f32c(md0, "md0")), _ptr(_f32c(md1, "md1")), _ptr(_f32c(z0, "z0")),
                            _ptr(_f32c(z1, "z1")), _ptr(_i32(m_len)), _ptr(_i32(n_len)), float(prescale),
                            _ptr(scores), _ptr(ws), B, M, N, _stream()), "lg_assign")
+    _count(5)
     return scores
 
 
@@ -170,4 +191,5 @@ def filter_matches(scores, th: float, m_len=None, n_len=None):
     ws = torch.empty(lib().lg_filter_ws_bytes(B, M, N), device=dev, dtype=torch.uint8)
     _check(lib().lg_filter_matches(_ptr(scores), N1, _ptr(_i32(m_len)), _ptr(_i32(n_len)), float(th), _ptr(m0),
                                    _ptr(m1), _ptr(ms0), _ptr(ms1), _ptr(ws), B, M, N, _stream()), "lg_filter_matches")
+    _count(2)
     return m0, m1, ms0, ms1
