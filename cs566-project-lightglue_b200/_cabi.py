@@ -28,6 +28,9 @@ SIGNATURES = {
     "lg_attention": (_I, [_P, _P, _P, _P, _P, _P, _I, _I, _I, _I, _I, _I, _F, _P]),
     "lg_assign_ws_bytes": (_c.c_size_t, [_I, _I, _I]),
     "lg_assign": (_I, [_P, _P, _P, _P, _P, _P, _F, _P, _P, _I, _I, _I, _P]),
+    "lg_token_scores": (_I, [_P, _P, _P, _P, _P, _P, _P, _P, _I, _I, _P]),
+    "lg_prune_plan": (_I, [_P, _P, _P, _F, _F, _P, _P, _I, _I, _P]),
+    "lg_prune_gather": (_I, [_P, _P, _P, _P, _P, _P, _P, _P, _P, _P, _P, _I, _I, _I, _I, _P]),
     "lg_filter_ws_bytes": (_c.c_size_t, [_I, _I, _I]),
     "lg_filter_matches": (_I, [_P, _L, _P, _P, _F, _P, _P, _P, _P, _P, _I, _I, _I, _P]),
 }
@@ -193,3 +196,39 @@ def filter_matches(scores, th: float, m_len=None, n_len=None):
                                    _ptr(m1), _ptr(ms0), _ptr(ms1), _ptr(ws), B, M, N, _stream()), "lg_filter_matches")
     _count(2)
     return m0, m1, ms0, ms1
+
+
+def token_scores(desc, w_tok, b_tok, w_match, b_match, lens=None):
+    """-> (conf or None, match), each (B,N) f32. w_tok None skips the confidence head."""
+    B, N, D = desc.shape
+    assert D == 256
+    match = torch.empty(B, N, device=desc.device, dtype=torch.float32)
+    conf = torch.empty_like(match) if w_tok is not None else None
+    _check(lib().lg_token_scores(_ptr(_f32c(desc, "desc")), _ptr(w_tok), _ptr(b_tok), _ptr(_f32c(w_match, "w_match")),
+                                 _ptr(b_match), _ptr(_i32(lens)), _ptr(conf), _ptr(match), B, N, _stream()),
+           "lg_token_scores")
+    _count(1)
+    return conf, match
+
+
+def prune_plan(conf, match, thr: float, min_match: float, lens=None):
+    """-> keep_idx (B,N) i32 (first counts[b,0] entries valid, ascending), counts (B,2) i32."""
+    B, N = match.shape
+    keep_idx = torch.empty(B, N, device=match.device, dtype=torch.int32)
+    counts = torch.empty(B, 2, device=match.device, dtype=torch.int32)
+    _check(lib().lg_prune_plan(_ptr(conf), _ptr(_f32c(match, "match")), _ptr(_i32(lens)), float(thr), float(min_match),
+                               _ptr(keep_idx), _ptr(counts), B, N, _stream()), "lg_prune_plan")
+    _count(1)
+    return keep_idx, counts
+
+
+def prune_gather(desc, cos, sin, ind, keep_idx, counts, prune):
+    """Gather kept rows into fresh (B,N,..) buffers (rows >= counts[b,0] are unspecified)."""
+    B, N, _ = desc.shape
+    desc_o, cos_o, sin_o, ind_o = torch.empty_like(desc), torch.empty_like(cos), torch.empty_like(sin), torch.empty_like(ind)
+    assert ind.dtype == torch.int64 and prune.dtype == torch.int64
+    _check(lib().lg_prune_gather(_ptr(_f32c(desc, "desc")), _ptr(_f32c(cos, "cos")), _ptr(_f32c(sin, "sin")), _ptr(ind),
+                                 _ptr(keep_idx), _ptr(counts), _ptr(desc_o), _ptr(cos_o), _ptr(sin_o), _ptr(ind_o),
+                                 _ptr(prune), B, N, N, prune.shape[1], _stream()), "lg_prune_gather")
+    _count(1)
+    return desc_o, cos_o, sin_o, ind_o

@@ -77,6 +77,24 @@ size_t lg_filter_ws_bytes(int B, int M, int N);
 int lg_filter_matches(const float* scores, int64_t pitch, const int* m_len, const int* n_len, float th, int64_t* m0,
                       int64_t* m1, float* ms0, float* ms1, void* ws, int B, int M, int N, cudaStream_t stream);
 
+/* (5) adaptive depth / width (lightglue.py:527-547).
+ * lg_token_scores: conf (B,N) = sigmoid(w_tok.desc + b_tok) (TokenConfidence.forward :102-107; w_tok NULL
+ *   => skipped) and match (B,N) = sigmoid(w_match.desc + b_match) (get_matchability :317-318), one read
+ *   of desc (B,N,256).
+ * lg_prune_plan: keep = match > min_match | conf <= thr (get_pruning_mask :586-593; conf NULL => first
+ *   term only); keep_idx (B,N) i32 = ascending kept positions (== torch.where(mask)[1]); counts (B,2) i32
+ *   = {kept, #(conf < thr)} (the count check_if_stop :595-606 needs).
+ * lg_prune_gather: index_select of desc / cos / sin / ind by keep_idx into buffers of N_out rows per
+ *   image, and prune[b, ind] += 1 (:537-540); prune is (B, N_orig) i64. */
+int lg_token_scores(const float* desc, const float* w_tok, const float* b_tok, const float* w_match,
+                    const float* b_match, const int* len, float* conf, float* match, int B, int N,
+                    cudaStream_t stream);
+int lg_prune_plan(const float* conf, const float* match, const int* len, float thr, float min_match, int* keep_idx,
+                  int* counts, int B, int N, cudaStream_t stream);
+int lg_prune_gather(const float* desc, const float* cos_t, const float* sin_t, const int64_t* ind,
+                    const int* keep_idx, const int* counts, float* desc_o, float* cos_o, float* sin_o, int64_t* ind_o,
+                    int64_t* prune, int B, int N, int N_out, int N_orig, cudaStream_t stream);
+
 #ifdef __cplusplus
 }
 #endif

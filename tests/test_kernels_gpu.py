@@ -225,3 +225,57 @@ def test_assign_varlen(C):
         assert (got[b, M, :c] - ref[a, :c]).abs().max() < 1e-6
         if a < M:
             assert torch.isinf(got[b, a:M, :N]).all()
+
+
+# ----------------------------------------------------------------------------- (5) confidence / pruning
+@pytest.mark.parametrize("B,N,use_conf", [(1, 1024, True), (3, 777, True), (2, 4096, False), (1, 5, True)])
+def test_prune_plan_bit_exact_on_reference_scores(C, B, N, use_conf):
+    """Keep mask + order-preserving compaction + stop count, fed the oracle's own score tensors."""
+    g = _gen(N + B)
+    conf = torch.rand(B, N, generator=g) if use_conf else None
+    match = torch.rand(B, N, generator=g)
+    # plant exact-threshold values: `<=` / `<` / `>` boundaries must behave like torch
+    thr = O.confidence_threshold(2, 9)
+    wc = 0.95
+    match[:, ::7] = float(np.float32(1 - wc))
+    if use_conf:
+        conf[:, ::5] = float(np.float32(thr))
+    keep_idx, counts = C.prune_plan(None if conf is None else conf.cuda(), match.cuda(), thr, float(np.float32(1 - wc)))
+    for b in range(B):
+        mask = O.pruning_mask(None if conf is None else conf[b:b + 1], match[b:b + 1], thr, wc)
+        want = torch.where(mask)[1]
+        k = int(counts[b, 0])
+        assert k == want.numel()
+        assert torch.equal(keep_idx[b, :k].cpu().long(), want)
+        if use_conf:
+            assert int(counts[b, 1]) == int((conf[b] < thr).sum())
+
+
+def test_token_scores_and_gather(C):
+    g = _gen(3)
+    B, N = 2, 1500
+    sd = W.make_state_dict({}, seed=0, adaptive_fixture=True)
+    desc = torch.randn(B, N, 256, generator=g)
+    conf_r, _ = O.token_confidence(sd, 3, desc, desc)
+    match_r = O.matchability(sd, 3, desc)
+    conf, match = C.token_scores(desc.cuda(), sd["token_confidence.3.token.0.weight"].cuda().reshape(-1),
+                                 sd["token_confidence.3.token.0.bias"].cuda(),
+                                 sd["log_assignment.3.matchability.weight"].cuda().reshape(-1),
+                                 sd["log_assignment.3.matchability.bias"].cuda())
+    assert (conf.cpu() - conf_r).abs().max() < 2e-6 and (match.cpu() - match_r).abs().max() < 2e-6
+    # gather
+    cos, sin = torch.randn(B, N, 32, generator=g), torch.randn(B, N, 32, generator=g)
+    ind = torch.stack([torch.randperm(2 * N, generator=g)[:N].sort().values for _ in range(B)])
+    prune = torch.ones(B, 2 * N, dtype=torch.int64)
+    keep_idx, counts = C.prune_plan(conf, match, 0.85, 0.05)
+    d_o, c_o, s_o, i_o = C.prune_gather(desc.cuda(), cos.cuda(), sin.cuda(), ind.cuda(), keep_idx, counts, pr := prune.cuda())
+    for b in range(B):
+        k = int(counts[b, 0])
+        sel = keep_idx[b, :k].cpu().long()
+        assert torch.equal(d_o[b, :k].cpu(), desc[b].index_select(0, sel))
+        assert torch.equal(c_o[b, :k].cpu(), cos[b].index_select(0, sel))
+        assert torch.equal(s_o[b, :k].cpu(), sin[b].index_select(0, sel))
+        assert torch.equal(i_o[b, :k].cpu(), ind[b].index_select(0, sel))
+        want = prune[b].clone()
+        want[ind[b].index_select(0, sel)] += 1
+        assert torch.equal(pr[b].cpu(), want)
