@@ -32,6 +32,16 @@ SIGNATURES = {
     "lg_prune_plan": (_I, [_P, _P, _P, _F, _F, _P, _P, _I, _I, _P]),
     "lg_prune_gather": (_I, [_P, _P, _P, _P, _P, _P, _P, _P, _P, _P, _P, _I, _I, _I, _I, _P]),
     "lg_filter_ws_bytes": (_c.c_size_t, [_I, _I, _I]),
+    "lg_pack_weight": (_I, [_P, _P, _I, _I, _I, _P]),
+    "lg_rows_to_tiles": (_I, [_P, _P, _I, _I, _I, _I, _P]),
+    "lg_tiles_to_rows": (_I, [_P, _P, _I, _I, _I, _I, _P]),
+    "lg_rotary_tiles": (_I, [_P, _P, _P, _I, _I, _I, _P]),
+    "lg_ln_gelu_tiles": (_I, [_P, _P, _P, _F, _P, _I, _P]),
+    "lg_linear_split": (_I, [_P, _I, _P, _I, _P, _P, _P, _P, _I, _I, _P]),
+    "lg_linear_f32": (_I, [_P, _I, _P, _I, _P, _P, _P, _L, _I, _I, _P]),
+    "lg_linear_qkv_self": (_I, [_P, _P, _P, _P, _P, _P, _P, _P, _P, _P, _I, _I, _I, _I, _P]),
+    "lg_linear_qkv_cross": (_I, [_P, _P, _P, _P, _P, _P, _P, _I, _I, _I, _I, _P]),
+    "lg_attention_tiles": (_I, [_P, _P, _P, _P, _I, _P, _P, _I, _I, _I, _I, _I, _I, _F, _P]),
     "lg_filter_matches": (_I, [_P, _L, _P, _P, _F, _P, _P, _P, _P, _P, _I, _I, _I, _P]),
 }
 
@@ -232,3 +242,115 @@ def prune_gather(desc, cos, sin, ind, keep_idx, counts, prune):
                                  _ptr(prune), B, N, N, prune.shape[1], _stream()), "lg_prune_gather")
     _count(1)
     return desc_o, cos_o, sin_o, ind_o
+
+
+# ----------------------------------------------------------------------------- split tiles + linears
+SPLIT_ATOM = 32768
+
+
+def alloc_split(row_tiles: int, k: int, device):
+    """Split-tile activation buffer [row_tiles][k/64][hi 16 KB | lo 16 KB]."""
+    return torch.empty(row_tiles, k // 64, SPLIT_ATOM, device=device, dtype=torch.uint8)
+
+
+def pack_weight(w, nt: int = 256):
+    """nn.Linear weight (n_out, k) f32 -> packed split-bf16 tiles (one-off, at weight-load time)."""
+    n_out, k = w.shape
+    out = torch.empty(n_out * k * 4, device=w.device, dtype=torch.uint8)
+    _check(lib().lg_pack_weight(_ptr(_f32c(w, "w")), _ptr(out), n_out, k, nt, _stream()), "lg_pack_weight")
+    _count(1)
+    return out
+
+
+def rows_to_tiles(x, tp: int, out=None):
+    """x (B,N,K) f32 -> split tiles (B*tp, K/64, 32 KB)."""
+    B, N, K = x.shape
+    if out is None:
+        out = alloc_split(B * tp, K, x.device)
+    _check(lib().lg_rows_to_tiles(_ptr(_f32c(x, "x")), _ptr(out), B, N, K, tp, _stream()), "lg_rows_to_tiles")
+    _count(1)
+    return out
+
+
+def tiles_to_rows(tiles, B: int, N: int, K: int, tp: int):
+    x = torch.empty(B, N, K, device=tiles.device, dtype=torch.float32)
+    _check(lib().lg_tiles_to_rows(_ptr(tiles), _ptr(x), B, N, K, tp, _stream()), "lg_tiles_to_rows")
+    _count(1)
+    return x
+
+
+def rotary_tiles(cos, sin, tp: int, out=None):
+    B, N, _ = cos.shape
+    if out is None:
+        out = torch.empty(B * tp, SPLIT_ATOM, device=cos.device, dtype=torch.uint8)
+    _check(lib().lg_rotary_tiles(_ptr(_f32c(cos, "cos")), _ptr(_f32c(sin, "sin")), _ptr(out), B, N, tp, _stream()),
+           "lg_rotary_tiles")
+    _count(1)
+    return out
+
+
+def ln_gelu_tiles(h, gamma, beta, eps: float, out=None):
+    rows = h.shape[0]
+    assert h.shape[1] == 512
+    if out is None:
+        out = alloc_split(rows // TILE, 512, h.device)
+    _check(lib().lg_ln_gelu_tiles(_ptr(_f32c(h, "h")), _ptr(_f32c(gamma, "gamma")), _ptr(_f32c(beta, "beta")), float(eps),
+                                  _ptr(out), rows, _stream()), "lg_ln_gelu_tiles")
+    _count(1)
+    return out
+
+
+def linear_split(a0, w, bias, n_out: int, a1=None, resid=None, out=None):
+    """[a0 | a1] . w^T + bias (+ resid) -> split tiles (row_tiles, n_out/64, 32 KB)."""
+    rt = a0.shape[0]
+    if out is None:
+        out = alloc_split(rt, n_out, a0.device)
+    _check(lib().lg_linear_split(_ptr(a0), a0.shape[1], _ptr(a1), 0 if a1 is None else a1.shape[1], _ptr(w),
+                                 _ptr(_f32c(bias, "bias")), _ptr(resid), _ptr(out), rt, n_out, _stream()),
+           "lg_linear_split")
+    _count(1)
+    return out
+
+
+def linear_f32(a0, w, bias, n_out: int, a1=None, out=None):
+    """[a0 | a1] . w^T + bias -> f32 rows (row_tiles*128, n_out)."""
+    rt = a0.shape[0]
+    if out is None:
+        out = torch.empty(rt * TILE, n_out, device=a0.device, dtype=torch.float32)
+    _check(lib().lg_linear_f32(_ptr(a0), a0.shape[1], _ptr(a1), 0 if a1 is None else a1.shape[1], _ptr(w),
+                               _ptr(_f32c(bias, "bias")), _ptr(out), out.stride(0), rt, n_out, _stream()),
+           "lg_linear_f32")
+    _count(1)
+    return out
+
+
+def linear_qkv_self(a, w, bias, rot, B: int, tp0: int, tp1: int, bufs, H: int = 4):
+    """bufs = ((q0,k0,v0), (q1,k1,v1) or None): attention operand tiles per side."""
+    s0, s1 = bufs[0], (bufs[1] if tp1 else (None, None, None))
+    _check(lib().lg_linear_qkv_self(_ptr(a), _ptr(w), _ptr(_f32c(bias, "bias")), _ptr(rot), _ptr(s0[0]), _ptr(s0[1]),
+                                    _ptr(s0[2]), _ptr(s1[0]), _ptr(s1[1]), _ptr(s1[2]), B, H, tp0, tp1, _stream()),
+           "lg_linear_qkv_self")
+    _count(1)
+
+
+def linear_qkv_cross(a, w, bias, B: int, tp0: int, tp1: int, bufs, H: int = 4):
+    """bufs = ((qk0,v0), (qk1,v1) or None)."""
+    s0, s1 = bufs[0], (bufs[1] if tp1 else (None, None))
+    _check(lib().lg_linear_qkv_cross(_ptr(a), _ptr(w), _ptr(_f32c(bias, "bias")), _ptr(s0[0]), _ptr(s0[1]), _ptr(s1[0]),
+                                     _ptr(s1[1]), B, H, tp0, tp1, _stream()), "lg_linear_qkv_cross")
+    _count(1)
+
+
+def attention_tiles(q_tiles, k_tiles, v_tiles, out_tiles, rt_base: int, nq, nk, q_len=None, k_len=None, scale=0.125):
+    """Context written as split tiles (K atom = head) into out_tiles starting at row tile rt_base."""
+    B, H = q_tiles.shape[:2]
+    if ATTN_EVENTS is not None:
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+    _check(lib().lg_attention_tiles(_ptr(q_tiles), _ptr(k_tiles), _ptr(v_tiles), _ptr(out_tiles), rt_base,
+                                    _ptr(_i32(q_len)), _ptr(_i32(k_len)), B, H, nq, nk, q_tiles.shape[2],
+                                    k_tiles.shape[2], float(scale), _stream()), "lg_attention_tiles")
+    if ATTN_EVENTS is not None:
+        e1.record()
+        ATTN_EVENTS.append((e0, e1, 4.0 * 64 * nq * nk * B * H))
+    _count(1)

@@ -32,7 +32,9 @@ struct AttnParams {
   const uint8_t* q_tiles;
   const uint8_t* k_tiles;
   const uint8_t* v_tiles;
-  float* out;          // (B, nq, H*64) fp32
+  float* out;          // (B, nq, H*64) fp32, or null when out_tiles is set
+  uint8_t* out_tiles;  // split tiles [rt][H atoms][hi 16 KB | lo 16 KB]: context as the A operand of lg_linear
+  int out_rt_base;     // row tile of (b=0, query tile 0) inside out_tiles; image b starts at + b*tq_pad
   const int* q_len;    // per-image valid query rows, or null
   const int* k_len;    // per-image valid keys, or null
   int B, H, nq, nk, tq_pad, tk_pad;
@@ -69,6 +71,14 @@ __global__ void __launch_bounds__(kAttnThreads, 1) attention_kernel(const AttnPa
 
   if (qt0 * kTile >= q_len || nkt == 0) {
     // nothing to attend from / to: rows are zero (reference: nan_to_num of an all-masked softmax)
+    if (p.out_tiles) {
+      for (int i = threadIdx.x; i < 2 * 32768 / 16; i += kAttnThreads) {
+        const int t = i / 2048, o = i % 2048;
+        uint8_t* dst = p.out_tiles + ((static_cast<size_t>(p.out_rt_base + b * p.tq_pad + qt0 + t) * p.H + h) * 32768);
+        reinterpret_cast<uint4*>(dst)[o] = make_uint4(0u, 0u, 0u, 0u);
+      }
+      return;
+    }
     const int r0 = qt0 * kTile, r1 = min(p.nq, r0 + 2 * kTile);
     for (int i = threadIdx.x; i < (r1 - r0) * (kHeadDim / 4); i += kAttnThreads) {
       const int r = r0 + i / (kHeadDim / 4), c4 = i % (kHeadDim / 4);
@@ -233,6 +243,29 @@ __global__ void __launch_bounds__(kAttnThreads, 1) attention_kernel(const AttnPa
     tc_fence_after();
     const int row = (qt0 + t) * kTile + r;
     const float inv = (row < q_len) ? 1.f / l : 0.f;  // padded query rows -> 0
+    if (p.out_tiles) {
+      // context rows as split bf16 tiles: head h is K atom h of the (rows x 256) matrix
+      uint8_t* dt = p.out_tiles + ((static_cast<size_t>(p.out_rt_base + b * p.tq_pad + qt0 + t) * p.H + h) * 32768);
+#pragma unroll
+      for (int cb = 0; cb < 2; ++cb) {
+        tmem_ld32(tO + cb * 32, v);
+        tmem_wait_ld();
+#pragma unroll
+        for (int q = 0; q < 4; ++q) {
+          uint32_t hh[4], ll[4];
+#pragma unroll
+          for (int i = 0; i < 4; ++i) {
+            const float x0 = __uint_as_float(v[8 * q + 2 * i]) * inv, x1 = __uint_as_float(v[8 * q + 2 * i + 1]) * inv;
+            const __nv_bfloat16 h0 = __float2bfloat16_rn(x0), h1 = __float2bfloat16_rn(x1);
+            hh[i] = static_cast<uint32_t>(__bfloat16_as_ushort(h0)) | (static_cast<uint32_t>(__bfloat16_as_ushort(h1)) << 16);
+            ll[i] = pack_bf16x2(x0 - __bfloat162float(h0), x1 - __bfloat162float(h1));
+          }
+          uint8_t* at = dt + sw128_offset(r, cb * 4 + q);
+          *reinterpret_cast<uint4*>(at) = make_uint4(hh[0], hh[1], hh[2], hh[3]);
+          *reinterpret_cast<uint4*>(at + 16384) = make_uint4(ll[0], ll[1], ll[2], ll[3]);
+        }
+      }
+    } else {
     float4* dst = reinterpret_cast<float4*>(p.out + (static_cast<size_t>(b) * p.nq + row) * row_stride + h * kHeadDim);
 #pragma unroll
     for (int cb = 0; cb < 2; ++cb) {
@@ -245,6 +278,7 @@ __global__ void __launch_bounds__(kAttnThreads, 1) attention_kernel(const AttnPa
                                         __uint_as_float(v[4 * i + 2]) * inv, __uint_as_float(v[4 * i + 3]) * inv);
       }
     }
+    }
   }
   tc_fence_before();
   __syncthreads();
@@ -253,11 +287,11 @@ __global__ void __launch_bounds__(kAttnThreads, 1) attention_kernel(const AttnPa
 
 }  // namespace lg
 
-extern "C" int lg_attention(const void* q_tiles, const void* k_tiles, const void* v_tiles, float* out,
-                            const int* q_len, const int* k_len, int B, int H, int nq, int nk, int tq_pad, int tk_pad,
-                            float softmax_scale, cudaStream_t stream) {
-  if (!q_tiles || !k_tiles || !v_tiles || !out) return LG_ERR_NULL;
-  if (B <= 0 || H <= 0 || nq <= 0 || nk <= 0) return LG_ERR_SHAPE;
+static int launch_attention(const void* q_tiles, const void* k_tiles, const void* v_tiles, float* out, void* out_tiles,
+                            int out_rt_base, const int* q_len, const int* k_len, int B, int H, int nq, int nk,
+                            int tq_pad, int tk_pad, float softmax_scale, cudaStream_t stream) {
+  if (!q_tiles || !k_tiles || !v_tiles || (!out && !out_tiles)) return LG_ERR_NULL;
+  if (B <= 0 || H <= 0 || nq <= 0 || nk <= 0 || out_rt_base < 0) return LG_ERR_SHAPE;
   if (tq_pad * lg::kTile < nq || tk_pad * lg::kTile < nk || (tq_pad & 1) || (tk_pad & 1)) return LG_ERR_SHAPE;
   static bool attr_done = false;  // idempotent attribute; a benign race at worst sets it twice
   if (!attr_done) {
@@ -267,8 +301,24 @@ extern "C" int lg_attention(const void* q_tiles, const void* k_tiles, const void
     attr_done = true;
   }
   lg::AttnParams p{static_cast<const uint8_t*>(q_tiles), static_cast<const uint8_t*>(k_tiles),
-                   static_cast<const uint8_t*>(v_tiles), out, q_len, k_len, B, H, nq, nk, tq_pad, tk_pad,
-                   softmax_scale * 1.4426950408889634f};
+                   static_cast<const uint8_t*>(v_tiles), out, static_cast<uint8_t*>(out_tiles), out_rt_base, q_len,
+                   k_len, B, H, nq, nk, tq_pad, tk_pad, softmax_scale * 1.4426950408889634f};
   lg::attention_kernel<<<dim3(tq_pad / 2, H, B), lg::kAttnThreads, lg::kAttnSmem, stream>>>(p);
   return static_cast<int>(cudaGetLastError());
+}
+
+extern "C" int lg_attention(const void* q_tiles, const void* k_tiles, const void* v_tiles, float* out,
+                            const int* q_len, const int* k_len, int B, int H, int nq, int nk, int tq_pad, int tk_pad,
+                            float softmax_scale, cudaStream_t stream) {
+  if (!out) return LG_ERR_NULL;
+  return launch_attention(q_tiles, k_tiles, v_tiles, out, nullptr, 0, q_len, k_len, B, H, nq, nk, tq_pad, tk_pad,
+                          softmax_scale, stream);
+}
+
+extern "C" int lg_attention_tiles(const void* q_tiles, const void* k_tiles, const void* v_tiles, void* out_tiles,
+                                  int out_rt_base, const int* q_len, const int* k_len, int B, int H, int nq, int nk,
+                                  int tq_pad, int tk_pad, float softmax_scale, cudaStream_t stream) {
+  if (!out_tiles) return LG_ERR_NULL;
+  return launch_attention(q_tiles, k_tiles, v_tiles, nullptr, out_tiles, out_rt_base, q_len, k_len, B, H, nq, nk,
+                          tq_pad, tk_pad, softmax_scale, stream);
 }

@@ -1,0 +1,612 @@
+// lg_linear : the per-token linears of SelfBlock / CrossBlock / MatchAssignment on tcgen05.
+//
+// Replaces the nn.Linear calls of the reference (gluefactory/models/matchers/lightglue.py):
+//   SelfBlock   Wqkv :184 (+ unflatten/rotary :185-188), out_proj :190, ffn.0 / ffn.3 :171-176,191
+//   CrossBlock  to_qk / to_v :223-228, to_out :246, ffn.0 / ffn.3 :205-210,247-248
+//   MatchAssignment.final_proj :310, LightGlue.input_proj :370-373,478-479
+//
+// Precision: bf16 tensor-core operands alone cost 1e-1 on log_assignment when used in the FFN
+// (scripts/exp_linear_precision.py), so every linear runs as a 3-term split-bf16 product
+//   x = xh + xl, w = wh + wl (bf16 each):  y = xh.wh + xl.wh + xh.wl     (fp32 accumulate in TMEM)
+// which carries ~16 mantissa bits (2e-4 end to end) at 3 bf16 MMAs per product.
+//
+// Data layout ("split tiles"): an activation matrix [rows][K] lives in HBM as
+//   [row tile of 128][K atom of 64][hi 16 KB | lo 16 KB]
+// where each 16 KB block is the exact byte image of a SWIZZLE_128B K-major shared-memory tile,
+// so one flat bulk (TMA engine) copy stages a 32 KB hi|lo atom.  Weights [Nout][K] are packed once
+// as [N tile][K atom][hi | lo][Nt x 128 B] in the same pattern (lg_pack_weight).
+//
+// One persistent CTA per SM, 192 threads:
+//   warp 4 (one lane)  producer: bulk copies A atom (32 KB) + W atom into a 2-stage ring
+//   warp 5 (one lane)  tcgen05.mma issue, 128 x Nt x 16 per instruction, 12 per stage;
+//                      two TMEM accumulators (2 x 256 columns) so tile i+1 accumulates while
+//   warps 0-3          the epilogue of tile i runs (thread == row == TMEM lane)
+// Epilogues (template): split tiles (+bias, +residual), fp32 rows, and the attention operand
+// producers (self: de-interleaved Wqkv + rotary; cross: to_qk | to_v) that write the bf16
+// Q / K / V^T tiles lg_attention consumes, through shared-memory staging + bulk stores.
+#include "lg_common.cuh"
+#include "lg_b200.h"
+
+namespace lg {
+
+constexpr int kLinThreads = 192;
+constexpr int kLinStages = 2;
+constexpr int kSplitAtom = 32768;   // hi | lo
+constexpr int kHalfAtom = 16384;
+constexpr int kStageOut = 32768;    // epilogue staging (one split atom, or two bf16 tiles)
+
+enum LinearEpilogue { kEpiSplit = 0, kEpiF32 = 1, kEpiQkvSelf = 2, kEpiQkvCross = 3 };
+
+struct LinearParams {
+  const uint8_t* a0;       // A source 0: [row_tiles][a0_atoms][32 KB]
+  const uint8_t* a1;       // A source 1 (concatenated along K after a0), may be null
+  int a0_atoms, a1_atoms;
+  const uint8_t* w;        // [n_tiles][k_atoms][hi | lo][Nt*128]
+  const float* bias;       // [n_tiles * Nt] (same row order as w)
+  int row_tiles, n_tiles;
+  // kEpiSplit
+  uint8_t* out_tiles;            // [row_tiles][n_tiles*Nt/64][32 KB]
+  const uint8_t* resid_tiles;    // same shape, or null
+  // kEpiF32
+  float* out_f32;
+  int64_t ld;                    // row pitch in floats
+  // kEpiQkv*: attention operand tiles per side (image 0 rows first, then image 1)
+  uint8_t* q_tiles[2];
+  uint8_t* k_tiles[2];
+  uint8_t* v_tiles[2];
+  const uint8_t* rot_tiles;      // [row_tiles][cos 16 KB | sin 16 KB], fp32, chunk-swizzled rows
+  int B, H, tp0, tp1;            // row tile rt -> side 0: (b, t) = divmod(rt, tp0); side 1 after B*tp0
+};
+
+struct __align__(8) LinearBarriers {
+  uint64_t full[kLinStages];
+  uint64_t empty[kLinStages];
+  uint64_t acc_full[2];
+  uint64_t acc_empty[2];
+  uint64_t aux_full;     // residual atom / rotary table landed
+  uint32_t tmem_base;
+};
+
+template <int kNt, int kEpi>
+constexpr int linear_smem_bytes() {
+  return 1024 + kLinStages * (kSplitAtom + kNt * 256) + kStageOut + (kEpi == kEpiQkvSelf ? 32768 : 0) +
+         static_cast<int>(sizeof(LinearBarriers));
+}
+
+template <int N>
+__device__ __forceinline__ void bulk_wait_read() {
+  asm volatile("cp.async.bulk.wait_group.read %0;" ::"n"(N) : "memory");
+}
+__device__ __forceinline__ void epi_bar_sync() { asm volatile("bar.sync 1, 128;" ::: "memory"); }
+
+// 8 fp32 -> (hi, lo) bf16x8 chunks
+__device__ __forceinline__ void split8(const float* x, uint4& hi, uint4& lo) {
+  uint32_t h[4], l[4];
+#pragma unroll
+  for (int i = 0; i < 4; ++i) {
+    const __nv_bfloat16 h0 = __float2bfloat16_rn(x[2 * i]), h1 = __float2bfloat16_rn(x[2 * i + 1]);
+    const float r0 = x[2 * i] - __bfloat162float(h0), r1 = x[2 * i + 1] - __bfloat162float(h1);
+    h[i] = static_cast<uint32_t>(__bfloat16_as_ushort(h0)) | (static_cast<uint32_t>(__bfloat16_as_ushort(h1)) << 16);
+    l[i] = pack_bf16x2(r0, r1);
+  }
+  hi = make_uint4(h[0], h[1], h[2], h[3]);
+  lo = make_uint4(l[0], l[1], l[2], l[3]);
+}
+__device__ __forceinline__ float bf16lo(uint32_t u) { return __uint_as_float(u << 16); }
+__device__ __forceinline__ float bf16hi(uint32_t u) { return __uint_as_float(u & 0xFFFF0000u); }
+
+// attention tile address of (row tile rt, head h) inside the per-side [B][H][tp][16 KB] buffers
+__device__ __forceinline__ size_t attn_tile_offset(const LinearParams& p, int rt, int h, int& side) {
+  int b, t, tp;
+  if (rt < p.B * p.tp0) { side = 0; tp = p.tp0; b = rt / tp; t = rt - b * tp; }
+  else { side = 1; tp = p.tp1; const int r2 = rt - p.B * p.tp0; b = r2 / tp; t = r2 - b * tp; }
+  return ((static_cast<size_t>(b) * p.H + h) * tp + t) * static_cast<size_t>(kHalfAtom);
+}
+
+template <int kNt, int kEpi>
+__global__ void __launch_bounds__(kLinThreads, 1) linear_kernel(const LinearParams p) {
+  constexpr int kWAtom = kNt * 256;                       // hi | lo of one K atom of the weight tile
+  constexpr int kStage = kSplitAtom + kWAtom;
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* base = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+  uint8_t* ring = base;
+  uint8_t* stg = ring + kLinStages * kStage;              // 32 KB epilogue staging
+  uint8_t* rot = stg + kStageOut;                         // 32 KB rotary table (kEpiQkvSelf only)
+  LinearBarriers* bar =
+      reinterpret_cast<LinearBarriers*>(stg + kStageOut + (kEpi == kEpiQkvSelf ? 32768 : 0));
+
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int k_atoms = p.a0_atoms + p.a1_atoms;
+  const int items = p.row_tiles * p.n_tiles;
+
+  if (threadIdx.x == 0) {
+    for (int s = 0; s < kLinStages; ++s) { mbar_init(&bar->full[s], 1); mbar_init(&bar->empty[s], 1); }
+    for (int i = 0; i < 2; ++i) { mbar_init(&bar->acc_full[i], 1); mbar_init(&bar->acc_empty[i], 128); }
+    mbar_init(&bar->aux_full, 1);
+    fence_mbar_init();
+  }
+  if (warp == 5) tmem_alloc<512>(&bar->tmem_base);
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem = bar->tmem_base;
+
+  if (warp == 4) {
+    // ------------------------------------------------------------------ producer
+    if (lane == 0) {
+      uint32_t it = 0;
+      for (int item = blockIdx.x; item < items; item += gridDim.x) {
+        const int rt = item / p.n_tiles, nt = item - rt * p.n_tiles;
+        const uint8_t* gw = p.w + static_cast<size_t>(nt) * k_atoms * kWAtom;
+        for (int ka = 0; ka < k_atoms; ++ka, ++it) {
+          const int s = it % kLinStages;
+          if (it >= kLinStages) mbar_wait(&bar->empty[s], ((it / kLinStages) - 1) & 1);
+          const uint8_t* ga = ka < p.a0_atoms
+                                  ? p.a0 + (static_cast<size_t>(rt) * p.a0_atoms + ka) * kSplitAtom
+                                  : p.a1 + (static_cast<size_t>(rt) * p.a1_atoms + (ka - p.a0_atoms)) * kSplitAtom;
+          mbar_arrive_expect_tx(&bar->full[s], kStage);
+          bulk_g2s(ring + s * kStage, ga, kSplitAtom, &bar->full[s]);
+          bulk_g2s(ring + s * kStage + kSplitAtom, gw + static_cast<size_t>(ka) * kWAtom, kWAtom, &bar->full[s]);
+        }
+      }
+    }
+  } else if (warp == 5) {
+    // ------------------------------------------------------------------ MMA issuer
+    if (lane == 0) {
+      constexpr uint32_t idesc = umma_idesc(kFmtBF16, 128, kNt);
+      const uint32_t ring_a = smem_u32(ring);
+      uint32_t it = 0;
+      int local = 0;
+      for (int item = blockIdx.x; item < items; item += gridDim.x, ++local) {
+        const int buf = local & 1;
+        if (local >= 2) { mbar_wait(&bar->acc_empty[buf], ((local >> 1) - 1) & 1); tc_fence_after(); }
+        const uint32_t acc = tmem + buf * 256;
+        for (int ka = 0; ka < k_atoms; ++ka, ++it) {
+          const int s = it % kLinStages;
+          mbar_wait(&bar->full[s], (it / kLinStages) & 1);
+          tc_fence_after();
+          const uint32_t a_hi = ring_a + s * kStage, a_lo = a_hi + kHalfAtom;
+          const uint32_t w_hi = a_hi + kSplitAtom, w_lo = w_hi + kNt * 128;
+          const uint64_t dah = umma_desc_kmajor_sw128(a_hi), dal = umma_desc_kmajor_sw128(a_lo);
+          const uint64_t dwh = umma_desc_kmajor_sw128(w_hi), dwl = umma_desc_kmajor_sw128(w_lo);
+#pragma unroll
+          for (int kk = 0; kk < 4; ++kk) {  // 64 bf16 per atom = 4 x K16, 32 B per step
+            umma_bf16_ss(acc, dal + 2 * kk, dwh + 2 * kk, idesc, (ka > 0 || kk > 0));
+            umma_bf16_ss(acc, dah + 2 * kk, dwl + 2 * kk, idesc, 1);
+            umma_bf16_ss(acc, dah + 2 * kk, dwh + 2 * kk, idesc, 1);
+          }
+          umma_commit(&bar->empty[s]);
+        }
+        umma_commit(&bar->acc_full[buf]);
+      }
+    }
+  } else {
+    // ------------------------------------------------------------------ epilogue: thread == row
+    const int r = warp * 32 + lane;
+    const bool leader = threadIdx.x == 0;
+    uint32_t aux_phase = 0, sbi = 0;  // sbi: running half-buffer index of the bf16 tile staging
+    uint32_t v[32];
+    float f[32];
+    int local = 0;
+    for (int item = blockIdx.x; item < items; item += gridDim.x, ++local) {
+      const int rt = item / p.n_tiles, nt = item - rt * p.n_tiles;
+      const int buf = local & 1;
+      const uint32_t tacc = tmem + (static_cast<uint32_t>(warp * 32) << 16) + buf * 256;
+      const float* bias = p.bias + nt * kNt;
+
+      if (kEpi == kEpiQkvSelf) {
+        // rotary table of this row tile (all reads of the previous table ended before the
+        // previous item's last epi_bar_sync)
+        if (leader) {
+          mbar_arrive_expect_tx(&bar->aux_full, 32768);
+          bulk_g2s(rot, p.rot_tiles + static_cast<size_t>(rt) * 32768, 32768, &bar->aux_full);
+        }
+      }
+      mbar_wait(&bar->acc_full[buf], (local >> 1) & 1);
+      tc_fence_after();
+
+      if (kEpi == kEpiF32) {
+        float* dst = p.out_f32 + (static_cast<int64_t>(rt) * kTile + r) * p.ld + nt * kNt;
+#pragma unroll 1
+        for (int cb = 0; cb < kNt / 32; ++cb) {
+          tmem_ld32(tacc + cb * 32, v);
+          tmem_wait_ld();
+#pragma unroll
+          for (int i = 0; i < 8; ++i) {
+            float4 o;
+            o.x = __uint_as_float(v[4 * i]) + __ldg(bias + cb * 32 + 4 * i);
+            o.y = __uint_as_float(v[4 * i + 1]) + __ldg(bias + cb * 32 + 4 * i + 1);
+            o.z = __uint_as_float(v[4 * i + 2]) + __ldg(bias + cb * 32 + 4 * i + 2);
+            o.w = __uint_as_float(v[4 * i + 3]) + __ldg(bias + cb * 32 + 4 * i + 3);
+            reinterpret_cast<float4*>(dst + cb * 32)[i] = o;
+          }
+        }
+        tc_fence_before();
+        mbar_arrive(&bar->acc_empty[buf]);
+      } else if (kEpi == kEpiSplit) {
+        const int out_atoms = p.n_tiles * (kNt / 64);
+#pragma unroll 1
+        for (int j = 0; j < kNt / 64; ++j) {
+          const size_t goff = (static_cast<size_t>(rt) * out_atoms + nt * (kNt / 64) + j) * kSplitAtom;
+          if (leader) {
+            bulk_wait_read<0>();  // the previous atom's store has drained the staging buffer
+            if (p.resid_tiles) {
+              mbar_arrive_expect_tx(&bar->aux_full, kSplitAtom);
+              bulk_g2s(stg, p.resid_tiles + goff, kSplitAtom, &bar->aux_full);
+            }
+          }
+          if (p.resid_tiles) { mbar_wait(&bar->aux_full, aux_phase); aux_phase ^= 1; }
+          else epi_bar_sync();
+#pragma unroll
+          for (int cbh = 0; cbh < 2; ++cbh) {
+            tmem_ld32(tacc + j * 64 + cbh * 32, v);
+            tmem_wait_ld();
+            if (j == kNt / 64 - 1 && cbh == 1) { tc_fence_before(); mbar_arrive(&bar->acc_empty[buf]); }
+#pragma unroll
+            for (int q = 0; q < 4; ++q) {
+              uint8_t* at = stg + sw128_offset(r, cbh * 4 + q);
+              float x[8];
+#pragma unroll
+              for (int i = 0; i < 8; ++i)
+                x[i] = __uint_as_float(v[8 * q + i]) + __ldg(bias + j * 64 + cbh * 32 + 8 * q + i);
+              if (p.resid_tiles) {
+                const uint4 rh = *reinterpret_cast<const uint4*>(at), rl = *reinterpret_cast<const uint4*>(at + kHalfAtom);
+                const uint32_t hh[4] = {rh.x, rh.y, rh.z, rh.w}, ll[4] = {rl.x, rl.y, rl.z, rl.w};
+#pragma unroll
+                for (int i = 0; i < 4; ++i) {
+                  x[2 * i] = (bf16lo(hh[i]) + bf16lo(ll[i])) + x[2 * i];
+                  x[2 * i + 1] = (bf16hi(hh[i]) + bf16hi(ll[i])) + x[2 * i + 1];
+                }
+              }
+              uint4 hi, lo;
+              split8(x, hi, lo);
+              *reinterpret_cast<uint4*>(at) = hi;
+              *reinterpret_cast<uint4*>(at + kHalfAtom) = lo;
+            }
+          }
+          fence_proxy_async_smem();
+          epi_bar_sync();
+          if (leader) { bulk_s2g(p.out_tiles + goff, stg, kSplitAtom); bulk_commit(); }
+        }
+      } else {
+        // ---------------------------------------------------------------- attention operand tiles
+        // kEpiQkvSelf : n tile == head; columns [q 64 | k 64 | v 64]; rotary on q, k
+        // kEpiQkvCross: n tile 0 = qk of the 4 heads, n tile 1 = v of the 4 heads
+        if (kEpi == kEpiQkvSelf) { mbar_wait(&bar->aux_full, aux_phase); aux_phase ^= 1; }
+        constexpr int kParts = kEpi == kEpiQkvSelf ? 3 : 4;
+#pragma unroll 1
+        for (int part = 0; part < kParts; ++part) {
+          const int h = kEpi == kEpiQkvSelf ? nt : part;
+          const int kind = kEpi == kEpiQkvSelf ? part : (nt == 0 ? 0 : 2);  // 0 q, 1 k, 2 v
+          uint8_t* sb = stg + (sbi++ & 1) * kHalfAtom;
+          if (leader) bulk_wait_read<1>();  // the store issued two parts ago has drained this half
+          epi_bar_sync();
+#pragma unroll
+          for (int cbh = 0; cbh < 2; ++cbh) {
+            tmem_ld32(tacc + part * 64 + cbh * 32, v);
+            tmem_wait_ld();
+            if (part == kParts - 1 && cbh == 1) { tc_fence_before(); mbar_arrive(&bar->acc_empty[buf]); }
+#pragma unroll
+            for (int i = 0; i < 32; ++i) f[i] = __uint_as_float(v[i]) + __ldg(bias + part * 64 + cbh * 32 + i);
+            if (kEpi == kEpiQkvSelf && kind < 2) {
+#pragma unroll
+              for (int q = 0; q < 4; ++q) {  // 4 frequencies per 16-byte table chunk
+                const uint32_t off = r * 128 + (((cbh * 4 + q) ^ (r & 7)) << 4);
+                const float4 c4 = *reinterpret_cast<const float4*>(rot + off);
+                const float4 s4 = *reinterpret_cast<const float4*>(rot + kHalfAtom + off);
+                const float cc[4] = {c4.x, c4.y, c4.z, c4.w}, ss[4] = {s4.x, s4.y, s4.z, s4.w};
+#pragma unroll
+                for (int e = 0; e < 4; ++e) {
+                  // (t*cos) + (rot(t)*sin), reference rounding sequence (lightglue.py:36-43)
+                  const float x0 = f[8 * q + 2 * e], x1 = f[8 * q + 2 * e + 1];
+                  f[8 * q + 2 * e] = __fadd_rn(__fmul_rn(x0, cc[e]), __fmul_rn(-x1, ss[e]));
+                  f[8 * q + 2 * e + 1] = __fadd_rn(__fmul_rn(x1, cc[e]), __fmul_rn(x0, ss[e]));
+                }
+              }
+            }
+            if (kind < 2) {
+#pragma unroll
+              for (int q = 0; q < 4; ++q) {
+                uint4 o;
+                o.x = pack_bf16x2(f[8 * q], f[8 * q + 1]); o.y = pack_bf16x2(f[8 * q + 2], f[8 * q + 3]);
+                o.z = pack_bf16x2(f[8 * q + 4], f[8 * q + 5]); o.w = pack_bf16x2(f[8 * q + 6], f[8 * q + 7]);
+                *reinterpret_cast<uint4*>(sb + sw128_offset(r, cbh * 4 + q)) = o;
+              }
+            } else {
+              // V^T: element (dh d, point r) of 2 atoms x [64 dh][64 points]
+              uint8_t* col = sb + (r >> 6) * 8192 + (r & 7) * 2;
+              const uint32_t pc = (r & 63) >> 3;
+#pragma unroll
+              for (int i = 0; i < 32; ++i) {
+                const int d = cbh * 32 + i;
+                *reinterpret_cast<__nv_bfloat16*>(col + d * 128 + ((pc ^ (d & 7)) << 4)) = __float2bfloat16_rn(f[i]);
+              }
+            }
+          }
+          fence_proxy_async_smem();
+          epi_bar_sync();
+          if (leader) {
+            int side;
+            const size_t off = attn_tile_offset(p, rt, h, side);
+            uint8_t* dst = (kind == 0 ? p.q_tiles[side] : kind == 1 ? p.k_tiles[side] : p.v_tiles[side]) + off;
+            bulk_s2g(dst, sb, kHalfAtom);
+            bulk_commit();
+          }
+        }
+      }
+    }
+    if (leader) bulk_wait_all();
+  }
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 5) tmem_dealloc<512>(tmem);
+}
+
+}  // namespace lg
+
+// ============================================================================ format kernels
+namespace lg {
+
+// W (n_out, k) f32 row-major -> [n_out/nt][k/64][hi | lo][nt x 128 B] swizzled bf16 tiles.
+// one thread per (row, 8-element chunk)
+__global__ void pack_weight_kernel(const float* __restrict__ w, uint8_t* __restrict__ out, int n_out, int k, int nt) {
+  const int idx = blockIdx.x * blockDim.x + threadIdx.x;
+  const int chunks = k / 8;
+  if (idx >= n_out * chunks) return;
+  const int n = idx / chunks, ch = idx - n * chunks;
+  const float4 a = __ldg(reinterpret_cast<const float4*>(w + static_cast<size_t>(n) * k + ch * 8));
+  const float4 b = __ldg(reinterpret_cast<const float4*>(w + static_cast<size_t>(n) * k + ch * 8) + 1);
+  const float x[8] = {a.x, a.y, a.z, a.w, b.x, b.y, b.z, b.w};
+  uint4 hi, lo;
+  split8(x, hi, lo);
+  const int tile = n / nt, r = n - tile * nt, ka = ch >> 3, c = ch & 7;
+  uint8_t* at = out + (static_cast<size_t>(tile) * (k / 64) + ka) * (static_cast<size_t>(nt) * 256) + sw128_offset(r, c);
+  *reinterpret_cast<uint4*>(at) = hi;
+  *reinterpret_cast<uint4*>(at + static_cast<size_t>(nt) * 128) = lo;
+}
+
+// x (B, N, K) f32 -> split tiles [B*tp][K/64][32 KB]; rows >= N of each image are zero.
+// grid (tp, B), block 1024: thread -> (row, chunk) tasks
+__global__ void __launch_bounds__(1024) rows_to_tiles_kernel(const float* __restrict__ x, uint8_t* __restrict__ tiles,
+                                                             int N, int K, int tp) {
+  const int t = blockIdx.x, b = blockIdx.y, chunks = K / 8, atoms = K / 64;
+  uint8_t* dst = tiles + (static_cast<size_t>(b) * tp + t) * atoms * kSplitAtom;
+  for (int task = threadIdx.x; task < kTile * chunks; task += blockDim.x) {
+    const int r = task / chunks, ch = task - r * chunks, n = t * kTile + r;
+    float v[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
+    if (n < N) {
+      const float4* src = reinterpret_cast<const float4*>(x + (static_cast<size_t>(b) * N + n) * K + ch * 8);
+      const float4 a = __ldg(src), c = __ldg(src + 1);
+      v[0] = a.x; v[1] = a.y; v[2] = a.z; v[3] = a.w; v[4] = c.x; v[5] = c.y; v[6] = c.z; v[7] = c.w;
+    }
+    uint4 hi, lo;
+    split8(v, hi, lo);
+    uint8_t* at = dst + (ch >> 3) * kSplitAtom + sw128_offset(r, ch & 7);
+    *reinterpret_cast<uint4*>(at) = hi;
+    *reinterpret_cast<uint4*>(at + kHalfAtom) = lo;
+  }
+}
+
+// inverse: x (B, N, K) f32 = hi + lo
+__global__ void __launch_bounds__(1024) tiles_to_rows_kernel(const uint8_t* __restrict__ tiles, float* __restrict__ x,
+                                                             int N, int K, int tp) {
+  const int t = blockIdx.x, b = blockIdx.y, chunks = K / 8, atoms = K / 64;
+  const uint8_t* src = tiles + (static_cast<size_t>(b) * tp + t) * atoms * kSplitAtom;
+  for (int task = threadIdx.x; task < kTile * chunks; task += blockDim.x) {
+    const int r = task / chunks, ch = task - r * chunks, n = t * kTile + r;
+    if (n >= N) continue;
+    const uint8_t* at = src + (ch >> 3) * kSplitAtom + sw128_offset(r, ch & 7);
+    const uint4 h = *reinterpret_cast<const uint4*>(at), l = *reinterpret_cast<const uint4*>(at + kHalfAtom);
+    float4 o0, o1;
+    o0.x = bf16lo(h.x) + bf16lo(l.x); o0.y = bf16hi(h.x) + bf16hi(l.x);
+    o0.z = bf16lo(h.y) + bf16lo(l.y); o0.w = bf16hi(h.y) + bf16hi(l.y);
+    o1.x = bf16lo(h.z) + bf16lo(l.z); o1.y = bf16hi(h.z) + bf16hi(l.z);
+    o1.z = bf16lo(h.w) + bf16lo(l.w); o1.w = bf16hi(h.w) + bf16hi(l.w);
+    float4* dst = reinterpret_cast<float4*>(x + (static_cast<size_t>(b) * N + n) * K + ch * 8);
+    dst[0] = o0;
+    dst[1] = o1;
+  }
+}
+
+// compact cos / sin tables (B, N, 32) f32 -> [B*tp][cos 16 KB | sin 16 KB], 128-byte rows whose
+// 16-byte chunks are XOR-swizzled with (row & 7) (conflict-free thread-per-row reads)
+__global__ void __launch_bounds__(1024) rotary_tiles_kernel(const float* __restrict__ cos_t, const float* __restrict__ sin_t,
+                                                            uint8_t* __restrict__ rot, int N, int tp) {
+  const int t = blockIdx.x, b = blockIdx.y;
+  const int r = threadIdx.x >> 3, c = threadIdx.x & 7, n = t * kTile + r;
+  float4 cv = make_float4(1.f, 1.f, 1.f, 1.f), sv = make_float4(0.f, 0.f, 0.f, 0.f);
+  if (n < N) {
+    cv = __ldg(reinterpret_cast<const float4*>(cos_t + (static_cast<size_t>(b) * N + n) * 32) + c);
+    sv = __ldg(reinterpret_cast<const float4*>(sin_t + (static_cast<size_t>(b) * N + n) * 32) + c);
+  }
+  uint8_t* dst = rot + (static_cast<size_t>(b) * tp + t) * 32768 + r * 128 + ((c ^ (r & 7)) << 4);
+  *reinterpret_cast<float4*>(dst) = cv;
+  *reinterpret_cast<float4*>(dst + kHalfAtom) = sv;
+}
+
+// h (rows, 512) f32 -> GELU(LayerNorm(h)) as split tiles [rows/128][8][32 KB]
+// (lightglue.py:173-174: LayerNorm(2d, eps, affine) then exact-erf GELU).  Warp per row.
+__global__ void __launch_bounds__(256) ln_gelu_tiles_kernel(const float* __restrict__ h, const float* __restrict__ gamma,
+                                                            const float* __restrict__ beta, float eps,
+                                                            uint8_t* __restrict__ tiles, int rows) {
+  const int lane = threadIdx.x & 31;
+  const int row = blockIdx.x * 8 + (threadIdx.x >> 5);
+  if (row >= rows) return;
+  const float4* src = reinterpret_cast<const float4*>(h + static_cast<size_t>(row) * 512);
+  float x[16];
+#pragma unroll
+  for (int j = 0; j < 4; ++j) {
+    const float4 a = __ldg(src + j * 32 + lane);
+    x[4 * j] = a.x; x[4 * j + 1] = a.y; x[4 * j + 2] = a.z; x[4 * j + 3] = a.w;
+  }
+  float s = 0.f;
+#pragma unroll
+  for (int i = 0; i < 16; ++i) s += x[i];
+  const float mean = warp_sum(s) * (1.f / 512.f);
+  float q = 0.f;
+#pragma unroll
+  for (int i = 0; i < 16; ++i) { const float d = x[i] - mean; q += d * d; }
+  const float rstd = rsqrtf(warp_sum(q) * (1.f / 512.f) + eps);
+  const int rt = row >> 7, r = row & 127;
+  uint8_t* tile = tiles + static_cast<size_t>(rt) * 8 * kSplitAtom;
+#pragma unroll
+  for (int j = 0; j < 4; ++j) {
+    const int col = j * 128 + lane * 4;
+    const float4 g = __ldg(reinterpret_cast<const float4*>(gamma + col)), bt = __ldg(reinterpret_cast<const float4*>(beta + col));
+    const float gg[4] = {g.x, g.y, g.z, g.w}, bb[4] = {bt.x, bt.y, bt.z, bt.w};
+    float y[4];
+#pragma unroll
+    for (int e = 0; e < 4; ++e) {
+      const float z = (x[4 * j + e] - mean) * rstd * gg[e] + bb[e];
+      y[e] = 0.5f * z * (1.f + erff(z * 0.70710678118654752f));
+    }
+    const __nv_bfloat16 h0 = __float2bfloat16_rn(y[0]), h1 = __float2bfloat16_rn(y[1]), h2 = __float2bfloat16_rn(y[2]),
+                        h3 = __float2bfloat16_rn(y[3]);
+    uint2 hi, lo;
+    hi.x = static_cast<uint32_t>(__bfloat16_as_ushort(h0)) | (static_cast<uint32_t>(__bfloat16_as_ushort(h1)) << 16);
+    hi.y = static_cast<uint32_t>(__bfloat16_as_ushort(h2)) | (static_cast<uint32_t>(__bfloat16_as_ushort(h3)) << 16);
+    lo.x = pack_bf16x2(y[0] - __bfloat162float(h0), y[1] - __bfloat162float(h1));
+    lo.y = pack_bf16x2(y[2] - __bfloat162float(h2), y[3] - __bfloat162float(h3));
+    const int ka = col >> 6, cc = col & 63;
+    uint8_t* at = tile + ka * kSplitAtom + sw128_offset(r, cc >> 3) + (cc & 7) * 2;
+    *reinterpret_cast<uint2*>(at) = hi;
+    *reinterpret_cast<uint2*>(at + kHalfAtom) = lo;
+  }
+}
+
+static int sm_count() {
+  static int n = 0;
+  if (n == 0) {
+    int dev = 0;
+    cudaGetDevice(&dev);
+    cudaDeviceGetAttribute(&n, cudaDevAttrMultiProcessorCount, dev);
+    if (n <= 0) n = 148;
+  }
+  return n;
+}
+
+template <int kNt, int kEpi>
+static int launch_linear(const LinearParams& p, cudaStream_t stream) {
+  constexpr int smem = linear_smem_bytes<kNt, kEpi>();
+  static bool attr_done = false;
+  if (!attr_done) {
+    cudaError_t e = cudaFuncSetAttribute(linear_kernel<kNt, kEpi>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
+    if (e != cudaSuccess) return static_cast<int>(e);
+    attr_done = true;
+  }
+  const int items = p.row_tiles * p.n_tiles;
+  const int grid = items < sm_count() ? items : sm_count();
+  linear_kernel<kNt, kEpi><<<grid, kLinThreads, smem, stream>>>(p);
+  return static_cast<int>(cudaGetLastError());
+}
+
+}  // namespace lg
+
+// ============================================================================ C ABI
+static bool aligned16(const void* p) { return (reinterpret_cast<uintptr_t>(p) & 15) == 0; }
+
+extern "C" int lg_pack_weight(const float* w, void* out, int n_out, int k, int nt, cudaStream_t stream) {
+  if (!w || !out) return LG_ERR_NULL;
+  if (n_out <= 0 || k <= 0 || k % 64 || (nt != 192 && nt != 256) || n_out % nt) return LG_ERR_SHAPE;
+  if (!aligned16(w) || !aligned16(out)) return LG_ERR_ALIGN;
+  const int total = n_out * (k / 8);
+  lg::pack_weight_kernel<<<(total + 255) / 256, 256, 0, stream>>>(w, static_cast<uint8_t*>(out), n_out, k, nt);
+  return static_cast<int>(cudaGetLastError());
+}
+
+extern "C" int lg_rows_to_tiles(const float* x, void* tiles, int B, int N, int K, int tp, cudaStream_t stream) {
+  if (!x || !tiles) return LG_ERR_NULL;
+  if (B <= 0 || N <= 0 || K <= 0 || K % 64 || tp * lg::kTile < N) return LG_ERR_SHAPE;
+  if (!aligned16(x) || !aligned16(tiles)) return LG_ERR_ALIGN;
+  lg::rows_to_tiles_kernel<<<dim3(tp, B), 1024, 0, stream>>>(x, static_cast<uint8_t*>(tiles), N, K, tp);
+  return static_cast<int>(cudaGetLastError());
+}
+
+extern "C" int lg_tiles_to_rows(const void* tiles, float* x, int B, int N, int K, int tp, cudaStream_t stream) {
+  if (!x || !tiles) return LG_ERR_NULL;
+  if (B <= 0 || N <= 0 || K <= 0 || K % 64 || tp * lg::kTile < N) return LG_ERR_SHAPE;
+  if (!aligned16(x) || !aligned16(tiles)) return LG_ERR_ALIGN;
+  lg::tiles_to_rows_kernel<<<dim3(tp, B), 1024, 0, stream>>>(static_cast<const uint8_t*>(tiles), x, N, K, tp);
+  return static_cast<int>(cudaGetLastError());
+}
+
+extern "C" int lg_rotary_tiles(const float* cos_t, const float* sin_t, void* rot_tiles, int B, int N, int tp,
+                               cudaStream_t stream) {
+  if (!cos_t || !sin_t || !rot_tiles) return LG_ERR_NULL;
+  if (B <= 0 || N <= 0 || tp * lg::kTile < N) return LG_ERR_SHAPE;
+  lg::rotary_tiles_kernel<<<dim3(tp, B), 1024, 0, stream>>>(cos_t, sin_t, static_cast<uint8_t*>(rot_tiles), N, tp);
+  return static_cast<int>(cudaGetLastError());
+}
+
+extern "C" int lg_ln_gelu_tiles(const float* h, const float* gamma, const float* beta, float eps, void* tiles, int rows,
+                                cudaStream_t stream) {
+  if (!h || !gamma || !beta || !tiles) return LG_ERR_NULL;
+  if (rows <= 0 || rows % lg::kTile) return LG_ERR_SHAPE;
+  lg::ln_gelu_tiles_kernel<<<(rows + 7) / 8, 256, 0, stream>>>(h, gamma, beta, eps, static_cast<uint8_t*>(tiles), rows);
+  return static_cast<int>(cudaGetLastError());
+}
+
+static int check_linear(const void* a0, int a0_atoms, const void* a1, int a1_atoms, const void* w, const float* bias,
+                        int row_tiles, int n_out, int nt) {
+  if (!a0 || !w || !bias) return LG_ERR_NULL;
+  if ((a1 == nullptr) != (a1_atoms == 0)) return LG_ERR_NULL;
+  if (a0_atoms <= 0 || a1_atoms < 0 || row_tiles <= 0 || n_out <= 0 || n_out % nt) return LG_ERR_SHAPE;
+  if (!aligned16(a0) || !aligned16(a1) || !aligned16(w)) return LG_ERR_ALIGN;
+  return 0;
+}
+
+extern "C" int lg_linear_split(const void* a0, int a0_atoms, const void* a1, int a1_atoms, const void* w,
+                               const float* bias, const void* resid_tiles, void* out_tiles, int row_tiles, int n_out,
+                               cudaStream_t stream) {
+  if (int e = check_linear(a0, a0_atoms, a1, a1_atoms, w, bias, row_tiles, n_out, 256)) return e;
+  if (!out_tiles) return LG_ERR_NULL;
+  lg::LinearParams p{};
+  p.a0 = static_cast<const uint8_t*>(a0); p.a1 = static_cast<const uint8_t*>(a1);
+  p.a0_atoms = a0_atoms; p.a1_atoms = a1_atoms;
+  p.w = static_cast<const uint8_t*>(w); p.bias = bias; p.row_tiles = row_tiles; p.n_tiles = n_out / 256;
+  p.out_tiles = static_cast<uint8_t*>(out_tiles); p.resid_tiles = static_cast<const uint8_t*>(resid_tiles);
+  return lg::launch_linear<256, lg::kEpiSplit>(p, stream);
+}
+
+extern "C" int lg_linear_f32(const void* a0, int a0_atoms, const void* a1, int a1_atoms, const void* w,
+                             const float* bias, float* out, int64_t ld, int row_tiles, int n_out, cudaStream_t stream) {
+  if (int e = check_linear(a0, a0_atoms, a1, a1_atoms, w, bias, row_tiles, n_out, 256)) return e;
+  if (!out) return LG_ERR_NULL;
+  if (ld < n_out || ld % 4 || !aligned16(out)) return LG_ERR_ALIGN;
+  lg::LinearParams p{};
+  p.a0 = static_cast<const uint8_t*>(a0); p.a1 = static_cast<const uint8_t*>(a1);
+  p.a0_atoms = a0_atoms; p.a1_atoms = a1_atoms;
+  p.w = static_cast<const uint8_t*>(w); p.bias = bias; p.row_tiles = row_tiles; p.n_tiles = n_out / 256;
+  p.out_f32 = out; p.ld = ld;
+  return lg::launch_linear<256, lg::kEpiF32>(p, stream);
+}
+
+extern "C" int lg_linear_qkv_self(const void* a, const void* w, const float* bias, const void* rot_tiles, void* q0,
+                                  void* k0, void* v0, void* q1, void* k1, void* v1, int B, int H, int tp0, int tp1,
+                                  cudaStream_t stream) {
+  if (!a || !w || !bias || !rot_tiles || !q0 || !k0 || !v0) return LG_ERR_NULL;
+  if (tp1 > 0 && (!q1 || !k1 || !v1)) return LG_ERR_NULL;
+  if (B <= 0 || H != 4 || tp0 <= 0 || tp1 < 0) return LG_ERR_SHAPE;
+  lg::LinearParams p{};
+  p.a0 = static_cast<const uint8_t*>(a); p.a0_atoms = 4;
+  p.w = static_cast<const uint8_t*>(w); p.bias = bias; p.row_tiles = B * (tp0 + tp1); p.n_tiles = H;
+  p.q_tiles[0] = static_cast<uint8_t*>(q0); p.k_tiles[0] = static_cast<uint8_t*>(k0); p.v_tiles[0] = static_cast<uint8_t*>(v0);
+  p.q_tiles[1] = static_cast<uint8_t*>(q1); p.k_tiles[1] = static_cast<uint8_t*>(k1); p.v_tiles[1] = static_cast<uint8_t*>(v1);
+  p.rot_tiles = static_cast<const uint8_t*>(rot_tiles);
+  p.B = B; p.H = H; p.tp0 = tp0; p.tp1 = tp1;
+  return lg::launch_linear<192, lg::kEpiQkvSelf>(p, stream);
+}
+
+extern "C" int lg_linear_qkv_cross(const void* a, const void* w, const float* bias, void* qk0, void* v0, void* qk1,
+                                   void* v1, int B, int H, int tp0, int tp1, cudaStream_t stream) {
+  if (!a || !w || !bias || !qk0 || !v0) return LG_ERR_NULL;
+  if (tp1 > 0 && (!qk1 || !v1)) return LG_ERR_NULL;
+  if (B <= 0 || H != 4 || tp0 <= 0 || tp1 < 0) return LG_ERR_SHAPE;
+  lg::LinearParams p{};
+  p.a0 = static_cast<const uint8_t*>(a); p.a0_atoms = 4;
+  p.w = static_cast<const uint8_t*>(w); p.bias = bias; p.row_tiles = B * (tp0 + tp1); p.n_tiles = 2;
+  p.q_tiles[0] = static_cast<uint8_t*>(qk0); p.v_tiles[0] = static_cast<uint8_t*>(v0);
+  p.q_tiles[1] = static_cast<uint8_t*>(qk1); p.v_tiles[1] = static_cast<uint8_t*>(v1);
+  p.B = B; p.H = H; p.tp0 = tp0; p.tp1 = tp1;
+  return lg::launch_linear<256, lg::kEpiQkvCross>(p, stream);
+}

@@ -59,6 +59,56 @@ int lg_attention(const void* q_tiles, const void* k_tiles, const void* v_tiles, 
                  const int* k_len, int B, int H, int nq, int nk, int tq_pad, int tk_pad, float softmax_scale,
                  cudaStream_t stream);
 
+/* ---- split-tile activations and the per-token linears (lg_linear.cu) ----------------------------
+ * "Split tiles": an activation matrix [rows][K] is held as [row tile of 128][K/64 atoms][hi 16 KB | lo 16 KB],
+ * each 16 KB block the byte image of a SWIZZLE_128B K-major tile of bf16 (x = hi + lo, ~16 mantissa bits).
+ * A batch of B images with N points each occupies B*tp row tiles (tp*128 >= N, rows >= N zero). */
+
+/* One-off weight packing: w (n_out, k) f32 row-major (nn.Linear.weight) -> [n_out/nt][k/64][hi | lo][nt*128 B].
+ * nt = 256 (192 for lg_linear_qkv_self); out holds n_out*k*4 bytes. */
+int lg_pack_weight(const float* w, void* out, int n_out, int k, int nt, cudaStream_t stream);
+
+/* x (B,N,K) f32 contiguous <-> split tiles [B*tp][K/64][32 KB]  (the .contiguous() copies of
+ * lightglue.py:478-479 become this format change). */
+int lg_rows_to_tiles(const float* x, void* tiles, int B, int N, int K, int tp, cudaStream_t stream);
+int lg_tiles_to_rows(const void* tiles, float* x, int B, int N, int K, int tp, cudaStream_t stream);
+
+/* Compact rotary tables (B,N,32) f32 from lg_posenc -> [B*tp][cos 16 KB | sin 16 KB] row tiles. */
+int lg_rotary_tiles(const float* cos_t, const float* sin_t, void* rot_tiles, int B, int N, int tp,
+                    cudaStream_t stream);
+
+/* FFN middle (lightglue.py:173-174): h (rows,512) f32 -> GELU(LayerNorm(h; gamma, beta, eps)) as split
+ * tiles [rows/128][8][32 KB]; rows is a multiple of 128. */
+int lg_ln_gelu_tiles(const float* h, const float* gamma, const float* beta, float eps, void* tiles, int rows,
+                     cudaStream_t stream);
+
+/* y = [a0 | a1] . w^T + bias as a 3-term split-bf16 tcgen05 GEMM (nn.Linear, lightglue.py:171-176,190,246,310).
+ * a0 / a1: split tiles with a0_atoms / a1_atoms K atoms (a1 NULL, 0 = none: torch.cat([x, msg], -1) of
+ * lightglue.py:191,247 without the copy); w from lg_pack_weight(nt=256); n_out multiple of 256.
+ * lg_linear_split: out (and optional residual, added in fp32: x + ffn(...)) are split tiles
+ *   [row_tiles][n_out/64][32 KB].   lg_linear_f32: out f32 rows with pitch ld floats. */
+int lg_linear_split(const void* a0, int a0_atoms, const void* a1, int a1_atoms, const void* w, const float* bias,
+                    const void* resid_tiles, void* out_tiles, int row_tiles, int n_out, cudaStream_t stream);
+int lg_linear_f32(const void* a0, int a0_atoms, const void* a1, int a1_atoms, const void* w, const float* bias,
+                  float* out, int64_t ld, int row_tiles, int n_out, cudaStream_t stream);
+
+/* SelfBlock Wqkv + head split + rotary (lightglue.py:184-188) -> lg_attention operand tiles.  a: split tiles
+ * of x, K = 256, rows = image-0 batch (B*tp0 tiles) then image-1 batch (B*tp1 tiles; tp1 may be 0).
+ * w: Wqkv rows permuted to [head][q 64 | k 64 | v 64] (row h*192 + d*3 + part of the reference ->
+ * h*192 + part*64 + d), packed with nt = 192; bias permuted alike.  q/k/v tiles per side: [B][H][tp][16 KB]. */
+int lg_linear_qkv_self(const void* a, const void* w, const float* bias, const void* rot_tiles, void* q0, void* k0,
+                       void* v0, void* q1, void* k1, void* v1, int B, int H, int tp0, int tp1, cudaStream_t stream);
+
+/* CrossBlock to_qk | to_v (lightglue.py:223-228): w = rows [to_qk (256) ; to_v (256)], nt = 256. */
+int lg_linear_qkv_cross(const void* a, const void* w, const float* bias, void* qk0, void* v0, void* qk1, void* v1,
+                        int B, int H, int tp0, int tp1, cudaStream_t stream);
+
+/* lg_attention writing the context as split tiles (K atom = head) for lg_linear: row tile of
+ * (image b, query tile t) = out_rt_base + b*tq_pad + t. */
+int lg_attention_tiles(const void* q_tiles, const void* k_tiles, const void* v_tiles, void* out_tiles,
+                       int out_rt_base, const int* q_len, const int* k_len, int B, int H, int nq, int nk, int tq_pad,
+                       int tk_pad, float softmax_scale, cudaStream_t stream);
+
 /* (3) MatchAssignment.forward from the similarity on (lightglue.py:310-315) + sigmoid_log_double_softmax
  * (lightglue.py:284-296).  md0 (B,M,256), md1 (B,N,256) f32 = final_proj outputs; prescale multiplies
  * both (d^-1/4 = 0.25, lightglue.py:310); z0 (B,M), z1 (B,N) f32 matchability logits.  Writes scores
