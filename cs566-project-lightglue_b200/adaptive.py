@@ -13,12 +13,12 @@ import torch
 from . import _cabi as C
 
 
-def forward_adaptive(model, data, desc0, desc1, cs0, cs1):
+def forward_adaptive(model, eng, cs0, cs1):
+    """eng: TileEngine already loaded with the (projected) descriptors of ONE pair."""
     conf = model.conf
-    b, m, _ = desc0.shape
-    _, n, _ = desc1.shape
+    b, m, n = eng.B, eng.M, eng.N
     assert b == 1, "adaptive depth/width runs one pair per call, like the reference (lightglue.py:528,533)"
-    dev = desc0.device
+    dev = eng.dev
     L = conf.n_layers
     do_early_stop = conf.depth_confidence > 0
     do_point_pruning = conf.width_confidence > 0
@@ -30,10 +30,8 @@ def forward_adaptive(model, data, desc0, desc1, cs0, cs1):
     last = L - 1
     ref_desc = None
     for i in range(L):
-        layer = model.transformers[i]
-        desc0 = model._self_block(layer.self_attn, desc0, cs0, None)
-        desc1 = model._self_block(layer.self_attn, desc1, cs1, None)
-        desc0, desc1 = model._cross_block(layer.cross_attn, desc0, desc1, None, None)
+        eng.layer(i)
+        desc0, desc1 = eng.rows()
         if i == L - 1:
             ref_desc = (desc0, desc1)
             break
@@ -53,14 +51,20 @@ def forward_adaptive(model, data, desc0, desc1, cs0, cs1):
             if ratio > np.float32(conf.depth_confidence):
                 last = i
                 break
-        if do_point_pruning:
+        if do_point_pruning and (k0 < eng.M or k1 < eng.N):
+            if k0 == 0 or k1 == 0:
+                raise RuntimeError("every keypoint of one image was pruned (the reference's max() would raise too)")
             desc0, c0, s0, ind0 = C.prune_gather(desc0, cs0[0], cs0[1], ind0, keep0, cnt0, prune0)
             desc1, c1, s1, ind1 = C.prune_gather(desc1, cs1[0], cs1[1], ind1, keep1, cnt1, prune1)
             desc0, cs0, ind0 = desc0[:, :k0].contiguous(), (c0[:, :k0].contiguous(), s0[:, :k0].contiguous()), ind0[:, :k0].contiguous()
             desc1, cs1, ind1 = desc1[:, :k1].contiguous(), (c1[:, :k1].contiguous(), s1[:, :k1].contiguous()), ind1[:, :k1].contiguous()
-            if k0 == 0 or k1 == 0:
-                raise RuntimeError("every keypoint of one image was pruned (the reference's max() would raise too)")
-    scores = model._assign(last, desc0, desc1, None, None)
+            # re-tile the compacted tokens (the index_select of lightglue.py:537-547)
+            eng = model._engine(1, k0, k1, dev)
+            eng.load_rows(desc0, desc1, cs0, cs1)
+        elif do_point_pruning:  # nothing dropped: only the prune counters advance (lightglue.py:540,547)
+            prune0[:, ind0[0]] += 1
+            prune1[:, ind1[0]] += 1
+    scores = model._assign(last, eng, desc0, desc1, None, None)
     m0, m1, ms0, ms1 = C.filter_matches(scores, conf.filter_threshold)
     if do_point_pruning:  # scatter back through ind0 / ind1 (lightglue.py:553-562)
         m0_ = torch.full((b, m), -1, device=dev, dtype=m0.dtype)

@@ -8,10 +8,10 @@ state_dict names (lightglue.py:380-396), selected through `__main_model__` like 
 (lightglue.py:666; gluefactory/models/__init__.py:20-25):  `model.matcher.name: b200glue.matcher`.
 
 The hot subsystems run as hand-written sm_100a kernels behind the C ABI in include/lg_b200.h
-(positional encoding, rotary + operand packing, tcgen05 flash attention, TF32x3 assignment,
-match filter, confidence / pruning).  The per-token linears, LayerNorm and GELU stay on
-cuBLAS / torch in this cut.  There is no CPU path and no fallback: inputs
-must live on a CUDA device and the shared library must be present.
+(positional encoding, split-bf16 tcgen05 linears with the rotary / head split / residual fused
+into their epilogues, LayerNorm + GELU, tcgen05 flash attention, TF32x3 assignment, match filter,
+confidence / pruning); see engine.py for the per-layer launch sequence.  There is no CPU path
+and no fallback: inputs must live on a CUDA device and the shared library must be present.
 """
 import math
 from pathlib import Path
@@ -111,13 +111,6 @@ class _TokenConfidence(nn.Module):  # lightglue.py:96-99
         self.token = nn.Sequential(nn.Linear(d, 1), nn.Sigmoid())
 
 
-def _apply_ffn(ffn, x, msg):
-    """x + Linear(GELU(LayerNorm(Linear(cat[x, msg])))) -- lightglue.py:171-176,191 (cuBLAS/torch, N1)."""
-    h = F.linear(torch.cat([x, msg], -1), ffn[0].weight, ffn[0].bias)
-    h = F.layer_norm(h, (h.shape[-1],), ffn[1].weight, ffn[1].bias, ffn[1].eps)
-    return x + F.linear(F.gelu(h), ffn[3].weight, ffn[3].bias)
-
-
 class LightGlue(nn.Module):
     default_conf = {
         "name": "lightglue",
@@ -183,35 +176,25 @@ class LightGlue(nn.Module):
     def confidence_threshold(self, layer_index: int) -> float:  # lightglue.py:581-584
         return float(np.clip(0.8 + 0.1 * np.exp(-4.0 * layer_index / self.conf.n_layers), 0, 1))
 
-    # ------------------------------------------------------------------ blocks
-    def _self_block(self, blk, x, cs, lens):
-        H = self.conf.num_heads
-        qkv = F.linear(x, blk.Wqkv.weight, blk.Wqkv.bias)
-        q, k, v = C.pack_self_qkv(qkv, cs[0], cs[1], lens, H)
-        n = x.shape[1]
-        ctx = C.attention(q, k, v, n, n, lens, lens, scale=64 ** -0.5)
-        msg = F.linear(ctx, blk.out_proj.weight, blk.out_proj.bias)
-        return _apply_ffn(blk.ffn, x, msg)
+    # ------------------------------------------------------------------ packed weights / engine
+    def _packed(self):
+        from .engine import PackedWeights
 
-    def _cross_block(self, blk, x0, x1, len0, len1):
-        H = self.conf.num_heads
-        qk0, qk1 = F.linear(x0, blk.to_qk.weight, blk.to_qk.bias), F.linear(x1, blk.to_qk.weight, blk.to_qk.bias)
-        v0, v1 = F.linear(x0, blk.to_v.weight, blk.to_v.bias), F.linear(x1, blk.to_v.weight, blk.to_v.bias)
-        qt0, vt0 = C.pack_cross_qkv(qk0, v0, len0, H)
-        qt1, vt1 = C.pack_cross_qkv(qk1, v1, len1, H)
-        m, n = x0.shape[1], x1.shape[1]
-        # each direction is one flash pass over the shared to_qk projection (why the
-        # similarity tile is not shared between the two softmax directions)
-        m0 = C.attention(qt0, qt1, vt1, m, n, len0, len1, scale=64 ** -0.5)
-        m1 = C.attention(qt1, qt0, vt0, n, m, len1, len0, scale=64 ** -0.5)
-        m0 = F.linear(m0, blk.to_out.weight, blk.to_out.bias)
-        m1 = F.linear(m1, blk.to_out.weight, blk.to_out.bias)
-        return _apply_ffn(blk.ffn, x0, m0), _apply_ffn(blk.ffn, x1, m1)
+        pk = getattr(self, "_pk", None)
+        if pk is None or pk.signature != PackedWeights.sign(self):
+            pk = self._pk = PackedWeights(self)
+        return pk
 
-    def _assign(self, i, d0, d1, len0, len1):
+    def _engine(self, B, M, N, device):
+        from .engine import TileEngine
+
+        return TileEngine(self._packed(), B, M, N, device, self.conf.num_heads)
+
+    def _assign(self, i, eng, d0, d1, len0, len1):
+        """MatchAssignment.forward (lightglue.py:306-315): final_proj on tcgen05, matchability logits, then
+        the fused similarity + double log-softmax kernel."""
         head = self.log_assignment[i]
-        md0 = F.linear(d0, head.final_proj.weight, head.final_proj.bias)
-        md1 = F.linear(d1, head.final_proj.weight, head.final_proj.bias)
+        md0, md1 = eng.final_proj(i)
         z0 = F.linear(d0, head.matchability.weight, head.matchability.bias).squeeze(-1).contiguous()
         z1 = F.linear(d1, head.matchability.weight, head.matchability.bias).squeeze(-1).contiguous()
         return C.assign(md0, md1, z0, z1, len0, len1, prescale=self.conf.descriptor_dim ** -0.25)
@@ -259,24 +242,21 @@ class LightGlue(nn.Module):
                        pe.condition_modulation.bias, float(m))
         cs1 = C.posenc(kpts1.float().contiguous(), self._image_size(data, "view1", kpts1), pe.Wr.weight, wc,
                        pe.condition_modulation.bias, float(n))
-        if conf.input_dim != conf.descriptor_dim:
-            desc0 = F.linear(desc0, self.input_proj.weight, self.input_proj.bias)
-            desc1 = F.linear(desc1, self.input_proj.weight, self.input_proj.bias)
+        eng = self._engine(b, m, n, dev)
+        eng.load(desc0, desc1, cs0, cs1)
 
         do_early_stop = conf.depth_confidence > 0
         do_point_pruning = conf.width_confidence > 0
         if do_early_stop or do_point_pruning:
             from .adaptive import forward_adaptive
 
-            return forward_adaptive(self, data, desc0, desc1, cs0, cs1)
+            return forward_adaptive(self, eng, cs0, cs1)
 
         L = conf.n_layers
         for i in range(L):
-            layer = self.transformers[i]
-            desc0 = self._self_block(layer.self_attn, desc0, cs0, len0)
-            desc1 = self._self_block(layer.self_attn, desc1, cs1, len1)
-            desc0, desc1 = self._cross_block(layer.cross_attn, desc0, desc1, len0, len1)
-        scores = self._assign(L - 1, desc0, desc1, len0, len1)
+            eng.layer(i, len0, len1)
+        desc0, desc1 = eng.rows()
+        scores = self._assign(L - 1, eng, desc0, desc1, len0, len1)
         m0, m1, ms0, ms1 = C.filter_matches(scores, conf.filter_threshold, len0, len1)
         return {
             "matches0": m0, "matches1": m1,
