@@ -5,7 +5,7 @@
 // score matrix.  For CrossBlock (lightglue.py:229-244) it is called once per direction on
 // the shared to_qk projection (qk0 against qk1/v1, then qk1 against qk0/v0).
 //
-// Shape of one CTA (320 threads, 1 CTA / SM):
+// Shape of one CTA (384 threads, 1 CTA / SM; setmaxnreg moves registers to the softmax warpgroups):
 //   * 256 query rows = two 128-row tiles, one per softmax warpgroup (warps 0-3, 4-7);
 //     both tiles share every staged K / V^T tile.
 //   * warp 8 (one lane): bulk (TMA engine) copies of the pre-swizzled bf16 operand tiles
@@ -15,7 +15,7 @@
 //   * softmax warpgroups: thread == row.  tcgen05.ld S from TMEM, fp32 online softmax in the
 //     exp2 domain with lazy (thresholded) rescaling of O, P written as bf16 into a
 //     SWIZZLE_128B shared tile that feeds the second MMA.
-// The MMA order  PV0_j, QK0_{j+1}, PV1_j, QK1_{j+1}  lets each warpgroup's softmax overlap the
+// The MMA order  QK0_{j+1}, PV0_j, QK1_{j+1}, PV1_j  lets each warpgroup's softmax overlap the
 // other tile's tensor work.
 #include "lg_common.cuh"
 #include "lg_b200.h"
@@ -24,9 +24,24 @@ namespace lg {
 
 constexpr int kStages = 3;
 constexpr int kTileBytes = 16384;
-constexpr int kAttnThreads = 320;
+constexpr int kAttnThreads = 384;  // 2 softmax warpgroups + 1 warpgroup holding the producer and MMA warps
 constexpr uint32_t kColS = 0, kColO = 256;  // TMEM column map: S_t at t*128, O_t at 256 + t*64
 constexpr float kRescaleThreshold = 8.0f;   // log2 units; P stays <= 2^8
+
+__device__ __forceinline__ float ex2_approx(float x) {
+  float y;
+  asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
+  return y;
+}
+template <int N>
+__device__ __forceinline__ void reg_inc() { asm volatile("setmaxnreg.inc.sync.aligned.u32 %0;" ::"n"(N)); }
+template <int N>
+__device__ __forceinline__ void reg_dec() { asm volatile("setmaxnreg.dec.sync.aligned.u32 %0;" ::"n"(N)); }
+__device__ __forceinline__ float fmax3(float a, float b, float c) {
+  float d;
+  asm("max.f32 %0, %1, %2, %3;" : "=f"(d) : "f"(a), "f"(b), "f"(c));
+  return d;
+}
 
 struct AttnParams {
   const uint8_t* q_tiles;
@@ -47,6 +62,7 @@ struct __align__(8) AttnBarriers {
   uint64_t kv_empty[kStages];
   uint64_t s_full[2];
   uint64_t p_full[2];
+  uint64_t pv_done[2];
   uint64_t o_final;
   uint32_t tmem_base;
 };
@@ -91,7 +107,7 @@ __global__ void __launch_bounds__(kAttnThreads, 1) attention_kernel(const AttnPa
   if (threadIdx.x == 0) {
     mbar_init(&bar->q_full, 1);
     for (int s = 0; s < kStages; ++s) { mbar_init(&bar->kv_full[s], 1); mbar_init(&bar->kv_empty[s], 1); }
-    for (int t = 0; t < 2; ++t) { mbar_init(&bar->s_full[t], 1); mbar_init(&bar->p_full[t], 128); }
+    for (int t = 0; t < 2; ++t) { mbar_init(&bar->s_full[t], 1); mbar_init(&bar->p_full[t], 128); mbar_init(&bar->pv_done[t], 1); }
     mbar_init(&bar->o_final, 1);
     fence_mbar_init();
   }
@@ -101,6 +117,8 @@ __global__ void __launch_bounds__(kAttnThreads, 1) attention_kernel(const AttnPa
   tc_fence_after();
   const uint32_t tmem = bar->tmem_base;
 
+  if (warp >= 8) {
+  reg_dec<88>();  // pool = 384 x 168: 128*(208+208+88) registers
   if (warp == 8) {
     // ------------------------------------------------------------------ producer
     if (lane == 0) {
@@ -150,19 +168,22 @@ __global__ void __launch_bounds__(kAttnThreads, 1) attention_kernel(const AttnPa
       for (int j = 0; j < nkt; ++j) {
         const int s = j % kStages, sn = (j + 1) % kStages;
         for (int t = 0; t < 2; ++t) {
-          mbar_wait(&bar->p_full[t], j & 1);
+          mbar_wait(&bar->p_full[t], j & 1);  // P_t(j) staged AND S_t(j) drained
           tc_fence_after();
-          issue_pv(t, s, j);
-          if (t == 1) umma_commit(&bar->kv_empty[s]);  // K_j and V_j are dead once PV1_j retires
           if (j + 1 < nkt) {
             if (t == 0) { mbar_wait(&bar->kv_full[sn], ((j + 1) / kStages) & 1); tc_fence_after(); }
-            issue_qk(t, sn);
+            issue_qk(t, sn);                  // S_t(j+1) first: it is what the softmax warpgroup waits for
           }
+          issue_pv(t, s, j);
+          umma_commit(&bar->pv_done[t]);
+          if (t == 1) umma_commit(&bar->kv_empty[s]);  // K_j and V_j are dead once PV1_j retires
         }
       }
       umma_commit(&bar->o_final);
     }
+  }
   } else {
+    reg_inc<208>();
     // ------------------------------------------------------------------ softmax warpgroups
     const int t = warp >> 2;                       // query tile of this warpgroup
     const int r = (warp & 3) * 32 + lane;          // row == TMEM lane
@@ -172,68 +193,109 @@ __global__ void __launch_bounds__(kAttnThreads, 1) attention_kernel(const AttnPa
     uint8_t* myP = sP + t * 2 * kTileBytes;
     const float c = p.scale_log2;
     float m_used = -INFINITY, l = 0.f;
-    uint32_t v[32];
+    uint32_t va[32], vb[32];
+    const float2 c2 = make_float2(c, c);
 
     for (int j = 0; j < nkt; ++j) {
       const int rem = k_len - j * kTile;           // valid keys in this block (>= 1)
       const bool partial = rem < kTile;
       mbar_wait(&bar->s_full[t], j & 1);
       tc_fence_after();
-      // pass 1: block row max
-      float mx = -INFINITY;
+      if (j == 0) {
+        // first block: the reference max is not known yet -> one max-only sweep
+        float mx = -INFINITY;
 #pragma unroll
-      for (int cb = 0; cb < 4; ++cb) {
-        tmem_ld32(tS + cb * 32, v);
-        tmem_wait_ld();
-        if (!partial) {
+        for (int cb = 0; cb < 4; ++cb) {
+          tmem_ld32(tS + cb * 32, va);
+          tmem_wait_ld();
+          float m0 = -INFINITY, m1 = -INFINITY;
 #pragma unroll
-          for (int i = 0; i < 32; ++i) mx = fmaxf(mx, __uint_as_float(v[i]));
-        } else {
-#pragma unroll
-          for (int i = 0; i < 32; ++i) mx = fmaxf(mx, (cb * 32 + i < rem) ? __uint_as_float(v[i]) : -INFINITY);
+          for (int i = 0; i < 32; i += 4) {
+            const bool k0 = !partial || cb * 32 + i < rem, k1 = !partial || cb * 32 + i + 1 < rem;
+            const bool k2 = !partial || cb * 32 + i + 2 < rem, k3 = !partial || cb * 32 + i + 3 < rem;
+            m0 = fmax3(m0, k0 ? __uint_as_float(va[i]) : -INFINITY, k1 ? __uint_as_float(va[i + 1]) : -INFINITY);
+            m1 = fmax3(m1, k2 ? __uint_as_float(va[i + 2]) : -INFINITY, k3 ? __uint_as_float(va[i + 3]) : -INFINITY);
+          }
+          mx = fmax3(mx, m0, m1);
         }
+        m_used = mx;
       }
-      // lazy rescale: only move the reference max when it grew by more than the threshold
-      const bool need = (mx - m_used) * c > kRescaleThreshold;  // true on the first block (m_used = -inf)
-      if (__any_sync(0xffffffffu, need)) {
+      // Single sweep: P = exp2(S*c - m_used*c) with the (possibly stale) reference max of the previous
+      // blocks while the block max is gathered on the side.  Only when some row of the warp outgrew its
+      // reference by more than 2^kRescaleThreshold is O rescaled and the sweep repeated (rare after the
+      // first blocks) -- P <= 2^8 otherwise, harmless for the fp32 row sums and the bf16 P operand.
+      float tile_sum = 0.f;
+#pragma unroll 1
+      for (int attempt = 0; attempt < 2; ++attempt) {
+        const float ms = m_used * c;
+        const float2 nms2 = make_float2(-ms, -ms);
+        float2 s0 = make_float2(0.f, 0.f), s1 = make_float2(0.f, 0.f);
+        float m0 = -INFINITY, m1 = -INFINITY, m2 = -INFINITY, m3 = -INFINITY;
+        auto sweep = [&](uint32_t(&v)[32], const int cb) {
+          if (partial) {
+#pragma unroll
+            for (int i = 0; i < 32; ++i)
+              if (cb * 32 + i >= rem) v[i] = 0xff800000u;  // -inf: exp2 -> 0, ignored by max
+          }
+#pragma unroll
+          for (int q = 0; q < 4; ++q) {
+            float e[8];
+#pragma unroll
+            for (int i = 0; i < 8; i += 4) {
+              const float x0 = __uint_as_float(v[8 * q + i]), x1 = __uint_as_float(v[8 * q + i + 1]);
+              const float x2 = __uint_as_float(v[8 * q + i + 2]), x3 = __uint_as_float(v[8 * q + i + 3]);
+              if (i == 0) { m0 = fmax3(m0, x0, x1); m1 = fmax3(m1, x2, x3); }
+              else { m2 = fmax3(m2, x0, x1); m3 = fmax3(m3, x2, x3); }
+              const float2 t0 = __ffma2_rn(make_float2(x0, x1), c2, nms2);
+              const float2 t1 = __ffma2_rn(make_float2(x2, x3), c2, nms2);
+              e[i] = ex2_approx(t0.x); e[i + 1] = ex2_approx(t0.y);
+              e[i + 2] = ex2_approx(t1.x); e[i + 3] = ex2_approx(t1.y);
+              s0 = __fadd2_rn(s0, make_float2(e[i], e[i + 1]));
+              s1 = __fadd2_rn(s1, make_float2(e[i + 2], e[i + 3]));
+            }
+            uint4 o;
+            o.x = pack_bf16x2(e[0], e[1]); o.y = pack_bf16x2(e[2], e[3]);
+            o.z = pack_bf16x2(e[4], e[5]); o.w = pack_bf16x2(e[6], e[7]);
+            const int g = cb * 4 + q;  // 16 B chunk index along the 128 keys
+            *reinterpret_cast<uint4*>(myP + (g >> 3) * kTileBytes + sw128_offset(r, g & 7)) = o;
+          }
+        };
+        // TMEM loads run one 32-column chunk ahead of the arithmetic
+        tmem_ld32(tS, va);
+        tmem_wait_ld();
+        tmem_ld32(tS + 32, vb);
+        sweep(va, 0);
+        tmem_wait_ld();
+        tmem_ld32(tS + 64, va);
+        sweep(vb, 1);
+        tmem_wait_ld();
+        tmem_ld32(tS + 96, vb);
+        sweep(va, 2);
+        tmem_wait_ld();
+        sweep(vb, 3);
+        tile_sum = (s0.x + s0.y) + (s1.x + s1.y);
+        if (attempt == 1) break;
+        const float mx = fmaxf(fmax3(m0, m1, m2), m3);
+        const bool need = (mx - m_used) * c > kRescaleThreshold;
+        if (!__any_sync(0xffffffffu, need)) break;
         float alpha = 1.f;
-        if (need) { alpha = exp2f((m_used - mx) * c); m_used = mx; }
+        if (need) { alpha = ex2_approx((m_used - mx) * c); m_used = mx; }
         l *= alpha;
-        if (j > 0) {  // s_full(j) retiring implies PV_t(j-1) has retired: O_t is quiescent
+        if (j > 0) {
+          mbar_wait(&bar->pv_done[t], (j - 1) & 1);  // O_t quiescent: PV_t(j-1) has retired
+          tc_fence_after();
 #pragma unroll
           for (int cb = 0; cb < 2; ++cb) {
-            tmem_ld32(tO + cb * 32, v);
+            tmem_ld32(tO + cb * 32, va);
             tmem_wait_ld();
 #pragma unroll
-            for (int i = 0; i < 32; ++i) v[i] = __float_as_uint(__uint_as_float(v[i]) * alpha);
-            tmem_st32(tO + cb * 32, v);
+            for (int i = 0; i < 32; ++i) va[i] = __float_as_uint(__uint_as_float(va[i]) * alpha);
+            tmem_st32(tO + cb * 32, va);
           }
           tmem_wait_st();
         }
       }
-      const float ms = m_used * c;
-      // pass 2: P = exp2(S*c - ms) -> bf16 -> swizzled smem tile (A operand of the PV MMA)
-#pragma unroll
-      for (int cb = 0; cb < 4; ++cb) {
-        tmem_ld32(tS + cb * 32, v);
-        tmem_wait_ld();
-        float e[32];
-#pragma unroll
-        for (int i = 0; i < 32; ++i) {
-          float x = exp2f(fmaf(__uint_as_float(v[i]), c, -ms));
-          if (partial && cb * 32 + i >= rem) x = 0.f;
-          e[i] = x;
-          l += x;
-        }
-#pragma unroll
-        for (int q = 0; q < 4; ++q) {
-          uint4 o;
-          o.x = pack_bf16x2(e[8 * q], e[8 * q + 1]); o.y = pack_bf16x2(e[8 * q + 2], e[8 * q + 3]);
-          o.z = pack_bf16x2(e[8 * q + 4], e[8 * q + 5]); o.w = pack_bf16x2(e[8 * q + 6], e[8 * q + 7]);
-          const int g = cb * 4 + q;  // 16 B chunk index along the 128 keys
-          *reinterpret_cast<uint4*>(myP + (g >> 3) * kTileBytes + sw128_offset(r, g & 7)) = o;
-        }
-      }
+      l += tile_sum;
       fence_proxy_async_smem();
       tc_fence_before();
       mbar_arrive(&bar->p_full[t]);
@@ -248,14 +310,14 @@ __global__ void __launch_bounds__(kAttnThreads, 1) attention_kernel(const AttnPa
       uint8_t* dt = p.out_tiles + ((static_cast<size_t>(p.out_rt_base + b * p.tq_pad + qt0 + t) * p.H + h) * 32768);
 #pragma unroll
       for (int cb = 0; cb < 2; ++cb) {
-        tmem_ld32(tO + cb * 32, v);
+        tmem_ld32(tO + cb * 32, va);
         tmem_wait_ld();
 #pragma unroll
         for (int q = 0; q < 4; ++q) {
           uint32_t hh[4], ll[4];
 #pragma unroll
           for (int i = 0; i < 4; ++i) {
-            const float x0 = __uint_as_float(v[8 * q + 2 * i]) * inv, x1 = __uint_as_float(v[8 * q + 2 * i + 1]) * inv;
+            const float x0 = __uint_as_float(va[8 * q + 2 * i]) * inv, x1 = __uint_as_float(va[8 * q + 2 * i + 1]) * inv;
             const __nv_bfloat16 h0 = __float2bfloat16_rn(x0), h1 = __float2bfloat16_rn(x1);
             hh[i] = static_cast<uint32_t>(__bfloat16_as_ushort(h0)) | (static_cast<uint32_t>(__bfloat16_as_ushort(h1)) << 16);
             ll[i] = pack_bf16x2(x0 - __bfloat162float(h0), x1 - __bfloat162float(h1));
@@ -269,13 +331,13 @@ __global__ void __launch_bounds__(kAttnThreads, 1) attention_kernel(const AttnPa
     float4* dst = reinterpret_cast<float4*>(p.out + (static_cast<size_t>(b) * p.nq + row) * row_stride + h * kHeadDim);
 #pragma unroll
     for (int cb = 0; cb < 2; ++cb) {
-      tmem_ld32(tO + cb * 32, v);
+      tmem_ld32(tO + cb * 32, va);
       tmem_wait_ld();
       if (row < p.nq) {
 #pragma unroll
         for (int i = 0; i < 8; ++i)
-          dst[cb * 8 + i] = make_float4(__uint_as_float(v[4 * i]) * inv, __uint_as_float(v[4 * i + 1]) * inv,
-                                        __uint_as_float(v[4 * i + 2]) * inv, __uint_as_float(v[4 * i + 3]) * inv);
+          dst[cb * 8 + i] = make_float4(__uint_as_float(va[4 * i]) * inv, __uint_as_float(va[4 * i + 1]) * inv,
+                                        __uint_as_float(va[4 * i + 2]) * inv, __uint_as_float(va[4 * i + 3]) * inv);
       }
     }
     }
