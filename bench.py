@@ -221,6 +221,7 @@ def run_b200(a):
     peak = float(peaks.get("bf16_tflops_sustained", 1400.0))  # kernel timed inside a long step
     achieved = attn_flops / (attn_ms / 1e3) / 1e12
     roofline = {"kernel": "attention_kernel (tcgen05 flash attention, self + cross)", "bound": "tensor",
+                "flops": "algorithmic: 4*64*nq*nk per self launch, 3*64*nq*nk per cross direction (S counted once)",
                 "achieved": achieved, "peak": peak, "unit": "TFLOP/s", "frac": achieved / peak, "traffic": None,
                 "peak_source": "MEASURED_PEAKS.json bf16_tflops_sustained" if peaks else "fallback 1.4 PFLOP/s sustained",
                 "launches_timed": len(ev), "avg_launch_ms": attn_ms / max(len(ev), 1),
@@ -231,7 +232,7 @@ def run_b200(a):
         line = {
             "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": a.steps, "warmup": max(a.warmup, 3),
             "ms_per_step": ms / a.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
-            "dtype": "bf16 attention operands / tf32x3 assignment / f32 elsewhere", "data": "synthetic",
+            "dtype": "bf16 attention operands, 3-term split-bf16 linears, tf32x3 assignment, f32 accumulate / softmax / LayerNorm", "data": "synthetic",
             "config": {"workload": workload_name(a), "pairs_per_gpu": a.batch, "keypoints": a.kpts,
                        "l2": "inputs+activations per step (>4 GB) exceed the 126 MB L2; no flush needed",
                        "parallelism": f"pairs sharded over {world} GPU(s), no data-path collective"},

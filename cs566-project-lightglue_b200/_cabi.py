@@ -341,8 +341,11 @@ def linear_qkv_cross(a, w, bias, B: int, tp0: int, tp1: int, bufs, H: int = 4):
     _count(1)
 
 
-def attention_tiles(q_tiles, k_tiles, v_tiles, out_tiles, rt_base: int, nq, nk, q_len=None, k_len=None, scale=0.125):
-    """Context written as split tiles (K atom = head) into out_tiles starting at row tile rt_base."""
+def attention_tiles(q_tiles, k_tiles, v_tiles, out_tiles, rt_base: int, nq, nk, q_len=None, k_len=None, scale=0.125,
+                    cross=False):
+    """Context written as split tiles (K atom = head) into out_tiles starting at row tile rt_base.
+    cross: one of the two directions of CrossBlock; its ALGORITHMIC flops count the shared similarity once
+    (6*d*M*N per layer for both directions), although this launch issues its own QK^T."""
     B, H = q_tiles.shape[:2]
     if ATTN_EVENTS is not None:
         e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
@@ -352,5 +355,5 @@ def attention_tiles(q_tiles, k_tiles, v_tiles, out_tiles, rt_base: int, nq, nk, 
                                     k_tiles.shape[2], float(scale), _stream()), "lg_attention_tiles")
     if ATTN_EVENTS is not None:
         e1.record()
-        ATTN_EVENTS.append((e0, e1, 4.0 * 64 * nq * nk * B * H))
+        ATTN_EVENTS.append((e0, e1, (3.0 if cross else 4.0) * 64 * nq * nk * B * H))
     _count(1)

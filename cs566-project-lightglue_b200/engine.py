@@ -132,8 +132,8 @@ class TileEngine:
         self._ffn(blk_s)
         # CrossBlock (lightglue.py:270-272): shared to_qk projection, both directions
         C.linear_qkv_cross(self.x, blk_c["wqkv"], blk_c["bqkv"], B, self.tp0, self.tp1, ((q0, v0), (q1, v1)), self.H)
-        C.attention_tiles(q0, q1, v1, self.ctx, 0, M, N, len0, len1, scale)
-        C.attention_tiles(q1, q0, v0, self.ctx, self.rt0, N, M, len1, len0, scale)
+        C.attention_tiles(q0, q1, v1, self.ctx, 0, M, N, len0, len1, scale, cross=True)
+        C.attention_tiles(q1, q0, v0, self.ctx, self.rt0, N, M, len1, len0, scale, cross=True)
         self._ffn(blk_c)
 
     # ------------------------------------------------------------------ read-out
