@@ -22,16 +22,32 @@
 
 namespace lg {
 
-constexpr int kStages = 3;
+constexpr int kStages = 4;
 constexpr int kTileBytes = 16384;
 constexpr int kAttnThreads = 384;  // 2 softmax warpgroups + 1 warpgroup holding the producer and MMA warps
-constexpr uint32_t kColS = 0, kColO = 256;  // TMEM column map: S_t at t*128, O_t at 256 + t*64
+constexpr uint32_t kColS = 0, kColO = 384;  // TMEM column map: 3 rotating S buffers at i*128, O_t at 384 + t*64
 constexpr float kRescaleThreshold = 8.0f;   // log2 units; P stays <= 2^8
 
 __device__ __forceinline__ float ex2_approx(float x) {
+#ifdef LG_NOEXP
+  return x;  // timing experiment only
+#endif
   float y;
   asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
   return y;
+}
+__device__ __forceinline__ void st_shared_v4(uint32_t addr, const uint4& v) {
+  asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(addr), "r"(v.x), "r"(v.y), "r"(v.z), "r"(v.w) : "memory");
+}
+// D[tmem] (+)= A[tmem] * B[smem]^T : A = bf16 rows packed two per 32-bit column (lane = row), issued by ONE thread
+__device__ __forceinline__ void umma_bf16_ts(uint32_t tmem_d, uint32_t tmem_a, uint64_t desc_b, uint32_t idesc,
+                                             uint32_t accumulate) {
+  asm volatile(
+      "{\n\t.reg .pred p;\n\t"
+      "setp.ne.b32 p, %4, 0;\n\t"
+      "tcgen05.mma.cta_group::1.kind::f16 [%0], [%1], %2, %3, p;\n\t}" ::"r"(tmem_d),
+      "r"(tmem_a), "l"(desc_b), "r"(idesc), "r"(accumulate)
+      : "memory");
 }
 template <int N>
 __device__ __forceinline__ void reg_inc() { asm volatile("setmaxnreg.inc.sync.aligned.u32 %0;" ::"n"(N)); }
@@ -42,6 +58,18 @@ __device__ __forceinline__ float fmax3(float a, float b, float c) {
   asm("max.f32 %0, %1, %2, %3;" : "=f"(d) : "f"(a), "f"(b), "f"(c));
   return d;
 }
+
+#ifdef LG_ATTN_TRACE
+__device__ unsigned long long g_trace[8192];
+__device__ __forceinline__ unsigned long long gtime() {
+  unsigned long long t;
+  asm volatile("mov.u64 %0, %globaltimer;" : "=l"(t));
+  return t;
+}
+#define TRACE(slot, idx) do { if (blockIdx.x == 1 && blockIdx.y == 1 && blockIdx.z == 1 && (idx) < 256) g_trace[(slot) * 256 + (idx)] = gtime(); } while (0)
+#else
+#define TRACE(slot, idx) do {} while (0)
+#endif
 
 struct AttnParams {
   const uint8_t* q_tiles;
@@ -60,14 +88,14 @@ struct __align__(8) AttnBarriers {
   uint64_t q_full;
   uint64_t kv_full[kStages];
   uint64_t kv_empty[kStages];
-  uint64_t s_full[2];
+  uint64_t s_full[3];
   uint64_t p_full[2];
   uint64_t pv_done[2];
   uint64_t o_final;
   uint32_t tmem_base;
 };
 
-constexpr int kAttnSmem = 1024 /*align slack*/ + 2 * kTileBytes + kStages * 2 * kTileBytes + 2 * 2 * kTileBytes +
+constexpr int kAttnSmem = 1024 /*align slack*/ + 2 * kTileBytes + kStages * 2 * kTileBytes +
                           static_cast<int>(sizeof(AttnBarriers));
 
 __global__ void __launch_bounds__(kAttnThreads, 1) attention_kernel(const AttnParams p) {
@@ -75,8 +103,7 @@ __global__ void __launch_bounds__(kAttnThreads, 1) attention_kernel(const AttnPa
   uint8_t* base = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
   uint8_t* sQ = base;                               // 2 x 16 KB
   uint8_t* sKV = sQ + 2 * kTileBytes;               // kStages x (K 16 KB | V^T 16 KB)
-  uint8_t* sP = sKV + kStages * 2 * kTileBytes;     // 2 x 32 KB
-  AttnBarriers* bar = reinterpret_cast<AttnBarriers*>(sP + 4 * kTileBytes);
+  AttnBarriers* bar = reinterpret_cast<AttnBarriers*>(sKV + kStages * 2 * kTileBytes);
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int b = blockIdx.z, h = blockIdx.y, qt0 = blockIdx.x * 2;
@@ -107,7 +134,8 @@ __global__ void __launch_bounds__(kAttnThreads, 1) attention_kernel(const AttnPa
   if (threadIdx.x == 0) {
     mbar_init(&bar->q_full, 1);
     for (int s = 0; s < kStages; ++s) { mbar_init(&bar->kv_full[s], 1); mbar_init(&bar->kv_empty[s], 1); }
-    for (int t = 0; t < 2; ++t) { mbar_init(&bar->s_full[t], 1); mbar_init(&bar->p_full[t], 128); mbar_init(&bar->pv_done[t], 1); }
+    for (int t = 0; t < 3; ++t) mbar_init(&bar->s_full[t], 1);
+    for (int t = 0; t < 2; ++t) { mbar_init(&bar->p_full[t], 128); mbar_init(&bar->pv_done[t], 1); }
     mbar_init(&bar->o_final, 1);
     fence_mbar_init();
   }
@@ -139,47 +167,61 @@ __global__ void __launch_bounds__(kAttnThreads, 1) attention_kernel(const AttnPa
     }
   } else if (warp == 9) {
     // ------------------------------------------------------------------ MMA issuer
-    if (lane == 0) {
+    {
+      const bool leader = elect_one();  // all lanes run the loop (uniform operands); one lane issues
       constexpr uint32_t idesc_qk = umma_idesc(kFmtBF16, 128, 128);
       constexpr uint32_t idesc_pv = umma_idesc(kFmtBF16, 128, 64);
-      const uint32_t aQ = smem_u32(sQ), aKV = smem_u32(sKV), aP = smem_u32(sP);
-      auto issue_qk = [&](int t, int s) {
+      const uint32_t aQ = smem_u32(sQ), aKV = smem_u32(sKV);
+      // step n = 2j + t (key block j, query tile t) owns S buffer n % 3: QK(n+3) is queued as soon as the
+      // sweep of step n has drained that buffer, i.e. 1.5 key blocks ahead of the softmax that consumes it.
+      auto issue_qk = [&](int n) {
+        const int t = n & 1, s = (n >> 1) % kStages, sb = n % 3;
         const uint64_t da = umma_desc_kmajor_sw128(aQ + t * kTileBytes);
         const uint64_t db = umma_desc_kmajor_sw128(aKV + s * 2 * kTileBytes);
 #pragma unroll
         for (int kk = 0; kk < 4; ++kk)  // K = 64 = 4 x 16, 32 B per step inside the 128 B swizzle row
-          umma_bf16_ss(tmem + kColS + t * 128, da + 2 * kk, db + 2 * kk, idesc_qk, kk > 0);
-        umma_commit(&bar->s_full[t]);
+          if (leader) umma_bf16_ss(tmem + kColS + sb * 128, da + 2 * kk, db + 2 * kk, idesc_qk, kk > 0);
+        if (leader) umma_commit(&bar->s_full[sb]);
       };
-      auto issue_pv = [&](int t, int s, int j) {
+      auto issue_pv = [&](int n) {
+        // P(n) sits in the first 64 columns of S buffer n % 3 as packed bf16 (A operand from TMEM)
+        const int t = n & 1, j = n >> 1, s = j % kStages;
+        const uint32_t tP = tmem + kColS + (n % 3) * 128;
 #pragma unroll
-        for (int kk = 0; kk < 8; ++kk) {  // K = 128 keys = 2 swizzle atoms x 4 steps
-          const uint32_t offA = (kk >> 2) * kTileBytes + (kk & 3) * 32;
+        for (int kk = 0; kk < 8; ++kk) {  // K = 128 keys = 8 x 16: 8 TMEM columns / 32 B of a V^T row per step
           const uint32_t offB = kTileBytes + (kk >> 2) * (kTileBytes / 2) + (kk & 3) * 32;
-          umma_bf16_ss(tmem + kColO + t * 64, umma_desc_kmajor_sw128(aP + t * 2 * kTileBytes + offA),
-                       umma_desc_kmajor_sw128(aKV + s * 2 * kTileBytes + offB), idesc_pv, (j > 0 || kk > 0));
+          if (leader)
+            umma_bf16_ts(tmem + kColO + t * 64, tP + kk * 8, umma_desc_kmajor_sw128(aKV + s * 2 * kTileBytes + offB),
+                         idesc_pv, (j > 0 || kk > 0));
         }
       };
+      const int steps = 2 * nkt;
       mbar_wait(&bar->q_full, 0);
       mbar_wait(&bar->kv_full[0], 0);
       tc_fence_after();
-      issue_qk(0, 0);
-      issue_qk(1, 0);
-      for (int j = 0; j < nkt; ++j) {
-        const int s = j % kStages, sn = (j + 1) % kStages;
-        for (int t = 0; t < 2; ++t) {
-          mbar_wait(&bar->p_full[t], j & 1);  // P_t(j) staged AND S_t(j) drained
-          tc_fence_after();
-          if (j + 1 < nkt) {
-            if (t == 0) { mbar_wait(&bar->kv_full[sn], ((j + 1) / kStages) & 1); tc_fence_after(); }
-            issue_qk(t, sn);                  // S_t(j+1) first: it is what the softmax warpgroup waits for
+      issue_qk(0);
+      issue_qk(1);
+      if (steps > 2) { mbar_wait(&bar->kv_full[1], 0); tc_fence_after(); issue_qk(2); }
+      for (int n = 0; n < steps; ++n) {
+        const int t = n & 1, j = n >> 1, s = j % kStages;
+        mbar_wait(&bar->p_full[t], j & 1);  // P_t(j) staged AND its S buffer drained
+        tc_fence_after();
+        if (leader) TRACE(0, n);
+        issue_pv(n);  // QK(n+3) below reuses this S buffer: same-thread MMAs execute in order
+        if (leader) umma_commit(&bar->pv_done[t]);
+        if (leader && t == 1) umma_commit(&bar->kv_empty[s]);  // K_j and V_j are dead once PV1_j retires
+        const int n3 = n + 3;
+        if (n3 < steps) {
+          if ((n3 & 1) == 0) {  // first use of key block n3/2
+            const int j3 = n3 >> 1;
+            mbar_wait(&bar->kv_full[j3 % kStages], (j3 / kStages) & 1);
+            tc_fence_after();
           }
-          issue_pv(t, s, j);
-          umma_commit(&bar->pv_done[t]);
-          if (t == 1) umma_commit(&bar->kv_empty[s]);  // K_j and V_j are dead once PV1_j retires
+          issue_qk(n3);
         }
+        if (leader) TRACE(1, n);
       }
-      umma_commit(&bar->o_final);
+      if (leader) umma_commit(&bar->o_final);
     }
   }
   } else {
@@ -188,19 +230,23 @@ __global__ void __launch_bounds__(kAttnThreads, 1) attention_kernel(const AttnPa
     const int t = warp >> 2;                       // query tile of this warpgroup
     const int r = (warp & 3) * 32 + lane;          // row == TMEM lane
     const uint32_t lane_addr = static_cast<uint32_t>((warp & 3) * 32) << 16;
-    const uint32_t tS = tmem + lane_addr + kColS + t * 128;
+    const uint32_t tS0 = tmem + lane_addr + kColS;
     const uint32_t tO = tmem + lane_addr + kColO + t * 64;
-    uint8_t* myP = sP + t * 2 * kTileBytes;
     const float c = p.scale_log2;
     float m_used = -INFINITY, l = 0.f;
     uint32_t va[32], vb[32];
+    uint32_t pk0[32], pk1[32];  // P of the block as packed bf16 pairs: 64 TMEM columns
     const float2 c2 = make_float2(c, c);
 
     for (int j = 0; j < nkt; ++j) {
       const int rem = k_len - j * kTile;           // valid keys in this block (>= 1)
       const bool partial = rem < kTile;
-      mbar_wait(&bar->s_full[t], j & 1);
+      const int n = 2 * j + t;
+      const uint32_t tS = tS0 + (n % 3) * 128;
+      if (lane == 0 && (warp & 3) == 0) TRACE(2 + t * 3, j);
+      mbar_wait(&bar->s_full[n % 3], (n / 3) & 1);
       tc_fence_after();
+      if (lane == 0 && (warp & 3) == 0) TRACE(3 + t * 3, j);
       if (j == 0) {
         // first block: the reference max is not known yet -> one max-only sweep
         float mx = -INFINITY;
@@ -256,8 +302,9 @@ __global__ void __launch_bounds__(kAttnThreads, 1) attention_kernel(const AttnPa
             uint4 o;
             o.x = pack_bf16x2(e[0], e[1]); o.y = pack_bf16x2(e[2], e[3]);
             o.z = pack_bf16x2(e[4], e[5]); o.w = pack_bf16x2(e[6], e[7]);
-            const int g = cb * 4 + q;  // 16 B chunk index along the 128 keys
-            *reinterpret_cast<uint4*>(myP + (g >> 3) * kTileBytes + sw128_offset(r, g & 7)) = o;
+            uint32_t(&pk)[32] = cb < 2 ? pk0 : pk1;  // cb, q are compile-time after unrolling
+            pk[(cb & 1) * 16 + q * 4] = o.x; pk[(cb & 1) * 16 + q * 4 + 1] = o.y;
+            pk[(cb & 1) * 16 + q * 4 + 2] = o.z; pk[(cb & 1) * 16 + q * 4 + 3] = o.w;
           }
         };
         // TMEM loads run one 32-column chunk ahead of the arithmetic
@@ -282,7 +329,9 @@ __global__ void __launch_bounds__(kAttnThreads, 1) attention_kernel(const AttnPa
         if (need) { alpha = ex2_approx((m_used - mx) * c); m_used = mx; }
         l *= alpha;
         if (j > 0) {
-          mbar_wait(&bar->pv_done[t], (j - 1) & 1);  // O_t quiescent: PV_t(j-1) has retired
+          // O_t must be quiescent: PV_t(j-1) retired.  The barrier is at most one phase ahead of (j-1), so a
+          // parity wait is valid although earlier phases were never waited for.
+          mbar_wait(&bar->pv_done[t], (j - 1) & 1);
           tc_fence_after();
 #pragma unroll
           for (int cb = 0; cb < 2; ++cb) {
@@ -296,9 +345,14 @@ __global__ void __launch_bounds__(kAttnThreads, 1) attention_kernel(const AttnPa
         }
       }
       l += tile_sum;
-      fence_proxy_async_smem();
+      // P overwrites the first 64 columns of its own S buffer (every S value has been consumed); the PV MMA reads
+      // it from TMEM as the A operand, then QK(n+3) recycles the buffer.
+      tmem_st32(tS, pk0);
+      tmem_st32(tS + 32, pk1);
+      tmem_wait_st();
       tc_fence_before();
       mbar_arrive(&bar->p_full[t]);
+      if (lane == 0 && (warp & 3) == 0) TRACE(4 + t * 3, j);
     }
     // epilogue: O / l -> fp32 rows of the (B, nq, H*64) context tensor
     mbar_wait(&bar->o_final, 0);
@@ -384,3 +438,9 @@ extern "C" int lg_attention_tiles(const void* q_tiles, const void* k_tiles, cons
   return launch_attention(q_tiles, k_tiles, v_tiles, nullptr, out_tiles, out_rt_base, q_len, k_len, B, H, nq, nk,
                           tq_pad, tk_pad, softmax_scale, stream);
 }
+
+#ifdef LG_ATTN_TRACE
+extern "C" int lg_debug_attn_trace(unsigned long long* host_out, int n) {
+  return static_cast<int>(cudaMemcpyFromSymbol(host_out, lg::g_trace, sizeof(unsigned long long) * n));
+}
+#endif

@@ -119,6 +119,19 @@ __device__ __forceinline__ void tmem_st32(uint32_t taddr, const uint32_t (&r)[32
 __device__ __forceinline__ void tmem_wait_ld() { asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory"); }
 __device__ __forceinline__ void tmem_wait_st() { asm volatile("tcgen05.wait::st.sync.aligned;" ::: "memory"); }
 
+// One lane of a converged warp (the same lane every time).  Code that computes MMA operands on ALL lanes and
+// only predicates the tcgen05 instruction itself lets the compiler keep descriptors in uniform registers
+// (no per-MMA R2UR chain: measured 55 ns -> per MMA issue with `if (lane == 0)` around the whole loop).
+__device__ __forceinline__ bool elect_one() {
+  uint32_t pred;
+  asm volatile(
+      "{\n\t.reg .pred p;\n\t"
+      "elect.sync _|p, 0xffffffff;\n\t"
+      "selp.u32 %0, 1, 0, p;\n\t}"
+      : "=r"(pred));
+  return pred != 0;
+}
+
 // ----------------------------------------------------------------------------- UMMA descriptors
 // Shared-memory matrix descriptor, K-major operand, SWIZZLE_128B, tile base 1024 B aligned:
 //   rows are 128 B apart, 8-row groups 1024 B apart (SBO), LBO unused for swizzled K-major (1).
