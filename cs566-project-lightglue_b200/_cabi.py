@@ -11,7 +11,7 @@ import subprocess
 import torch
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, "liblg_b200.so")
+LIB_PATH = os.environ.get("LG_B200_LIB") or os.path.join(_HERE, "liblg_b200.so")  # env override: kernel experiments
 TILE = 128
 TILE_BYTES = 16384
 

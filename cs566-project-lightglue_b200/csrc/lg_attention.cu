@@ -34,6 +34,10 @@ constexpr uint32_t kColS = 0, kColO = 384;  // TMEM column map: 3 rotating S buf
 #ifndef LG_SUMLIMIT
 #define LG_SUMLIMIT 256.0f
 #endif
+#ifndef LG_POLYEXP
+#define LG_POLYEXP 1  // 0: none, 1: 25 %, 2: 37.5 %, 3: 50 %, 4: 75 % of the exponentials on the FMA pipe
+#endif
+constexpr bool kPolyExp = LG_POLYEXP != 0;
 constexpr float kSumLimit = LG_SUMLIMIT;        // a block row sum below this bounds every P of the block by 2^8
 
 __device__ __forceinline__ float ex2_approx(float x) {
@@ -46,6 +50,27 @@ __device__ __forceinline__ float fmax3(float a, float b, float c) {
   asm("max.f32 %0, %1, %2, %3;" : "=f"(d) : "f"(a), "f"(b), "f"(c));
   return d;
 }
+// exp2 of two logits on the FMA / ALU pipes (MUFU.EX2 is the scarce unit at dh = 64: 16 lanes/clk/SM against
+// 8192 MMA flop/clk/SM).  x = s*c - m*c is mapped to y = sat(x/252 + 1/2), which also clamps x to [-126, 126]
+// (exponent field stays in 1..253; 2^126 still trips the row-sum overflow check, masked -inf gives 2^-126 ~ 0);
+// n = round(x) by the magic-number add, 2^frac by a degree-3 minimax polynomial (7.5e-5 relative, P is rounded
+// to bf16 = 3.9e-3), exponent inserted with an integer shift-add.
+__device__ __forceinline__ float2 exp2_poly2(float sa, float sb, float cs, float bs) {
+  constexpr float kMagic126 = 12582912.f - 126.f;  // 1.5 * 2^23 - 126
+  float ya, yb;
+  asm("fma.rn.sat.f32 %0, %1, %2, %3;" : "=f"(ya) : "f"(sa), "f"(cs), "f"(bs));
+  asm("fma.rn.sat.f32 %0, %1, %2, %3;" : "=f"(yb) : "f"(sb), "f"(cs), "f"(bs));
+  const float2 y = make_float2(ya, yb), k252 = make_float2(252.f, 252.f), km = make_float2(kMagic126, kMagic126);
+  const float2 rr = __ffma2_rn(y, k252, km);                              // magic + n
+  const float2 kk = __fadd2_rn(km, make_float2(-rr.x, -rr.y));            // -126 - n (exact)
+  const float2 fr = __ffma2_rn(y, k252, kk);                              // x - n in [-0.5, 0.5]
+  float2 pp = __ffma2_rn(make_float2(0.0551716685f, 0.0551716685f), fr, make_float2(0.2426111251f, 0.2426111251f));
+  pp = __ffma2_rn(pp, fr, make_float2(0.6932609677f, 0.6932609677f));
+  pp = __ffma2_rn(pp, fr, make_float2(0.9999280572f, 0.9999280572f));
+  return make_float2(__int_as_float((__float_as_int(rr.x) << 23) + __float_as_int(pp.x)),
+                     __int_as_float((__float_as_int(rr.y) << 23) + __float_as_int(pp.y)));
+}
+
 // D[tmem] (+)= A[tmem] * B[smem]^T : A = bf16 rows packed two per 32-bit column (lane = row)
 __device__ __forceinline__ void umma_bf16_ts(uint32_t tmem_d, uint32_t tmem_a, uint64_t desc_b, uint32_t idesc,
                                              uint32_t accumulate) {
@@ -321,6 +346,7 @@ __global__ void __launch_bounds__(kAttnThreads, 1) attention_kernel(const AttnPa
           }
           const float ms = m_used * c;
           const float2 nms2 = make_float2(-ms, -ms);
+          const float cs252 = c * (1.f / 252.f), bs252 = fmaf(-ms, 1.f / 252.f, 0.5f);
           float2 s0 = make_float2(0.f, 0.f), s1 = make_float2(0.f, 0.f);
           auto sweep = [&](uint32_t(&v)[32], const int cb) {
             if (partial) {
@@ -332,15 +358,20 @@ __global__ void __launch_bounds__(kAttnThreads, 1) attention_kernel(const AttnPa
             for (int q = 0; q < 4; ++q) {
               float e[8];
 #pragma unroll
-              for (int i = 0; i < 8; i += 4) {
-                const float2 t0 = __ffma2_rn(make_float2(__uint_as_float(v[8 * q + i]), __uint_as_float(v[8 * q + i + 1])),
-                                             c2, nms2);
-                const float2 t1 = __ffma2_rn(
-                    make_float2(__uint_as_float(v[8 * q + i + 2]), __uint_as_float(v[8 * q + i + 3])), c2, nms2);
-                e[i] = ex2_approx(t0.x); e[i + 1] = ex2_approx(t0.y);
-                e[i + 2] = ex2_approx(t1.x); e[i + 3] = ex2_approx(t1.y);
-                s0 = __fadd2_rn(s0, make_float2(e[i], e[i + 1]));
-                s1 = __fadd2_rn(s1, make_float2(e[i + 2], e[i + 3]));
+              for (int pi = 0; pi < 4; ++pi) {  // pairs of the 8-column group
+                const float xa = __uint_as_float(v[8 * q + 2 * pi]), xb = __uint_as_float(v[8 * q + 2 * pi + 1]);
+                // 6 of every 16 pairs take the polynomial path: balances the MUFU pipe against the issue slots
+                const bool poly = LG_POLYEXP == 1 ? (pi == 3) : LG_POLYEXP == 2 ? (pi == 3 || ((q & 1) && pi == 1))
+                                  : LG_POLYEXP == 3 ? (pi & 1) : LG_POLYEXP == 4 ? (pi != 0) : false;
+                float2 ee;
+                if (poly) {
+                  ee = exp2_poly2(xa, xb, cs252, bs252);
+                } else {
+                  const float2 tt = __ffma2_rn(make_float2(xa, xb), c2, nms2);
+                  ee = make_float2(ex2_approx(tt.x), ex2_approx(tt.y));
+                }
+                e[2 * pi] = ee.x; e[2 * pi + 1] = ee.y;
+                if (pi & 1) s1 = __fadd2_rn(s1, ee); else s0 = __fadd2_rn(s0, ee);
               }
               uint32_t(&pk)[32] = cb < 2 ? pk0 : pk1;  // cb, q are compile-time after unrolling
               pk[(cb & 1) * 16 + q * 4] = pack_bf16x2(e[0], e[1]);
