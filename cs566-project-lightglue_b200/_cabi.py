@@ -37,8 +37,8 @@ SIGNATURES = {
     "lg_tiles_to_rows": (_I, [_P, _P, _I, _I, _I, _I, _P]),
     "lg_rotary_tiles": (_I, [_P, _P, _P, _I, _I, _I, _P]),
     "lg_ln_gelu_tiles": (_I, [_P, _P, _P, _F, _P, _I, _P]),
-    "lg_linear_split": (_I, [_P, _I, _P, _I, _P, _P, _P, _P, _I, _I, _P]),
-    "lg_linear_f32": (_I, [_P, _I, _P, _I, _P, _P, _P, _L, _I, _I, _P]),
+    "lg_linear_split": (_I, [_P, _I, _P, _I, _I, _P, _P, _P, _P, _I, _I, _P]),
+    "lg_linear_f32": (_I, [_P, _I, _P, _I, _I, _P, _P, _P, _L, _I, _I, _P]),
     "lg_linear_qkv_self": (_I, [_P, _P, _P, _P, _P, _P, _P, _P, _P, _P, _I, _I, _I, _I, _P]),
     "lg_linear_qkv_cross": (_I, [_P, _P, _P, _P, _P, _P, _P, _I, _I, _I, _I, _P]),
     "lg_attention_tiles": (_I, [_P, _P, _P, _P, _I, _P, _P, _I, _I, _I, _I, _I, _I, _F, _P]),
@@ -248,6 +248,11 @@ def prune_gather(desc, cos, sin, ind, keep_idx, counts, prune):
 SPLIT_ATOM = 32768
 
 
+def alloc_bf16_tiles(row_tiles: int, k: int, device):
+    """Plain bf16 activation tiles [row_tiles][k/64][16 KB] (hi-only GEMM operand)."""
+    return torch.empty(row_tiles, k // 64, TILE_BYTES, device=device, dtype=torch.uint8)
+
+
 def alloc_split(row_tiles: int, k: int, device):
     """Split-tile activation buffer [row_tiles][k/64][hi 16 KB | lo 16 KB]."""
     return torch.empty(row_tiles, k // 64, SPLIT_ATOM, device=device, dtype=torch.uint8)
@@ -300,24 +305,24 @@ def ln_gelu_tiles(h, gamma, beta, eps: float, out=None):
     return out
 
 
-def linear_split(a0, w, bias, n_out: int, a1=None, resid=None, out=None):
+def linear_split(a0, w, bias, n_out: int, a1=None, resid=None, out=None, a1_hi_only=False):
     """[a0 | a1] . w^T + bias (+ resid) -> split tiles (row_tiles, n_out/64, 32 KB)."""
     rt = a0.shape[0]
     if out is None:
         out = alloc_split(rt, n_out, a0.device)
-    _check(lib().lg_linear_split(_ptr(a0), a0.shape[1], _ptr(a1), 0 if a1 is None else a1.shape[1], _ptr(w),
+    _check(lib().lg_linear_split(_ptr(a0), a0.shape[1], _ptr(a1), 0 if a1 is None else a1.shape[1], int(a1_hi_only), _ptr(w),
                                  _ptr(_f32c(bias, "bias")), _ptr(resid), _ptr(out), rt, n_out, _stream()),
            "lg_linear_split")
     _count(1)
     return out
 
 
-def linear_f32(a0, w, bias, n_out: int, a1=None, out=None):
+def linear_f32(a0, w, bias, n_out: int, a1=None, out=None, a1_hi_only=False):
     """[a0 | a1] . w^T + bias -> f32 rows (row_tiles*128, n_out)."""
     rt = a0.shape[0]
     if out is None:
         out = torch.empty(rt * TILE, n_out, device=a0.device, dtype=torch.float32)
-    _check(lib().lg_linear_f32(_ptr(a0), a0.shape[1], _ptr(a1), 0 if a1 is None else a1.shape[1], _ptr(w),
+    _check(lib().lg_linear_f32(_ptr(a0), a0.shape[1], _ptr(a1), 0 if a1 is None else a1.shape[1], int(a1_hi_only), _ptr(w),
                                _ptr(_f32c(bias, "bias")), _ptr(out), out.stride(0), rt, n_out, _stream()),
            "lg_linear_f32")
     _count(1)

@@ -19,8 +19,8 @@
 //   * warps 0-3 / 4-7 : softmax warpgroups, thread == row of query tile t.  One sweep per key block:
 //     P = exp2(S*c - m*c) against the running reference max m of the row (exact for the first block),
 //     FFMA2 / MUFU.EX2 / FADD2, TMEM loads one 32-column chunk ahead.  Overflow safety without a max
-//     pass: the block's row sum bounds its largest P; only if a row sum reaches 2^8 is the block max
-//     computed, O and l rescaled and the sweep repeated (rare after the first blocks).
+//     pass: the block's row sum bounds its largest P; only if a row sum reaches 2^60 is the block max
+//     computed, O and l rescaled and the sweep repeated (rare: a logit 2^60 above the row's reference).
 //     Epilogue O / l -> split bf16 tiles (or fp32 rows) overlaps the next item's first MMAs.
 #include "lg_common.cuh"
 #include "lg_b200.h"
@@ -32,13 +32,14 @@ constexpr int kTileBytes = 16384;
 constexpr int kAttnThreads = 384;  // 2 softmax warpgroups + 1 warpgroup holding the producer and MMA warps
 constexpr uint32_t kColS = 0, kColO = 384;  // TMEM column map: 3 rotating S buffers at i*128, O_t at 384 + t*64
 #ifndef LG_SUMLIMIT
-#define LG_SUMLIMIT 256.0f
+#define LG_SUMLIMIT 1.152921504606846976e18f  // 2^60
 #endif
 #ifndef LG_POLYEXP
 #define LG_POLYEXP 1  // 0: none, 1: 25 %, 2: 37.5 %, 3: 50 %, 4: 75 % of the exponentials on the FMA pipe
 #endif
 constexpr bool kPolyExp = LG_POLYEXP != 0;
-constexpr float kSumLimit = LG_SUMLIMIT;        // a block row sum below this bounds every P of the block by 2^8
+constexpr float kSumLimit = LG_SUMLIMIT;  // a block row sum below this bounds every P of the block: bf16 / fp32 hold
+                                          // 2^127, so P, the row sums and O stay finite; precision is scale free
 
 __device__ __forceinline__ float ex2_approx(float x) {
   float y;
@@ -81,10 +82,25 @@ __device__ __forceinline__ void umma_bf16_ts(uint32_t tmem_d, uint32_t tmem_a, u
       "r"(tmem_a), "l"(desc_b), "r"(idesc), "r"(accumulate)
       : "memory");
 }
+__device__ __forceinline__ void st_shared_v4(uint32_t addr, const uint4& v) {
+  asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(addr), "r"(v.x), "r"(v.y), "r"(v.z), "r"(v.w) : "memory");
+}
 template <int N>
 __device__ __forceinline__ void reg_inc() { asm volatile("setmaxnreg.inc.sync.aligned.u32 %0;" ::"n"(N)); }
 template <int N>
 __device__ __forceinline__ void reg_dec() { asm volatile("setmaxnreg.dec.sync.aligned.u32 %0;" ::"n"(N)); }
+
+#ifdef LG_ATTN_TRACE
+__device__ unsigned long long g_trace[8192];
+__device__ __forceinline__ unsigned long long gtime() {
+  unsigned long long t;
+  asm volatile("mov.u64 %0, %globaltimer;" : "=l"(t));
+  return t;
+}
+#define TRACE(slot, idx) do { if (blockIdx.x == 5 && (idx) < 256) g_trace[(slot) * 256 + (idx)] = gtime(); } while (0)
+#else
+#define TRACE(slot, idx) do {} while (0)
+#endif
 
 struct AttnParams {
   const uint8_t* q_tiles;
@@ -112,7 +128,8 @@ struct __align__(8) AttnBarriers {
   uint32_t tmem_base;
 };
 
-constexpr int kAttnSmem = 1024 /*align slack*/ + 2 * 2 * kTileBytes + kStages * 2 * kTileBytes +
+constexpr int kOutStage = 8 * 4096;  // per softmax warp: 32 rows x 128 B of the context tile, for bulk stores
+constexpr int kAttnSmem = 1024 /*align slack*/ + 2 * 2 * kTileBytes + kStages * 2 * kTileBytes + kOutStage +
                           static_cast<int>(sizeof(AttnBarriers));
 
 // One work item, decoded identically by every role.
@@ -139,7 +156,8 @@ __global__ void __launch_bounds__(kAttnThreads, 1) attention_kernel(const AttnPa
   uint8_t* base = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
   uint8_t* sQ = base;                               // 2 buffers x (2 x 16 KB)
   uint8_t* sKV = sQ + 4 * kTileBytes;               // kStages x (K 16 KB | V^T 16 KB)
-  AttnBarriers* bar = reinterpret_cast<AttnBarriers*>(sKV + kStages * 2 * kTileBytes);
+  uint8_t* sOut = sKV + kStages * 2 * kTileBytes;   // 8 x 4 KB epilogue staging
+  AttnBarriers* bar = reinterpret_cast<AttnBarriers*>(sOut + kOutStage);
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int row_stride = p.H * kHeadDim;
@@ -237,6 +255,7 @@ __global__ void __launch_bounds__(kAttnThreads, 1) attention_kernel(const AttnPa
           const int t = n & 1, j = n >> 1;
           const uint32_t kvi = p_kv + j, s = kvi % kStages;
           mbar_wait(&bar->p_full[t], kvi & 1);  // P_t(j) stored in its S buffer
+          if (leader) TRACE(6, G_p);
           if (j == 0 && p_cnt > 0) mbar_wait(&bar->o_free[t], (p_cnt - 1) & 1);  // previous item's O_t was read out
           tc_fence_after();
           // P sits in the first 64 columns of S buffer G % 3 as packed bf16 (A operand from TMEM)
@@ -251,6 +270,7 @@ __global__ void __launch_bounds__(kAttnThreads, 1) attention_kernel(const AttnPa
           if (leader) umma_commit(&bar->pv_done[t]);
           if (leader && t == 1) umma_commit(&bar->kv_empty[s]);  // K_j and V_j are dead once PV1_j retires
           issue_next_qk();  // step G+3 recycles this S buffer: same-thread MMAs execute in order
+          if (leader) TRACE(7, G_p);
         }
         p_kv += it.nkt;
         ++p_cnt;
@@ -300,15 +320,17 @@ __global__ void __launch_bounds__(kAttnThreads, 1) attention_kernel(const AttnPa
         const bool partial = rem < kTile;
         const uint32_t G = 2 * (kv_base + j) + t;    // global step: S buffer G % 3
         const uint32_t tS = tS0 + (G % 3) * 128;
+        if ((threadIdx.x & 127) == 0) TRACE(t * 3, kv_base + j);
         mbar_wait(&bar->s_full[G % 3], (G / 3) & 1);
         tc_fence_after();
+        if ((threadIdx.x & 127) == 0) TRACE(t * 3 + 1, kv_base + j);
 
         float tile_sum = 0.f;
         const bool first = j == 0;
 #pragma unroll 1
         for (int attempt = 0; attempt < 2; ++attempt) {
           if (first || attempt == 1) {
-            // exact block max (first block of a row, or a row sum that reached 2^8): new reference, rescale
+            // exact block max (first block of a row, or a row sum that reached the limit): new reference, rescale
             float mx = -INFINITY;
 #pragma unroll
             for (int cb = 0; cb < 4; ++cb) {
@@ -395,7 +417,7 @@ __global__ void __launch_bounds__(kAttnThreads, 1) attention_kernel(const AttnPa
           sweep(vb, 3);
           tile_sum = (s0.x + s0.y) + (s1.x + s1.y);
           if (first || attempt == 1) break;
-          // every P <= row sum: below 2^8 nothing can have overflowed the bf16 / fp32 ranges
+          // every P <= row sum: below the limit nothing can have overflowed the bf16 / fp32 ranges
           if (!__any_sync(0xffffffffu, !(tile_sum < kSumLimit))) break;
         }
         l += tile_sum;
@@ -409,46 +431,72 @@ __global__ void __launch_bounds__(kAttnThreads, 1) attention_kernel(const AttnPa
         // one block ahead: ONE arrival per block, after all 128 rows are stored (a 128-count barrier could be
         // completed by a mix of arrivals of block j and block j+1).
         asm volatile("bar.sync %0, 128;" ::"r"(1 + t) : "memory");
-        if ((threadIdx.x & 127) == 0) mbar_arrive(&bar->p_full[t]);
+        if ((threadIdx.x & 127) == 0) { mbar_arrive(&bar->p_full[t]); TRACE(t * 3 + 2, kv_base + j); }
       }
 
       // epilogue: O / l.  O_t is copied to registers and released first so the next item's PV can start.
+      if ((threadIdx.x & 127) == 0) TRACE(8 + t * 4, kv_base);
       mbar_wait(&bar->pv_done[t], (kv_base + it.nkt - 1) & 1);
       tc_fence_after();
+      if ((threadIdx.x & 127) == 0) TRACE(9 + t * 4, kv_base);
       tmem_ld32(tO, va);
       tmem_ld32(tO + 32, vb);
       tmem_wait_ld();
       tc_fence_before();
       mbar_arrive(&bar->o_free[t]);
+      if ((threadIdx.x & 127) == 0) TRACE(10 + t * 4, kv_base);
       kv_base += it.nkt;
       const float inv = (row < it.q_len) ? 1.f / l : 0.f;  // padded query rows -> 0
-      auto emit = [&](const uint32_t(&v)[32], const int cb) {
-        if (dt) {
-          // context rows as split bf16 tiles: head h is K atom h of the (rows x 256) matrix
+      if (dt) {
+        // context rows as split bf16 tiles (head h = K atom h of the rows x 256 matrix).  A single bf16 is NOT
+        // enough here: rounding the context costs 1e-2 on log_assignment (P's rounding averages out over the
+        // keys, the context's does not).  The warp's 32 rows are a contiguous 4 KB slice of the 16 KB hi (and
+        // lo) tile image: stage in shared memory, one bulk store each.
+        uint8_t* stg = sOut + warp * 4096;
+        const uint32_t stg_row = smem_u32(stg) + lane * 128;
+        uint32_t lo_w[32];
+        if (lane == 0) bulk_wait_read_all();  // previous item's stores have drained the staging slice
+        __syncwarp();
+        auto split_store = [&](const uint32_t(&v)[32], const int cb) {
 #pragma unroll
           for (int q = 0; q < 4; ++q) {
-            uint32_t hh[4], ll[4];
+            uint32_t hh[4];
 #pragma unroll
             for (int i = 0; i < 4; ++i) {
               const float x0 = __uint_as_float(v[8 * q + 2 * i]) * inv, x1 = __uint_as_float(v[8 * q + 2 * i + 1]) * inv;
               const __nv_bfloat16 h0 = __float2bfloat16_rn(x0), h1 = __float2bfloat16_rn(x1);
               hh[i] = static_cast<uint32_t>(__bfloat16_as_ushort(h0)) | (static_cast<uint32_t>(__bfloat16_as_ushort(h1)) << 16);
-              ll[i] = pack_bf16x2(x0 - __bfloat162float(h0), x1 - __bfloat162float(h1));
+              lo_w[cb * 16 + q * 4 + i] = pack_bf16x2(x0 - __bfloat162float(h0), x1 - __bfloat162float(h1));
             }
-            uint8_t* at = dt + sw128_offset(r, cb * 4 + q);
-            *reinterpret_cast<uint4*>(at) = make_uint4(hh[0], hh[1], hh[2], hh[3]);
-            *reinterpret_cast<uint4*>(at + 16384) = make_uint4(ll[0], ll[1], ll[2], ll[3]);
+            st_shared_v4(stg_row + (((cb * 4 + q) ^ (lane & 7)) << 4), make_uint4(hh[0], hh[1], hh[2], hh[3]));
           }
-        } else if (row < p.nq) {
+        };
+        split_store(va, 0);
+        split_store(vb, 1);
+        fence_proxy_async_smem();
+        __syncwarp();
+        uint8_t* gdst = dt + (warp & 3) * 4096;
+        if (lane == 0) { bulk_s2g(gdst, stg, 4096); bulk_commit(); bulk_wait_read_all(); }
+        __syncwarp();
 #pragma unroll
-          for (int i = 0; i < 8; ++i)
-            drow[cb * 8 + i] = make_float4(__uint_as_float(v[4 * i]) * inv, __uint_as_float(v[4 * i + 1]) * inv,
-                                           __uint_as_float(v[4 * i + 2]) * inv, __uint_as_float(v[4 * i + 3]) * inv);
+        for (int ch = 0; ch < 8; ++ch)
+          st_shared_v4(stg_row + ((ch ^ (lane & 7)) << 4),
+                       make_uint4(lo_w[4 * ch], lo_w[4 * ch + 1], lo_w[4 * ch + 2], lo_w[4 * ch + 3]));
+        fence_proxy_async_smem();
+        __syncwarp();
+        if (lane == 0) { bulk_s2g(gdst + 16384, stg, 4096); bulk_commit(); }
+        if ((threadIdx.x & 127) == 0) TRACE(11 + t * 4, kv_base - it.nkt);
+      } else if (row < p.nq) {
+#pragma unroll
+        for (int i = 0; i < 8; ++i) {
+          drow[i] = make_float4(__uint_as_float(va[4 * i]) * inv, __uint_as_float(va[4 * i + 1]) * inv,
+                                __uint_as_float(va[4 * i + 2]) * inv, __uint_as_float(va[4 * i + 3]) * inv);
+          drow[8 + i] = make_float4(__uint_as_float(vb[4 * i]) * inv, __uint_as_float(vb[4 * i + 1]) * inv,
+                                    __uint_as_float(vb[4 * i + 2]) * inv, __uint_as_float(vb[4 * i + 3]) * inv);
         }
-      };
-      emit(va, 0);
-      emit(vb, 1);
+      }
     }
+    if (lane == 0) bulk_wait_all();  // outstanding context stores
   }
   tc_fence_before();
   __syncthreads();
@@ -497,3 +545,9 @@ extern "C" int lg_attention_tiles(const void* q_tiles, const void* k_tiles, cons
   return launch_attention(q_tiles, k_tiles, v_tiles, nullptr, out_tiles, out_rt_base, q_len, k_len, B, H, nq, nk,
                           tq_pad, tk_pad, softmax_scale, stream);
 }
+
+#ifdef LG_ATTN_TRACE
+extern "C" int lg_debug_attn_trace(unsigned long long* host_out, int n) {
+  return static_cast<int>(cudaMemcpyFromSymbol(host_out, lg::g_trace, sizeof(unsigned long long) * n));
+}
+#endif

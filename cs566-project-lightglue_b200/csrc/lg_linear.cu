@@ -41,6 +41,7 @@ struct LinearParams {
   const uint8_t* a0;       // A source 0: [row_tiles][a0_atoms][32 KB]
   const uint8_t* a1;       // A source 1 (concatenated along K after a0), may be null
   int a0_atoms, a1_atoms;
+  int a1_hi_only;          // a1 holds plain bf16 tiles [row_tiles][a1_atoms][16 KB] (no lo half): 2-term product
   const uint8_t* w;        // [n_tiles][k_atoms][hi | lo][Nt*128]
   const float* bias;       // [n_tiles * Nt] (same row order as w)
   int row_tiles, n_tiles;
@@ -141,18 +142,22 @@ __global__ void __launch_bounds__(kLinThreads, 1) linear_kernel(const LinearPara
         for (int ka = 0; ka < k_atoms; ++ka, ++it) {
           const int s = it % kLinStages;
           if (it >= kLinStages) mbar_wait(&bar->empty[s], ((it / kLinStages) - 1) & 1);
+          const bool hi_only = ka >= p.a0_atoms && p.a1_hi_only;
           const uint8_t* ga = ka < p.a0_atoms
                                   ? p.a0 + (static_cast<size_t>(rt) * p.a0_atoms + ka) * kSplitAtom
-                                  : p.a1 + (static_cast<size_t>(rt) * p.a1_atoms + (ka - p.a0_atoms)) * kSplitAtom;
-          mbar_arrive_expect_tx(&bar->full[s], kStage);
-          bulk_g2s(ring + s * kStage, ga, kSplitAtom, &bar->full[s]);
+                                  : p.a1 + (static_cast<size_t>(rt) * p.a1_atoms + (ka - p.a0_atoms)) *
+                                               (hi_only ? kHalfAtom : kSplitAtom);
+          const uint32_t a_bytes = hi_only ? kHalfAtom : kSplitAtom;
+          mbar_arrive_expect_tx(&bar->full[s], a_bytes + kWAtom);
+          bulk_g2s(ring + s * kStage, ga, a_bytes, &bar->full[s]);
           bulk_g2s(ring + s * kStage + kSplitAtom, gw + static_cast<size_t>(ka) * kWAtom, kWAtom, &bar->full[s]);
         }
       }
     }
   } else if (warp == 5) {
     // ------------------------------------------------------------------ MMA issuer
-    if (lane == 0) {
+    {
+      const bool leader = elect_one();  // all lanes run the loop (operands stay uniform); one lane issues
       constexpr uint32_t idesc = umma_idesc(kFmtBF16, 128, kNt);
       const uint32_t ring_a = smem_u32(ring);
       uint32_t it = 0;
@@ -165,19 +170,20 @@ __global__ void __launch_bounds__(kLinThreads, 1) linear_kernel(const LinearPara
           const int s = it % kLinStages;
           mbar_wait(&bar->full[s], (it / kLinStages) & 1);
           tc_fence_after();
+          const bool hi_only = ka >= p.a0_atoms && p.a1_hi_only;
           const uint32_t a_hi = ring_a + s * kStage, a_lo = a_hi + kHalfAtom;
           const uint32_t w_hi = a_hi + kSplitAtom, w_lo = w_hi + kNt * 128;
           const uint64_t dah = umma_desc_kmajor_sw128(a_hi), dal = umma_desc_kmajor_sw128(a_lo);
           const uint64_t dwh = umma_desc_kmajor_sw128(w_hi), dwl = umma_desc_kmajor_sw128(w_lo);
 #pragma unroll
           for (int kk = 0; kk < 4; ++kk) {  // 64 bf16 per atom = 4 x K16, 32 B per step
-            umma_bf16_ss(acc, dal + 2 * kk, dwh + 2 * kk, idesc, (ka > 0 || kk > 0));
-            umma_bf16_ss(acc, dah + 2 * kk, dwl + 2 * kk, idesc, 1);
-            umma_bf16_ss(acc, dah + 2 * kk, dwh + 2 * kk, idesc, 1);
+            if (leader && !hi_only) umma_bf16_ss(acc, dal + 2 * kk, dwh + 2 * kk, idesc, (ka > 0 || kk > 0));
+            if (leader) umma_bf16_ss(acc, dah + 2 * kk, dwl + 2 * kk, idesc, hi_only ? (ka > 0 || kk > 0) : 1);
+            if (leader) umma_bf16_ss(acc, dah + 2 * kk, dwh + 2 * kk, idesc, 1);
           }
-          umma_commit(&bar->empty[s]);
+          if (leader) umma_commit(&bar->empty[s]);
         }
-        umma_commit(&bar->acc_full[buf]);
+        if (leader) umma_commit(&bar->acc_full[buf]);
       }
     }
   } else {
@@ -555,27 +561,27 @@ static int check_linear(const void* a0, int a0_atoms, const void* a1, int a1_ato
   return 0;
 }
 
-extern "C" int lg_linear_split(const void* a0, int a0_atoms, const void* a1, int a1_atoms, const void* w,
+extern "C" int lg_linear_split(const void* a0, int a0_atoms, const void* a1, int a1_atoms, int a1_hi_only, const void* w,
                                const float* bias, const void* resid_tiles, void* out_tiles, int row_tiles, int n_out,
                                cudaStream_t stream) {
   if (int e = check_linear(a0, a0_atoms, a1, a1_atoms, w, bias, row_tiles, n_out, 256)) return e;
   if (!out_tiles) return LG_ERR_NULL;
   lg::LinearParams p{};
   p.a0 = static_cast<const uint8_t*>(a0); p.a1 = static_cast<const uint8_t*>(a1);
-  p.a0_atoms = a0_atoms; p.a1_atoms = a1_atoms;
+  p.a0_atoms = a0_atoms; p.a1_atoms = a1_atoms; p.a1_hi_only = a1_hi_only;
   p.w = static_cast<const uint8_t*>(w); p.bias = bias; p.row_tiles = row_tiles; p.n_tiles = n_out / 256;
   p.out_tiles = static_cast<uint8_t*>(out_tiles); p.resid_tiles = static_cast<const uint8_t*>(resid_tiles);
   return lg::launch_linear<256, lg::kEpiSplit>(p, stream);
 }
 
-extern "C" int lg_linear_f32(const void* a0, int a0_atoms, const void* a1, int a1_atoms, const void* w,
+extern "C" int lg_linear_f32(const void* a0, int a0_atoms, const void* a1, int a1_atoms, int a1_hi_only, const void* w,
                              const float* bias, float* out, int64_t ld, int row_tiles, int n_out, cudaStream_t stream) {
   if (int e = check_linear(a0, a0_atoms, a1, a1_atoms, w, bias, row_tiles, n_out, 256)) return e;
   if (!out) return LG_ERR_NULL;
   if (ld < n_out || ld % 4 || !aligned16(out)) return LG_ERR_ALIGN;
   lg::LinearParams p{};
   p.a0 = static_cast<const uint8_t*>(a0); p.a1 = static_cast<const uint8_t*>(a1);
-  p.a0_atoms = a0_atoms; p.a1_atoms = a1_atoms;
+  p.a0_atoms = a0_atoms; p.a1_atoms = a1_atoms; p.a1_hi_only = a1_hi_only;
   p.w = static_cast<const uint8_t*>(w); p.bias = bias; p.row_tiles = row_tiles; p.n_tiles = n_out / 256;
   p.out_f32 = out; p.ld = ld;
   return lg::launch_linear<256, lg::kEpiF32>(p, stream);

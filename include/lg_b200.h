@@ -84,12 +84,14 @@ int lg_ln_gelu_tiles(const float* h, const float* gamma, const float* beta, floa
 
 /* y = [a0 | a1] . w^T + bias as a 3-term split-bf16 tcgen05 GEMM (nn.Linear, lightglue.py:171-176,190,246,310).
  * a0 / a1: split tiles with a0_atoms / a1_atoms K atoms (a1 NULL, 0 = none: torch.cat([x, msg], -1) of
- * lightglue.py:191,247 without the copy); w from lg_pack_weight(nt=256); n_out multiple of 256.
+ * lightglue.py:191,247 without the copy); a1_hi_only != 0: a1 holds plain bf16 tiles [row_tiles][a1_atoms][16 KB]
+ * (x = hi exactly, e.g. an operand that is bf16 by construction) and contributes a 2-term product; w from lg_pack_weight(nt=256);
+ * n_out multiple of 256.
  * lg_linear_split: out (and optional residual, added in fp32: x + ffn(...)) are split tiles
  *   [row_tiles][n_out/64][32 KB].   lg_linear_f32: out f32 rows with pitch ld floats. */
-int lg_linear_split(const void* a0, int a0_atoms, const void* a1, int a1_atoms, const void* w, const float* bias,
+int lg_linear_split(const void* a0, int a0_atoms, const void* a1, int a1_atoms, int a1_hi_only, const void* w, const float* bias,
                     const void* resid_tiles, void* out_tiles, int row_tiles, int n_out, cudaStream_t stream);
-int lg_linear_f32(const void* a0, int a0_atoms, const void* a1, int a1_atoms, const void* w, const float* bias,
+int lg_linear_f32(const void* a0, int a0_atoms, const void* a1, int a1_atoms, int a1_hi_only, const void* w, const float* bias,
                   float* out, int64_t ld, int row_tiles, int n_out, cudaStream_t stream);
 
 /* SelfBlock Wqkv + head split + rotary (lightglue.py:184-188) -> lg_attention operand tiles.  a: split tiles

@@ -17,9 +17,12 @@ lib.lg_debug_attn_trace.argtypes = [ctypes.c_void_p, ctypes.c_int]
 assert lib.lg_debug_attn_trace(buf.ctypes.data, 8192) == 0
 tr = buf.reshape(32, 256).astype(np.int64)
 t0 = tr[tr > 0].min()
-names = ["mma wake", "mma issued", "wg0 pre-wait", "wg0 got S", "wg0 arrived", "wg1 pre-wait", "wg1 got S", "wg1 arrived"]
-for j in range(16):
-    print(f"j={j:2d} " + "  ".join(f"{names[s][:11]}={tr[s, j] - t0:6d}" for s in range(2, 8)))
-print("mma (n, wake, issued):")
-for n in range(32):
-    print(f"  n={n:2d} wake={tr[0, n] - t0:6d} issued={tr[1, n] - t0:6d}")
+names = ["wg0 pre", "wg0 gotS", "wg0 arr", "wg1 pre", "wg1 gotS", "wg1 arr"]
+nb = int((tr[0] > 0).sum())
+for j in range(min(nb, 56)):
+    print(f"blk={j:3d} " + "  ".join(f"{names[s]}={tr[s, j] - t0:6d}" for s in range(6)) +
+          f" | mma wake(t0,t1)={tr[6, 2 * j] - t0:6d},{tr[6, 2 * j + 1] - t0:6d} issued={tr[7, 2 * j] - t0:6d},{tr[7, 2 * j + 1] - t0:6d}")
+
+print("item epilogues (per item: start, pv_done, o_free, stored) wg0 | wg1")
+for i in range(0, nb, 16):
+    print(f"kv_base={i:3d} wg0 " + " ".join(f"{tr[8 + k, i] - t0:6d}" for k in range(4)) + " | wg1 " + " ".join(f"{tr[12 + k, i] - t0:6d}" for k in range(4)))

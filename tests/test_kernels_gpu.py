@@ -183,6 +183,13 @@ def test_attention_large_logits(C):
         assert eb < 3e-2, (e32, eb)
 
 
+def test_attention_huge_logits(C):
+    """logits jumping by > 2^60 between key blocks: exercises the overflow detection + rescale/redo path."""
+    errs = _attn_case(C, 1, 4, 384, 1024, None, None, seed=6, scale_mag=9.0)
+    for e32, eb in errs:
+        assert eb < 3e-2, (e32, eb)
+
+
 def test_attention_varlen(C):
     errs = _attn_case(C, 4, 4, 512, 640, [512, 1, 200, 0], [640, 129, 128, 5], seed=9)
     for e32, eb in errs:

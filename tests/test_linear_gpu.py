@@ -191,3 +191,18 @@ def test_attention_tiles_matches_rows(C):
     C.attention_tiles(qt, kt, vt, out, 3, nq, nk, ql, kl, 0.125)
     got = C.tiles_to_rows(out[3:], B, nq, 256, tq)
     assert ((got - ref).abs() <= ref.abs() * 2.0 ** -16 + 1e-30).all()
+
+
+def test_linear_hi_only_second_source(C):
+    """[a0 | a1] with a1 as plain bf16 tiles (2-term product on those K atoms)."""
+    g = _gen(13)
+    RT = 6
+    x = torch.randn(1, RT * 128, 256, generator=g)
+    ctx = torch.randn(1, RT * 128, 256, generator=g).bfloat16().float()
+    w = (torch.rand(512, 512, generator=g) * 2 - 1) / 22
+    b = torch.randn(512, generator=g)
+    ref = torch.cat([x, ctx], -1)[0].double() @ w.double().t() + b.double()
+    a0 = C.rows_to_tiles(x.cuda(), RT)
+    a1 = C.rows_to_tiles(ctx.cuda(), RT)[:, :, :16384].contiguous()     # hi halves only (lo is exactly zero)
+    got = C.linear_f32(a0, C.pack_weight(w.cuda()), b.cuda(), 512, a1=a1, a1_hi_only=True).cpu().double()
+    assert (got - ref).abs().max() < 4e-5
