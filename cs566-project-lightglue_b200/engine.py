@@ -89,6 +89,11 @@ class TileEngine:
         self.hpre = torch.empty(self.rt * C.TILE, 512, device=device, dtype=torch.float32)
         self.rot = torch.empty(self.rt, C.SPLIT_ATOM, device=device, dtype=torch.uint8)
         self.qkv = [tuple(C.alloc_tiles(B, heads, n, device) for _ in range(3)) for n in (M, N)]
+        # CUDA-graph state of the layer stack (run_layers): static length buffers, the captured graph
+        self.len0 = torch.empty(B, device=device, dtype=torch.int32)
+        self.len1 = torch.empty(B, device=device, dtype=torch.int32)
+        self.graphs = {}
+        self.eager_runs = 0
 
     # ------------------------------------------------------------------ loading
     def load(self, desc0, desc1, cs0, cs1):
@@ -135,6 +140,38 @@ class TileEngine:
         C.attention_tiles(q0, q1, v1, self.ctx, 0, M, N, len0, len1, scale, cross=True)
         C.attention_tiles(q1, q0, v0, self.ctx, self.rt0, N, M, len1, len0, scale, cross=True)
         self._ffn(blk_c)
+
+    def run_layers(self, n_layers: int, len0=None, len1=None, use_graph: bool = True):
+        """All transformer layers.  The 12 x n_layers launches are captured once per engine into a CUDA graph
+        (streams + graphs instead of a tracing compiler) and replayed: the layer stack only touches this
+        engine's own buffers, so the graph is valid for every later batch of the same shape."""
+        if len0 is not None:
+            self.len0.copy_(len0)
+            self.len1.copy_(len1)
+        l0, l1 = (self.len0, self.len1) if len0 is not None else (None, None)
+        if not use_graph or C.ATTN_EVENTS is not None:
+            for i in range(n_layers):
+                self.layer(i, l0, l1)
+            return
+        key = (n_layers, len0 is not None)
+        g = self.graphs.get(key)
+        if g is None:
+            if self.eager_runs == 0:
+                # first use: eager, so every kernel has set its attributes / loaded before any capture
+                self.eager_runs = 1
+                for i in range(n_layers):
+                    self.layer(i, l0, l1)
+                return
+            x_before, n0 = self.x, C.LAUNCHES
+            graph = torch.cuda.CUDAGraph()
+            with torch.cuda.graph(graph):
+                for i in range(n_layers):
+                    self.layer(i, l0, l1)
+            assert self.x is x_before, "an even number of buffer swaps per layer keeps x in place"
+            g = self.graphs[key] = (graph, C.LAUNCHES - n0)
+            C.LAUNCHES = n0  # capture launched nothing; replays account for the kernels below
+        g[0].replay()
+        C._count(g[1])
 
     # ------------------------------------------------------------------ read-out
     def rows(self):

@@ -129,7 +129,7 @@ class LightGlue(nn.Module):
         "weights_from_version": "v0.1_arxiv",
         "loss": {"gamma": 1.0, "fn": "nll", "nll_balancing": 0.5},
         # namespaced additions (existing YAMLs stay valid)
-        "b200": {"precision": "bf16"},
+        "b200": {"precision": "bf16", "cuda_graph": True, "engine_cache": 2},
     }
     required_data_keys = ["keypoints0", "keypoints1", "descriptors0", "descriptors1"]
 
@@ -185,10 +185,22 @@ class LightGlue(nn.Module):
             pk = self._pk = PackedWeights(self)
         return pk
 
-    def _engine(self, B, M, N, device):
+    def _engine(self, B, M, N, device, cached=False):
+        """Activation buffers (+ captured CUDA graph) for one problem shape; the batched path keeps the last few."""
         from .engine import TileEngine
 
-        return TileEngine(self._packed(), B, M, N, device, self.conf.num_heads)
+        pk = self._packed()
+        if not cached:
+            return TileEngine(pk, B, M, N, device, self.conf.num_heads)
+        cache = self.__dict__.setdefault("_engines", {})
+        key = (B, M, N, str(device))
+        eng = cache.pop(key, None)
+        if eng is None or eng.pk is not pk:
+            eng = TileEngine(pk, B, M, N, device, self.conf.num_heads)
+        cache[key] = eng  # most recently used last
+        while len(cache) > max(int(self.conf.b200.engine_cache), 1):
+            cache.pop(next(iter(cache)))
+        return eng
 
     def _assign(self, i, eng, d0, d1, len0, len1):
         """MatchAssignment.forward (lightglue.py:306-315): final_proj on tcgen05, matchability logits, then
@@ -236,25 +248,27 @@ class LightGlue(nn.Module):
         assert desc0.shape[-1] == conf.input_dim and desc1.shape[-1] == conf.input_dim
         len0 = self._lens(data, "num_keypoints0", m, dev)
         len1 = self._lens(data, "num_keypoints1", n, dev)
+        if (len0 is None) != (len1 is None):  # one side given: the other is full length
+            len0 = torch.full((b,), m, device=dev, dtype=torch.int32) if len0 is None else len0
+            len1 = torch.full((b,), n, device=dev, dtype=torch.int32) if len1 is None else len1
         pe = self.posenc
         wc = pe.condition_modulation.weight.reshape(-1)
         cs0 = C.posenc(kpts0.float().contiguous(), self._image_size(data, "view0", kpts0), pe.Wr.weight, wc,
                        pe.condition_modulation.bias, float(m))
         cs1 = C.posenc(kpts1.float().contiguous(), self._image_size(data, "view1", kpts1), pe.Wr.weight, wc,
                        pe.condition_modulation.bias, float(n))
-        eng = self._engine(b, m, n, dev)
-        eng.load(desc0, desc1, cs0, cs1)
-
         do_early_stop = conf.depth_confidence > 0
         do_point_pruning = conf.width_confidence > 0
+        eng = self._engine(b, m, n, dev, cached=not (do_early_stop or do_point_pruning))
+        eng.load(desc0, desc1, cs0, cs1)
+
         if do_early_stop or do_point_pruning:
             from .adaptive import forward_adaptive
 
             return forward_adaptive(self, eng, cs0, cs1)
 
         L = conf.n_layers
-        for i in range(L):
-            eng.layer(i, len0, len1)
+        eng.run_layers(L, len0, len1, use_graph=bool(conf.b200.cuda_graph))
         desc0, desc1 = eng.rows()
         scores = self._assign(L - 1, eng, desc0, desc1, len0, len1)
         m0, m1, ms0, ms1 = C.filter_matches(scores, conf.filter_threshold, len0, len1)

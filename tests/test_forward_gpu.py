@@ -124,3 +124,23 @@ def test_adaptive_forward_vs_golden(name):
     else:  # a marginal keep decision flipped under bf16 attention: sizes must still be within 1 %
         assert abs(la.shape[1] - meta["la_shape"][1]) <= 0.01 * meta["la_shape"][1] + 1
         assert abs(la.shape[2] - meta["la_shape"][2]) <= 0.01 * meta["la_shape"][2] + 1
+
+
+def test_cuda_graph_replay_matches_eager():
+    """Same shape called repeatedly: eager first call, graph capture on the second, replay afterwards.
+    Every call must give bit-identical results to a graph-free model on the same inputs."""
+    conf = {"filter_threshold": 0.1}
+    sd = W.make_state_dict(conf, seed=0)
+    eager = _model({**conf, "b200": {"cuda_graph": False}}, sd)
+    graphed = _model(conf, sd)
+    for seed in (3, 4, 5, 3):
+        data = _cuda(W.make_inputs(2, 300, 200, seed=seed, correlated=0.6))
+        a, b = eager(data), graphed(data)
+        for k in ("log_assignment", "matches0", "matches1", "matching_scores0", "ref_descriptors1"):
+            assert torch.equal(a[k], b[k]), (seed, k)
+    # variable-length batches go through their own captured graph with static length buffers
+    for seed, lens in ((6, ([300, 150], [200, 31])), (7, ([10, 299], [200, 200])), (8, ([300, 300], [1, 77]))):
+        data = _cuda(W.make_inputs(2, 300, 200, seed=seed, correlated=0.6))
+        data["num_keypoints0"], data["num_keypoints1"] = torch.tensor(lens[0]).cuda(), torch.tensor(lens[1]).cuda()
+        a, b = eager(data), graphed(data)
+        assert torch.equal(a["log_assignment"], b["log_assignment"]) and torch.equal(a["matches0"], b["matches0"])
