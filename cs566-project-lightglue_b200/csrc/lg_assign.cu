@@ -9,7 +9,7 @@
 // tcgen05 (kind::tf32): x = hi + lo with hi = rn_tf32(x), sim = hi.hi + hi.lo + lo.hi, fp32
 // accumulation in TMEM (dropped lo.lo term ~2^-22).
 //
-// Two passes over 128x128 similarity tiles, one tile per CTA, the tile never leaves the SM:
+// Two passes over 128x128 similarity tiles by persistent CTAs (one per SM), the tile never leaves the SM:
 //   pass 1 (stats): per-tile row and column (max, sum exp) partials -> tiny partial buffers;
 //   reduce:         merge partials into row / column logsumexp, logsigmoid terms, dustbins;
 //   pass 2 (write): recompute the tile (cheaper than storing + reloading 16.8 MB/pair of sim),
@@ -25,7 +25,7 @@ constexpr int kAssignK = 256;                 // descriptor dim
 constexpr int kKAtoms = kAssignK / 32;        // 8 swizzle atoms of 32 fp32 along K
 constexpr int kAtomTile = 16384;              // [128 rows][32 fp32]
 constexpr int kOperandStage = 2 * kAtomTile;  // hi | lo
-constexpr int kAssignStages = 3;
+constexpr int kAssignStages = 2;
 constexpr int kAssignThreads = 192;
 constexpr int kStagePitch = 129;              // fp32 transpose buffer pitch (conflict-free both ways)
 
@@ -70,56 +70,74 @@ struct AssignParams {
   const float* row_ls;      // pass 2: logsigmoid(z0) [B][M]
   const float* col_ls;      // pass 2: logsigmoid(z1) [B][N]
   float* scores;            // pass 2: (B, M+1, N+1)
-  int M, N, rt, ct;         // sizes, tile counts
+  int B, M, N, rt, ct;      // sizes, tile counts
 };
 
 struct __align__(8) AssignBarriers {
   uint64_t full[kAssignStages];
   uint64_t empty[kAssignStages];
   uint64_t acc_full;
+  uint64_t acc_empty;   // 128 arrivals: the epilogue has read the four accumulators of this tile
   uint32_t tmem_base;
 };
 
-constexpr int kAssignSmem = 1024 + kAssignStages * 2 * kOperandStage + static_cast<int>(sizeof(AssignBarriers));
-static_assert(kTile * kStagePitch * 4 <= kAssignStages * 2 * kOperandStage, "transpose buffer aliases the ring");
+constexpr int kTransposeBytes = (kTile * kStagePitch * 4 + 1023) & ~1023;
+constexpr int kLenCache = 1024;  // per-pair lengths of the first kLenCache pairs are cached in shared memory
+constexpr int kAssignSmem = 1024 + kAssignStages * 2 * kOperandStage + kTransposeBytes + 2 * kTile * 4 +
+                            2 * kLenCache * 4 + static_cast<int>(sizeof(AssignBarriers));
 
+// One similarity tile of the (b, rtile, ctile) grid, linearised with ctile fastest.
+struct AssignTile {
+  int b, rtile, ctile, row0, col0, vrows, vcols;
+};
+
+__device__ __forceinline__ AssignTile assign_tile(const AssignParams& p, const int* s_len, int it) {
+  AssignTile t;
+  t.ctile = it % p.ct;
+  const int br = it / p.ct;
+  t.rtile = br % p.rt;
+  t.b = br / p.rt;
+  int m = p.M, n = p.N;
+  if (p.m_len) m = min(t.b < kLenCache ? s_len[2 * t.b] : p.m_len[t.b], p.M);
+  if (p.n_len) n = min(t.b < kLenCache ? s_len[2 * t.b + 1] : p.n_len[t.b], p.N);
+  t.row0 = t.rtile * kTile;
+  t.col0 = t.ctile * kTile;
+  t.vrows = max(0, min(kTile, m - t.row0));
+  t.vcols = max(0, min(kTile, n - t.col0));
+  return t;
+}
+
+__device__ __forceinline__ float exp_fast(float x) {  // x <= 0; 2 ulp of the exact exponential
+  float y;
+  asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x * 1.4426950408889634f));
+  return y;
+}
+
+// Persistent: one CTA per SM walks tiles it, it + grid, ...  The operand ring runs ahead across
+// tile boundaries and the tensor core starts tile k+1 as soon as the epilogue has pulled tile k
+// out of TMEM, i.e. under the column statistics (pass 1) / the stores (pass 2) of tile k.
 template <int kPass>
 __global__ void __launch_bounds__(kAssignThreads, 1) assign_tile_kernel(const AssignParams p) {
   extern __shared__ uint8_t smem_raw[];
   uint8_t* base = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
   uint8_t* ring = base;
-  float* stage = reinterpret_cast<float*>(base);  // aliases the ring once all MMAs have retired
-  AssignBarriers* bar = reinterpret_cast<AssignBarriers*>(base + kAssignStages * 2 * kOperandStage);
+  float* stage = reinterpret_cast<float*>(base + kAssignStages * 2 * kOperandStage);
+  float* s_rowterm = reinterpret_cast<float*>(base + kAssignStages * 2 * kOperandStage + kTransposeBytes);  // [2][128]
+  int* s_len = reinterpret_cast<int*>(s_rowterm + 2 * kTile);                                            // [kLenCache][2]
+  AssignBarriers* bar = reinterpret_cast<AssignBarriers*>(s_len + 2 * kLenCache);
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  const int ctile = blockIdx.x, rtile = blockIdx.y, b = blockIdx.z;
-  const int m = p.m_len ? min(p.m_len[b], p.M) : p.M, n = p.n_len ? min(p.n_len[b], p.N) : p.N;
-  const int row0 = rtile * kTile, col0 = ctile * kTile;
-  const int vrows = max(0, min(kTile, m - row0)), vcols = max(0, min(kTile, n - col0));
+  const int items = p.B * p.rt * p.ct;
   const int64_t pitch = p.N + 1;
 
-  if (vrows == 0 || vcols == 0) {
-    // tile entirely in the padding of a variable-count batch
-    if (kPass == 1) {
-      if (threadIdx.x < kTile) {
-        if (row0 + threadIdx.x < p.M)
-          p.row_part[(static_cast<size_t>(b) * p.ct + ctile) * p.M + row0 + threadIdx.x] = make_float2(-INFINITY, 0.f);
-        if (col0 + threadIdx.x < p.N)
-          p.col_part[(static_cast<size_t>(b) * p.rt + rtile) * p.N + col0 + threadIdx.x] = make_float2(-INFINITY, 0.f);
-      }
-    } else {
-      float* out = p.scores + static_cast<int64_t>(b) * (p.M + 1) * pitch;
-      for (int i = threadIdx.x; i < kTile * kTile; i += kAssignThreads) {
-        const int r = row0 + (i >> 7), c = col0 + (i & 127);
-        if (r < p.M && c < p.N) out[r * pitch + c] = -INFINITY;
-      }
-    }
-    return;
+  for (int i = threadIdx.x; i < min(p.B, kLenCache); i += kAssignThreads) {
+    s_len[2 * i] = p.m_len ? p.m_len[i] : p.M;
+    s_len[2 * i + 1] = p.n_len ? p.n_len[i] : p.N;
   }
-
   if (threadIdx.x == 0) {
     for (int s = 0; s < kAssignStages; ++s) { mbar_init(&bar->full[s], 1); mbar_init(&bar->empty[s], 1); }
     mbar_init(&bar->acc_full, 1);
+    mbar_init(&bar->acc_empty, kTile);
     fence_mbar_init();
   }
   if (warp == 5) tmem_alloc<512>(&bar->tmem_base);
@@ -129,24 +147,39 @@ __global__ void __launch_bounds__(kAssignThreads, 1) assign_tile_kernel(const As
   const uint32_t tmem = bar->tmem_base;
 
   if (warp == 4) {
+    // ------------------------------------------------------------------ producer: bulk copies of operand atoms
     if (lane == 0) {
-      const uint8_t* ga = p.a_tiles + (static_cast<size_t>(b) * p.rt + rtile) * (kKAtoms * kOperandStage);
-      const uint8_t* gb = p.b_tiles + (static_cast<size_t>(b) * p.ct + ctile) * (kKAtoms * kOperandStage);
-      for (int ka = 0; ka < kKAtoms; ++ka) {
-        const int s = ka % kAssignStages;
-        if (ka >= kAssignStages) mbar_wait(&bar->empty[s], ((ka / kAssignStages) - 1) & 1);
-        mbar_arrive_expect_tx(&bar->full[s], 2 * kOperandStage);
-        bulk_g2s(ring + s * 2 * kOperandStage, ga + ka * kOperandStage, kOperandStage, &bar->full[s]);
-        bulk_g2s(ring + s * 2 * kOperandStage + kOperandStage, gb + ka * kOperandStage, kOperandStage, &bar->full[s]);
+      uint32_t g = 0;  // running ring step
+      for (int it = blockIdx.x; it < items; it += gridDim.x) {
+        const AssignTile t = assign_tile(p, s_len, it);
+        if (t.vrows == 0 || t.vcols == 0) continue;
+        const uint8_t* ga = p.a_tiles + (static_cast<size_t>(t.b) * p.rt + t.rtile) * (kKAtoms * kOperandStage);
+        const uint8_t* gb = p.b_tiles + (static_cast<size_t>(t.b) * p.ct + t.ctile) * (kKAtoms * kOperandStage);
+        for (int ka = 0; ka < kKAtoms; ++ka, ++g) {
+          const int s = g % kAssignStages;
+          if (g >= kAssignStages) mbar_wait(&bar->empty[s], ((g / kAssignStages) - 1) & 1);
+          mbar_arrive_expect_tx(&bar->full[s], 2 * kOperandStage);
+          bulk_g2s(ring + s * 2 * kOperandStage, ga + ka * kOperandStage, kOperandStage, &bar->full[s]);
+          bulk_g2s(ring + s * 2 * kOperandStage + kOperandStage, gb + ka * kOperandStage, kOperandStage, &bar->full[s]);
+        }
       }
     }
   } else if (warp == 5) {
-    if (lane == 0) {
-      constexpr uint32_t idesc = umma_idesc(kFmtTF32, 128, 128);
-      const uint32_t ring_a = smem_u32(ring);
-      for (int ka = 0; ka < kKAtoms; ++ka) {
-        const int s = ka % kAssignStages;
-        mbar_wait(&bar->full[s], (ka / kAssignStages) & 1);
+    // ------------------------------------------------------------------ tensor core issue (warp-uniform, one elected lane)
+    constexpr uint32_t idesc = umma_idesc(kFmtTF32, 128, 128);
+    const uint32_t ring_a = smem_u32(ring);
+    const bool leader = elect_one();
+    uint32_t g = 0, done = 0;
+    for (int it = blockIdx.x; it < items; it += gridDim.x) {
+      const AssignTile t = assign_tile(p, s_len, it);
+      if (t.vrows == 0 || t.vcols == 0) continue;
+      if (done > 0) {  // the epilogue has read the previous tile out of TMEM
+        mbar_wait(&bar->acc_empty, (done - 1) & 1);
+        tc_fence_after();
+      }
+      for (int ka = 0; ka < kKAtoms; ++ka, ++g) {
+        const int s = g % kAssignStages;
+        mbar_wait(&bar->full[s], (g / kAssignStages) & 1);
         tc_fence_after();
         const uint32_t a_hi = ring_a + s * 2 * kOperandStage, a_lo = a_hi + kAtomTile;
         const uint32_t b_hi = a_hi + kOperandStage, b_lo = b_hi + kAtomTile;
@@ -157,86 +190,123 @@ __global__ void __launch_bounds__(kAssignThreads, 1) assign_tile_kernel(const As
         // spread over three TMEM accumulators (<= 12 steps each) and the 2^-11-small cross terms
         // go to a fourth; the epilogue adds the four with round-to-nearest.
         const uint32_t acc_hh = tmem + (ka % 3) * 128, acc_x = tmem + 384;
+        if (leader) {
 #pragma unroll
-        for (int kk = 0; kk < 4; ++kk) {  // 32 fp32 per atom = 4 x K8, 32 B per step
-          umma_tf32_ss(acc_x, dal + 2 * kk, dbh + 2 * kk, idesc, (ka > 0 || kk > 0));
-          umma_tf32_ss(acc_x, dah + 2 * kk, dbl + 2 * kk, idesc, 1);
-          umma_tf32_ss(acc_hh, dah + 2 * kk, dbh + 2 * kk, idesc, (ka >= 3 || kk > 0));
+          for (int kk = 0; kk < 4; ++kk) {  // 32 fp32 per atom = 4 x K8, 32 B per step
+            umma_tf32_ss(acc_x, dal + 2 * kk, dbh + 2 * kk, idesc, (ka > 0 || kk > 0));
+            umma_tf32_ss(acc_x, dah + 2 * kk, dbl + 2 * kk, idesc, 1);
+            umma_tf32_ss(acc_hh, dah + 2 * kk, dbh + 2 * kk, idesc, (ka >= 3 || kk > 0));
+          }
+          umma_commit(&bar->empty[s]);
         }
-        umma_commit(&bar->empty[s]);
+        __syncwarp();
       }
-      umma_commit(&bar->acc_full);
+      if (leader) umma_commit(&bar->acc_full);
+      __syncwarp();
+      ++done;
     }
   } else {
     // ------------------------------------------------------------------ epilogue (128 threads, thread == row)
     const int r = warp * 32 + lane;
     const uint32_t tS = tmem + (static_cast<uint32_t>(warp * 32) << 16);
-    mbar_wait(&bar->acc_full, 0);
-    tc_fence_after();
-    uint32_t v[32], w[32];
-    float rmax = -INFINITY, rsum = 0.f;
+    uint32_t done = 0;
+    for (int it = blockIdx.x; it < items; it += gridDim.x) {
+      const AssignTile t = assign_tile(p, s_len, it);
+      const int b = t.b, row0 = t.row0, col0 = t.col0, vrows = t.vrows, vcols = t.vcols;
+      if (vrows == 0 || vcols == 0) {
+        // tile entirely in the padding of a variable-count batch
+        if (kPass == 1) {
+          if (row0 + r < p.M)
+            p.row_part[(static_cast<size_t>(b) * p.ct + t.ctile) * p.M + row0 + r] = make_float2(-INFINITY, 0.f);
+          if (col0 + r < p.N)
+            p.col_part[(static_cast<size_t>(b) * p.rt + t.rtile) * p.N + col0 + r] = make_float2(-INFINITY, 0.f);
+        } else {
+          float* out = p.scores + static_cast<int64_t>(b) * (p.M + 1) * pitch;
+          for (int i = r; i < kTile * kTile; i += kTile) {
+            const int rr = row0 + (i >> 7), c = col0 + (i & 127);
+            if (rr < p.M && c < p.N) out[rr * pitch + c] = -INFINITY;
+          }
+        }
+        continue;
+      }
+      float rl = 0.f, ra = 0.f;
+      if (kPass == 2 && row0 + r < p.M) {  // this row's logsumexp / log-sigmoid term, fetched under the MMA
+        rl = p.row_lse[static_cast<size_t>(b) * p.M + row0 + r];
+        ra = p.row_ls[static_cast<size_t>(b) * p.M + row0 + r];
+      }
+      mbar_wait(&bar->acc_full, done & 1);
+      tc_fence_after();
+      asm volatile("bar.sync 1, 128;" ::: "memory");  // every warp is done with the previous tile's transpose buffer
+      if (kPass == 2) { s_rowterm[r] = rl; s_rowterm[kTile + r] = ra; }
+      uint32_t v[32], w0[32], w1[32], w2[32];
+      float rmax = -INFINITY, rsum = 0.f;
 #pragma unroll
-    for (int cb = 0; cb < 4; ++cb) {
-      tmem_ld32(tS + cb * 32, v);
-      tmem_ld32(tS + 128 + cb * 32, w);
-      tmem_wait_ld();
+      for (int cb = 0; cb < 4; ++cb) {
+        tmem_ld32(tS + cb * 32, v);
+        tmem_ld32(tS + 128 + cb * 32, w0);
+        tmem_ld32(tS + 256 + cb * 32, w1);
+        tmem_ld32(tS + 384 + cb * 32, w2);
+        tmem_wait_ld();
+        if (cb == 3) {  // accumulators are in registers: the tensor core may start the next tile
+          tc_fence_before();
+          mbar_arrive(&bar->acc_empty);
+        }
 #pragma unroll
-      for (int i = 0; i < 32; ++i) v[i] = __float_as_uint(__uint_as_float(v[i]) + __uint_as_float(w[i]));
-      tmem_ld32(tS + 256 + cb * 32, w);
-      tmem_wait_ld();
+        for (int i = 0; i < 32; ++i) {
+          float s = __uint_as_float(v[i]) + __uint_as_float(w0[i]);
+          s += __uint_as_float(w1[i]);
+          s += __uint_as_float(w2[i]);
+          v[i] = __float_as_uint(s);
+        }
+        if (kPass == 1) {
+          float cmax = -INFINITY;
 #pragma unroll
-      for (int i = 0; i < 32; ++i) v[i] = __float_as_uint(__uint_as_float(v[i]) + __uint_as_float(w[i]));
-      tmem_ld32(tS + 384 + cb * 32, w);
-      tmem_wait_ld();
+          for (int i = 0; i < 32; ++i)
+            if (cb * 32 + i < vcols) cmax = fmaxf(cmax, __uint_as_float(v[i]));
+          if (cmax > rmax) { rsum *= exp_fast(rmax - cmax); rmax = cmax; }
 #pragma unroll
-      for (int i = 0; i < 32; ++i) v[i] = __float_as_uint(__uint_as_float(v[i]) + __uint_as_float(w[i]));
+          for (int i = 0; i < 32; ++i)
+            if (cb * 32 + i < vcols) rsum += exp_fast(__uint_as_float(v[i]) - rmax);
+        }
+#pragma unroll
+        for (int i = 0; i < 32; ++i) stage[r * kStagePitch + cb * 32 + i] = __uint_as_float(v[i]);
+      }
+      ++done;
+      if (kPass == 1 && row0 + r < p.M)
+        p.row_part[(static_cast<size_t>(b) * p.ct + t.ctile) * p.M + row0 + r] =
+            r < vrows ? make_float2(rmax, rsum) : make_float2(-INFINITY, 0.f);
+      asm volatile("bar.sync 1, 128;" ::: "memory");  // epilogue warps only
       if (kPass == 1) {
-        float cmax = -INFINITY;
-#pragma unroll
-        for (int i = 0; i < 32; ++i)
-          if (cb * 32 + i < vcols) cmax = fmaxf(cmax, __uint_as_float(v[i]));
-        if (cmax > rmax) { rsum *= expf(rmax - cmax); rmax = cmax; }
-#pragma unroll
-        for (int i = 0; i < 32; ++i)
-          if (cb * 32 + i < vcols) rsum += expf(__uint_as_float(v[i]) - rmax);
-      }
-#pragma unroll
-      for (int i = 0; i < 32; ++i) stage[r * kStagePitch + cb * 32 + i] = __uint_as_float(v[i]);
-    }
-    if (kPass == 1 && row0 + r < p.M)
-      p.row_part[(static_cast<size_t>(b) * p.ct + ctile) * p.M + row0 + r] =
-          r < vrows ? make_float2(rmax, rsum) : make_float2(-INFINITY, 0.f);
-    asm volatile("bar.sync 1, 128;" ::: "memory");  // epilogue warps only
-    if (kPass == 1) {
-      // thread == column: online (max, sum exp) down the valid rows
-      const int c = r;
-      float cmax = -INFINITY, csum = 0.f;
-      for (int i = 0; i < vrows; ++i) cmax = fmaxf(cmax, stage[i * kStagePitch + c]);
-      for (int i = 0; i < vrows; ++i) csum += expf(stage[i * kStagePitch + c] - cmax);
-      if (col0 + c < p.N)
-        p.col_part[(static_cast<size_t>(b) * p.rt + rtile) * p.N + col0 + c] =
-            c < vcols ? make_float2(cmax, csum) : make_float2(-INFINITY, 0.f);
-    } else {
-      float* out = p.scores + static_cast<int64_t>(b) * (p.M + 1) * pitch;
-      float lc[4], lb[4];
-#pragma unroll
-      for (int q = 0; q < 4; ++q) {
-        const int c = q * 32 + lane;
-        const bool ok = c < vcols;
-        lc[q] = ok ? p.col_lse[static_cast<size_t>(b) * p.N + col0 + c] : 0.f;
-        lb[q] = ok ? p.col_ls[static_cast<size_t>(b) * p.N + col0 + c] : 0.f;
-      }
-      for (int i = warp; i < kTile; i += 4) {  // a warp stores one 512 B row segment per iteration
-        if (row0 + i >= p.M) break;
-        const float rl = p.row_lse[static_cast<size_t>(b) * p.M + min(row0 + i, p.M - 1)];
-        const float ra = p.row_ls[static_cast<size_t>(b) * p.M + min(row0 + i, p.M - 1)];
+        // thread == column: (max, sum exp) down the valid rows
+        const int c = r;
+        float cmax = -INFINITY, csum = 0.f;
+        for (int i = 0; i < vrows; ++i) cmax = fmaxf(cmax, stage[i * kStagePitch + c]);
+        for (int i = 0; i < vrows; ++i) csum += exp_fast(stage[i * kStagePitch + c] - cmax);
+        if (col0 + c < p.N)
+          p.col_part[(static_cast<size_t>(b) * p.rt + t.rtile) * p.N + col0 + c] =
+              c < vcols ? make_float2(cmax, csum) : make_float2(-INFINITY, 0.f);
+      } else {
+        float* out = p.scores + static_cast<int64_t>(b) * (p.M + 1) * pitch;
+        float lc[4], lb[4];
 #pragma unroll
         for (int q = 0; q < 4; ++q) {
           const int c = q * 32 + lane;
-          if (col0 + c < p.N) {
-            const float s = stage[i * kStagePitch + c];
-            const float val = (i < vrows && c < vcols) ? ((s - rl) + (s - lc[q])) + (ra + lb[q]) : -INFINITY;
-            out[static_cast<int64_t>(row0 + i) * pitch + col0 + c] = val;
+          const bool ok = c < vcols;
+          lc[q] = ok ? p.col_lse[static_cast<size_t>(b) * p.N + col0 + c] : 0.f;
+          lb[q] = ok ? p.col_ls[static_cast<size_t>(b) * p.N + col0 + c] : 0.f;
+        }
+        const int rows_here = min(kTile, p.M - row0);
+#pragma unroll 4
+        for (int i = warp; i < rows_here; i += 4) {  // a warp stores one 512 B row segment per iteration
+          const float rli = s_rowterm[i], rai = s_rowterm[kTile + i];
+#pragma unroll
+          for (int q = 0; q < 4; ++q) {
+            const int c = q * 32 + lane;
+            if (col0 + c < p.N) {
+              const float s = stage[i * kStagePitch + c];
+              const float val = (i < vrows && c < vcols) ? ((s - rli) + (s - lc[q])) + (rai + lb[q]) : -INFINITY;
+              out[static_cast<int64_t>(row0 + i) * pitch + col0 + c] = val;
+            }
           }
         }
       }
@@ -246,7 +316,6 @@ __global__ void __launch_bounds__(kAssignThreads, 1) assign_tile_kernel(const As
   __syncthreads();
   if (warp == 5) tmem_dealloc<512>(tmem);
 }
-
 }  // namespace lg
 
 namespace lg {
@@ -339,12 +408,19 @@ extern "C" int lg_assign(const float* md0, const float* md1, const float* z0, co
   lg::assign_pack_kernel<<<dim3(rt, B), 1024, 0, stream>>>(md0, m_len, a_tiles, M, rt, prescale);
   lg::assign_pack_kernel<<<dim3(ct, B), 1024, 0, stream>>>(md1, n_len, b_tiles, N, ct, prescale);
   lg::AssignParams p{a_tiles, b_tiles, m_len, n_len, row_part, col_part, row_lse, col_lse, row_ls, col_ls, scores,
-                     M, N, rt, ct};
-  lg::assign_tile_kernel<1><<<dim3(ct, rt, B), lg::kAssignThreads, lg::kAssignSmem, stream>>>(p);
+                     B, M, N, rt, ct};
+  int sms = 0, dev = 0;
+  cudaGetDevice(&dev);
+  cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+  if (sms <= 0) sms = 148;
+  const long long items = static_cast<long long>(B) * rt * ct;
+  if (items > 0x7fffffffLL) return LG_ERR_SHAPE;
+  const int grid = items < sms ? static_cast<int>(items) : sms;  // persistent: one CTA per SM
+  lg::assign_tile_kernel<1><<<grid, lg::kAssignThreads, lg::kAssignSmem, stream>>>(p);
   const int pts = (M > N ? M : N);
   lg::assign_reduce_kernel<<<dim3((pts + 255) / 256, B), 256, 0, stream>>>(row_part, col_part, z0, z1, m_len, n_len,
                                                                           row_lse, col_lse, row_ls, col_ls, scores, M,
                                                                           N, rt, ct);
-  lg::assign_tile_kernel<2><<<dim3(ct, rt, B), lg::kAssignThreads, lg::kAssignSmem, stream>>>(p);
+  lg::assign_tile_kernel<2><<<grid, lg::kAssignThreads, lg::kAssignSmem, stream>>>(p);
   return static_cast<int>(cudaGetLastError());
 }

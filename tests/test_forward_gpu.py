@@ -144,3 +144,20 @@ def test_cuda_graph_replay_matches_eager():
         data["num_keypoints0"], data["num_keypoints1"] = torch.tensor(lens[0]).cuda(), torch.tensor(lens[1]).cuda()
         a, b = eager(data), graphed(data)
         assert torch.equal(a["log_assignment"], b["log_assignment"]) and torch.equal(a["matches0"], b["matches0"])
+
+
+def test_host_pipeline_matches_direct_calls():
+    """HostPipeline (copies on side streams, double-buffered slots) returns, batch by batch and in order, exactly
+    what model(batch.cuda()) returns -- including when the host buffers are rewritten right after submission."""
+    P = pkg("pipeline")
+    conf = {"filter_threshold": 0.1}
+    model = _model(conf, W.make_state_dict(conf, seed=0))
+    batches = [W.make_inputs(2, 260, 190, seed=s, correlated=0.6) for s in (11, 12, 13, 14, 15)]
+    want = [{k: model(_cuda(b))[k].cpu() for k in P.RESULT_KEYS} for b in batches]
+    pinned = [{k: ({kk: vv.pin_memory() for kk, vv in v.items()} if isinstance(v, dict) else v.pin_memory())
+               for k, v in b.items()} for b in batches]
+    got = [{k: v.clone() for k, v in pred.items()} for pred in P.HostPipeline(model, depth=2).run(iter(pinned))]
+    assert len(got) == len(want)
+    for i, (a, b) in enumerate(zip(want, got)):
+        for k in P.RESULT_KEYS:
+            assert torch.equal(a[k], b[k]), (i, k)
