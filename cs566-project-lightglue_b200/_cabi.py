@@ -37,6 +37,7 @@ SIGNATURES = {
     "lg_tiles_to_rows": (_I, [_P, _P, _I, _I, _I, _I, _P]),
     "lg_rotary_tiles": (_I, [_P, _P, _P, _I, _I, _I, _P]),
     "lg_ln_gelu_tiles": (_I, [_P, _P, _P, _F, _P, _I, _P]),
+    "lg_ffn_ln_gelu": (_I, [_P, _I, _P, _I, _P, _P, _P, _P, _F, _P, _I, _P]),
     "lg_linear_split": (_I, [_P, _I, _P, _I, _I, _P, _P, _P, _P, _I, _I, _P]),
     "lg_linear_f32": (_I, [_P, _I, _P, _I, _I, _P, _P, _P, _L, _I, _I, _P]),
     "lg_linear_qkv_self": (_I, [_P, _P, _P, _P, _P, _P, _P, _P, _P, _P, _I, _I, _I, _I, _P]),
@@ -301,6 +302,18 @@ def ln_gelu_tiles(h, gamma, beta, eps: float, out=None):
         out = alloc_split(rows // TILE, 512, h.device)
     _check(lib().lg_ln_gelu_tiles(_ptr(_f32c(h, "h")), _ptr(_f32c(gamma, "gamma")), _ptr(_f32c(beta, "beta")), float(eps),
                                   _ptr(out), rows, _stream()), "lg_ln_gelu_tiles")
+    _count(1)
+    return out
+
+
+def ffn_ln_gelu(a0, w, bias, gamma, beta, eps: float, a1=None, out=None):
+    """GELU(LayerNorm([a0 | a1] . w^T + bias)) -> split tiles (row_tiles, 8, 32 KB); one fused launch."""
+    rt = a0.shape[0]
+    if out is None:
+        out = alloc_split(rt, 512, a0.device)
+    _check(lib().lg_ffn_ln_gelu(_ptr(a0), a0.shape[1], _ptr(a1), 0 if a1 is None else a1.shape[1], _ptr(w),
+                                _ptr(_f32c(bias, "bias")), _ptr(_f32c(gamma, "gamma")), _ptr(_f32c(beta, "beta")),
+                                float(eps), _ptr(out), rt, _stream()), "lg_ffn_ln_gelu")
     _count(1)
     return out
 

@@ -1,0 +1,299 @@
+// lg_ffn : first half of the block MLP in one kernel,
+//     h = GELU(LayerNorm([x | ctx] . W0'^T + b0'))         (512 -> 512, LayerNorm over the 512 outputs)
+// i.e. ffn.0 (with out_proj / to_out folded in), ffn.1 and ffn.2 of SelfBlock / CrossBlock
+// (reference gluefactory/models/matchers/lightglue.py:171-176,190-191 and :205-210,246-248).
+//
+// The pre-LayerNorm activations never leave the SM: the stand-alone path (lg_linear_f32 + lg_ln_gelu_tiles) wrote
+// 268 MB of fp32 rows per launch with thread-per-row 16-byte stores and read them back.
+//
+// A CTA PAIR (cluster of 2, one TPC) owns a row tile of 128 tokens; CTA `rank` computes output columns
+// [256 rank, 256 rank + 256) with its own single-CTA tcgen05 pipeline (A atom 32 KB + W atom 64 KB per stage, 2 stages,
+// two 256-column TMEM accumulators so the MMAs of row tile i+1 run under the epilogue of tile i).  LayerNorm needs
+// the statistics of the whole 512-wide row: every CTA reduces its half to (mean, M2 = sum (x - mean)^2), ships the
+// pair of floats per row to its peer through distributed shared memory (st.async + mbarrier complete_tx, no
+// cluster barrier), and merges the two halves exactly (Chan et al.):
+//     mean = (m0 + m1) / 2,   M2 = M2_0 + M2_1 + (m0 - m1)^2 * 128.
+// 320 threads: warps 0-7 epilogue (warp w: TMEM lanes 32 (w % 4).., columns 32 (w / 4).. of every 64-column atom),
+// warp 8 producer, warp 9 MMA issue.  Output: split tiles (hi | lo bf16 images) staged in shared memory and written
+// with one 32 KB bulk store per atom.
+#include "lg_common.cuh"
+#include "lg_tiles.cuh"
+#include "lg_b200.h"
+
+namespace lg {
+
+constexpr int kFfnThreads = 320;
+constexpr int kFfnStages = 2;
+constexpr int kFfnNt = 256;                       // output columns per CTA
+constexpr int kFfnWAtom = kFfnNt * 256;           // hi | lo of one K atom of the CTA's weight tile
+constexpr int kFfnStage = kSplitAtom + kFfnWAtom;  // 96 KB
+
+struct FfnParams {
+  const uint8_t* a0;     // [row_tiles][a0_atoms][32 KB]
+  const uint8_t* a1;     // [row_tiles][a1_atoms][32 KB], concatenated along K after a0 (may be null)
+  int a0_atoms, a1_atoms;
+  const uint8_t* w;      // lg_pack_weight(W (512, K), nt = 256): [2][k_atoms][hi | lo][256 x 128 B]
+  const float* bias;     // [512]
+  const float* gamma;    // [512] LayerNorm weight
+  const float* beta;     // [512] LayerNorm bias
+  float eps;
+  uint8_t* out_tiles;    // [row_tiles][8][32 KB]
+  int row_tiles;
+};
+
+struct __align__(8) FfnBarriers {
+  uint64_t full[kFfnStages];
+  uint64_t empty[kFfnStages];
+  uint64_t acc_full[2];
+  uint64_t acc_empty[2];
+  uint64_t xchg_full[2];   // the peer's row statistics of this item have landed in xchg[buf]
+  uint32_t tmem_base;
+};
+
+constexpr int kFfnXchgBytes = 2 * kTile * 8;  // [buf][row] (mean, M2)
+constexpr int kFfnSmem = kFfnStages * kFfnStage + kSplitAtom + kFfnXchgBytes + static_cast<int>(sizeof(FfnBarriers));
+static_assert(kFfnSmem <= 232448, "227 KB per CTA");
+
+__device__ __forceinline__ void epi_bar_sync_256() { asm volatile("bar.sync 1, 256;" ::: "memory"); }
+
+// 32-bit store into the peer CTA's shared memory that completes 4 tx bytes on the peer's mbarrier
+__device__ __forceinline__ void st_async_peer(void* local_slot, float value, uint64_t* local_bar, uint32_t peer) {
+  asm volatile(
+      "{\n\t.reg .b32 ra, rb;\n\t"
+      "mapa.shared::cluster.u32 ra, %0, %3;\n\t"
+      "mapa.shared::cluster.u32 rb, %2, %3;\n\t"
+      "st.async.shared::cluster.mbarrier::complete_tx::bytes.u32 [ra], %1, [rb];\n\t}" ::"r"(smem_u32(local_slot)),
+      "r"(__float_as_uint(value)), "r"(smem_u32(local_bar)), "r"(peer)
+      : "memory");
+}
+
+__device__ __forceinline__ float gelu_erf(float z) { return 0.5f * z * (1.f + erff(z * 0.70710678118654752f)); }
+
+__global__ void __launch_bounds__(kFfnThreads, 1) ffn_ln_gelu_kernel(const FfnParams p) {
+  extern __shared__ __align__(1024) uint8_t smem[];
+  uint8_t* ring = smem;
+  uint8_t* stg = ring + kFfnStages * kFfnStage;                  // one split atom of output
+  float2* xchg = reinterpret_cast<float2*>(stg + kSplitAtom);   // [2][128]
+  FfnBarriers* bar = reinterpret_cast<FfnBarriers*>(stg + kSplitAtom + kFfnXchgBytes);
+
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int k_atoms = p.a0_atoms + p.a1_atoms;
+  const uint32_t rank = cluster_ctarank();
+  const int first = blockIdx.x >> 1, stride = gridDim.x >> 1;
+
+  if (threadIdx.x == 0) {
+    if (smem_u32(smem) & 1023u) __trap();  // SWIZZLE_128B tiles need the 1 KB alignment the declaration asks for
+    for (int s = 0; s < kFfnStages; ++s) { mbar_init(&bar->full[s], 1); mbar_init(&bar->empty[s], 1); }
+    for (int i = 0; i < 2; ++i) {
+      mbar_init(&bar->acc_full[i], 1);
+      mbar_init(&bar->acc_empty[i], 256);
+      mbar_init(&bar->xchg_full[i], 1);
+    }
+    fence_mbar_init();
+  }
+  if (warp == 9) tmem_alloc<512>(&bar->tmem_base);
+  tc_fence_before();
+  cluster_sync_all();  // the peer's barriers exist before the first remote store
+  tc_fence_after();
+  const uint32_t tmem = bar->tmem_base;
+
+  if (warp == 8) {
+    // ------------------------------------------------------------------ producer
+    if (lane == 0) {
+      const uint8_t* gw = p.w + static_cast<size_t>(rank) * k_atoms * kFfnWAtom;
+      uint32_t it = 0;
+      for (int rt = first; rt < p.row_tiles; rt += stride) {
+        for (int ka = 0; ka < k_atoms; ++ka, ++it) {
+          const int s = it % kFfnStages;
+          if (it >= kFfnStages) mbar_wait(&bar->empty[s], ((it / kFfnStages) - 1) & 1);
+          const uint8_t* ga = ka < p.a0_atoms
+                                  ? p.a0 + (static_cast<size_t>(rt) * p.a0_atoms + ka) * kSplitAtom
+                                  : p.a1 + (static_cast<size_t>(rt) * p.a1_atoms + (ka - p.a0_atoms)) * kSplitAtom;
+          mbar_arrive_expect_tx(&bar->full[s], kFfnStage);
+          bulk_g2s(ring + s * kFfnStage, ga, kSplitAtom, &bar->full[s]);
+          bulk_g2s(ring + s * kFfnStage + kSplitAtom, gw + static_cast<size_t>(ka) * kFfnWAtom, kFfnWAtom,
+                   &bar->full[s]);
+        }
+      }
+    }
+  } else if (warp == 9) {
+    // ------------------------------------------------------------------ MMA issue (warp-uniform, one elected lane)
+    const bool leader = elect_one();
+    constexpr uint32_t idesc = umma_idesc(kFmtBF16, 128, kFfnNt);
+    const uint32_t ring_a = smem_u32(ring);
+    uint32_t it = 0;
+    int local = 0;
+    for (int rt = first; rt < p.row_tiles; rt += stride, ++local) {
+      const int buf = local & 1;
+      if (local >= 2) { mbar_wait(&bar->acc_empty[buf], ((local >> 1) - 1) & 1); tc_fence_after(); }
+      const uint32_t acc = tmem + buf * 256;
+      for (int ka = 0; ka < k_atoms; ++ka, ++it) {
+        const int s = it % kFfnStages;
+        mbar_wait(&bar->full[s], (it / kFfnStages) & 1);
+        tc_fence_after();
+        const uint32_t a_hi = ring_a + s * kFfnStage, a_lo = a_hi + kHalfAtom;
+        const uint32_t w_hi = a_hi + kSplitAtom, w_lo = w_hi + kFfnNt * 128;
+        const uint64_t dah = umma_desc_kmajor_sw128(a_hi), dal = umma_desc_kmajor_sw128(a_lo);
+        const uint64_t dwh = umma_desc_kmajor_sw128(w_hi), dwl = umma_desc_kmajor_sw128(w_lo);
+#pragma unroll
+        for (int kk = 0; kk < 4; ++kk) {  // 64 bf16 per atom = 4 x K16, 32 B per step
+          if (leader) umma_bf16_ss(acc, dal + 2 * kk, dwh + 2 * kk, idesc, (ka > 0 || kk > 0));
+          if (leader) umma_bf16_ss(acc, dah + 2 * kk, dwl + 2 * kk, idesc, 1);
+          if (leader) umma_bf16_ss(acc, dah + 2 * kk, dwh + 2 * kk, idesc, 1);
+        }
+        if (leader) umma_commit(&bar->empty[s]);
+      }
+      if (leader) umma_commit(&bar->acc_full[buf]);
+    }
+  } else {
+    // ------------------------------------------------------------------ epilogue: 2 threads per row
+    const int q = warp & 3, g = warp >> 2;
+    const int r = q * 32 + lane;
+    const bool leader = threadIdx.x == 0;
+    const float* bias = p.bias + rank * kFfnNt;
+    const float* gamma = p.gamma + rank * kFfnNt;
+    const float* beta = p.beta + rank * kFfnNt;
+    uint32_t v[32];
+    int local = 0;
+    for (int rt = first; rt < p.row_tiles; rt += stride, ++local) {
+      const int buf = local & 1;
+      const uint32_t par = (local >> 1) & 1;
+      const uint32_t tacc = tmem + (static_cast<uint32_t>(q * 32) << 16) + buf * 256;
+      if (leader) mbar_arrive_expect_tx(&bar->xchg_full[buf], kTile * 8);
+      mbar_wait(&bar->acc_full[buf], par);
+      tc_fence_after();
+
+      // ---- statistics of this CTA's 256 columns (both threads of a row compute them), shifted by the first element
+      float shift = 0.f, s1 = 0.f, s2 = 0.f;
+#pragma unroll 1
+      for (int cb = 0; cb < 8; ++cb) {
+        tmem_ld32(tacc + cb * 32, v);
+        tmem_wait_ld();
+        if (cb == 0) shift = __uint_as_float(v[0]) + __ldg(bias);
+#pragma unroll
+        for (int i4 = 0; i4 < 8; ++i4) {
+          const float4 b4 = __ldg(reinterpret_cast<const float4*>(bias + cb * 32) + i4);
+          const float bb[4] = {b4.x, b4.y, b4.z, b4.w};
+#pragma unroll
+          for (int e = 0; e < 4; ++e) {
+            const float d = (__uint_as_float(v[4 * i4 + e]) + bb[e]) - shift;
+            s1 += d;
+            s2 = fmaf(d, d, s2);
+          }
+        }
+      }
+      const float dm = s1 * (1.f / 256.f);
+      const float mean_c = shift + dm;
+      const float m2_c = fmaxf(s2 - s1 * dm, 0.f);
+      if (g == 0) {
+        st_async_peer(&xchg[buf * kTile + r].x, mean_c, &bar->xchg_full[buf], rank ^ 1);
+        st_async_peer(&xchg[buf * kTile + r].y, m2_c, &bar->xchg_full[buf], rank ^ 1);
+      }
+      mbar_wait(&bar->xchg_full[buf], par);
+      const float2 peer = xchg[buf * kTile + r];
+      const float mean = 0.5f * (mean_c + peer.x);
+      const float dmm = mean_c - peer.x;
+      const float var = (m2_c + peer.y + dmm * dmm * 128.f) * (1.f / 512.f);
+      const float rstd = rsqrtf(var + p.eps);
+      const float nmr = -mean * rstd;
+
+      // ---- normalise, GELU, split, stage, store: 4 atoms of 64 columns; this thread's 32 columns of each
+#pragma unroll 1
+      for (int j = 0; j < 4; ++j) {
+        tmem_ld32(tacc + j * 64 + g * 32, v);
+        tmem_wait_ld();
+        if (j == 3) { tc_fence_before(); mbar_arrive(&bar->acc_empty[buf]); }
+        uint4 hi[4], lo[4];
+#pragma unroll
+        for (int c = 0; c < 4; ++c) {
+          const int col = j * 64 + g * 32 + c * 8;
+          float y[8];
+#pragma unroll
+          for (int h2 = 0; h2 < 2; ++h2) {
+            const float4 b4 = __ldg(reinterpret_cast<const float4*>(bias + col) + h2);
+            const float4 g4 = __ldg(reinterpret_cast<const float4*>(gamma + col) + h2);
+            const float4 t4 = __ldg(reinterpret_cast<const float4*>(beta + col) + h2);
+            const float bb[4] = {b4.x, b4.y, b4.z, b4.w}, gg[4] = {g4.x, g4.y, g4.z, g4.w}, tt[4] = {t4.x, t4.y, t4.z, t4.w};
+#pragma unroll
+            for (int e = 0; e < 4; ++e) {
+              const float x = __uint_as_float(v[c * 8 + h2 * 4 + e]) + bb[e];
+              const float z = fmaf(fmaf(x, rstd, nmr), gg[e], tt[e]);
+              y[h2 * 4 + e] = gelu_erf(z);
+            }
+          }
+          split8(y, hi[c], lo[c]);
+        }
+        if (leader) bulk_wait_read<0>();  // the previous atom's store has drained the staging buffer
+        epi_bar_sync_256();
+#pragma unroll
+        for (int c = 0; c < 4; ++c) {
+          uint8_t* at = stg + sw128_offset(r, g * 4 + c);
+          *reinterpret_cast<uint4*>(at) = hi[c];
+          *reinterpret_cast<uint4*>(at + kHalfAtom) = lo[c];
+        }
+        fence_proxy_async_smem();
+        epi_bar_sync_256();
+        if (leader) {
+          bulk_s2g(p.out_tiles + (static_cast<size_t>(rt) * 8 + rank * 4 + j) * kSplitAtom, stg, kSplitAtom);
+          bulk_commit();
+        }
+      }
+    }
+    if (leader) bulk_wait_all();
+  }
+  tc_fence_before();
+  cluster_sync_all();  // no CTA exits while its peer may still store into its shared memory
+  if (warp == 9) tmem_dealloc<512>(tmem);
+}
+
+}  // namespace lg
+
+static bool ffn_aligned16(const void* p) { return (reinterpret_cast<uintptr_t>(p) & 15) == 0; }
+
+extern "C" int lg_ffn_ln_gelu(const void* a0, int a0_atoms, const void* a1, int a1_atoms, const void* w,
+                              const float* bias, const float* gamma, const float* beta, float eps, void* out_tiles,
+                              int row_tiles, cudaStream_t stream) {
+  if (!a0 || !w || !bias || !gamma || !beta || !out_tiles) return LG_ERR_NULL;
+  if (row_tiles <= 0 || a0_atoms <= 0 || a1_atoms < 0 || (a1_atoms > 0 && !a1)) return LG_ERR_SHAPE;
+  if (!ffn_aligned16(a0) || !ffn_aligned16(a1) || !ffn_aligned16(w) || !ffn_aligned16(out_tiles) ||
+      !ffn_aligned16(bias) || !ffn_aligned16(gamma) || !ffn_aligned16(beta))
+    return LG_ERR_ALIGN;
+  lg::FfnParams p{};
+  p.a0 = static_cast<const uint8_t*>(a0);
+  p.a1 = static_cast<const uint8_t*>(a1);
+  p.a0_atoms = a0_atoms;
+  p.a1_atoms = a1_atoms;
+  p.w = static_cast<const uint8_t*>(w);
+  p.bias = bias;
+  p.gamma = gamma;
+  p.beta = beta;
+  p.eps = eps;
+  p.out_tiles = static_cast<uint8_t*>(out_tiles);
+  p.row_tiles = row_tiles;
+
+  static bool attr_done = false;
+  static int tpcs = 0;
+  if (!attr_done) {
+    cudaError_t e =
+        cudaFuncSetAttribute(lg::ffn_ln_gelu_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, lg::kFfnSmem);
+    if (e != cudaSuccess) return static_cast<int>(e);
+    int dev = 0, sms = 0;
+    cudaGetDevice(&dev);
+    cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+    tpcs = sms > 1 ? sms / 2 : 74;
+    attr_done = true;
+  }
+  cudaLaunchConfig_t cfg = {};
+  cfg.gridDim = dim3(static_cast<unsigned>(2 * (row_tiles < tpcs ? row_tiles : tpcs)));  // persistent: one pair per TPC
+  cfg.blockDim = dim3(lg::kFfnThreads);
+  cfg.dynamicSmemBytes = lg::kFfnSmem;
+  cfg.stream = stream;
+  cudaLaunchAttribute attr[1];
+  attr[0].id = cudaLaunchAttributeClusterDimension;
+  attr[0].val.clusterDim.x = 2;
+  attr[0].val.clusterDim.y = 1;
+  attr[0].val.clusterDim.z = 1;
+  cfg.attrs = attr;
+  cfg.numAttrs = 1;
+  return static_cast<int>(cudaLaunchKernelEx(&cfg, lg::ffn_ln_gelu_kernel, p));
+}

@@ -24,15 +24,17 @@
 // Epilogues (template): split tiles (+bias, +residual), fp32 rows, and the attention operand
 // producers (self: de-interleaved Wqkv + rotary; cross: to_qk | to_v) that write the bf16
 // Q / K / V^T tiles lg_attention consumes, through shared-memory staging + bulk stores.
+#include <cstdlib>
+
 #include "lg_common.cuh"
+#include "lg_tiles.cuh"
 #include "lg_b200.h"
 
 namespace lg {
 
 constexpr int kLinThreads = 192;
-constexpr int kLinStages = 2;
-constexpr int kSplitAtom = 32768;   // hi | lo
-constexpr int kHalfAtom = 16384;
+constexpr int kLinMaxStages = 4;
+constexpr int kLinSmemMax = 232448;  // 227 KB per CTA
 constexpr int kStageOut = 32768;    // epilogue staging (one split atom, or two bf16 tiles)
 
 enum LinearEpilogue { kEpiSplit = 0, kEpiF32 = 1, kEpiQkvSelf = 2, kEpiQkvCross = 3 };
@@ -60,41 +62,46 @@ struct LinearParams {
 };
 
 struct __align__(8) LinearBarriers {
-  uint64_t full[kLinStages];
-  uint64_t empty[kLinStages];
+  uint64_t full[kLinMaxStages];
+  uint64_t peer_full[kLinMaxStages];  // even CTA of a pair: the odd CTA's stage has landed (relayed arrival)
+  uint64_t empty[kLinMaxStages];
   uint64_t acc_full[2];
   uint64_t acc_empty[2];
   uint64_t aux_full;     // residual atom / rotary table landed
   uint32_t tmem_base;
 };
 
-template <int kNt, int kEpi>
+// kCtas == 2: a CTA pair (cluster of 2 on one TPC) computes two row tiles with one 256-row MMA; each CTA stages its
+// own A atom but only HALF of the weight atom, which cuts the L2 -> shared-memory traffic per flop by a third and
+// leaves room for a deeper ring.
+template <int kNt, int kEpi, int kCtas>
+constexpr int linear_stage_bytes() { return kSplitAtom + kNt * 256 / kCtas; }
+template <int kNt, int kEpi, int kCtas>
+constexpr int linear_fixed_bytes() {
+  return 1024 + kStageOut + (kEpi == kEpiQkvSelf ? 32768 : 0) + static_cast<int>(sizeof(LinearBarriers));
+}
+template <int kNt, int kEpi, int kCtas>
+constexpr int linear_stages() {
+  constexpr int n = (kLinSmemMax - linear_fixed_bytes<kNt, kEpi, kCtas>()) / linear_stage_bytes<kNt, kEpi, kCtas>();
+  return n > kLinMaxStages ? kLinMaxStages : n;
+}
+template <int kNt, int kEpi, int kCtas>
 constexpr int linear_smem_bytes() {
-  return 1024 + kLinStages * (kSplitAtom + kNt * 256) + kStageOut + (kEpi == kEpiQkvSelf ? 32768 : 0) +
-         static_cast<int>(sizeof(LinearBarriers));
+  return linear_fixed_bytes<kNt, kEpi, kCtas>() +
+         linear_stages<kNt, kEpi, kCtas>() * linear_stage_bytes<kNt, kEpi, kCtas>();
 }
 
-template <int N>
-__device__ __forceinline__ void bulk_wait_read() {
-  asm volatile("cp.async.bulk.wait_group.read %0;" ::"n"(N) : "memory");
+// the accumulator buffer of this CTA has been read: tell the MMA issuer (which lives in the even CTA of a pair)
+// (a remote arrive carries a cluster-scope release = MEMBAR.ALL.GPU: one lane per warp pays it)
+__device__ __forceinline__ void acc_release(uint64_t* bar, uint32_t rank) {
+  if (rank == 0) {
+    mbar_arrive(bar);
+  } else {
+    __syncwarp();
+    if ((threadIdx.x & 31) == 0) mbar_arrive_remote(bar, 0);
+  }
 }
 __device__ __forceinline__ void epi_bar_sync() { asm volatile("bar.sync 1, 128;" ::: "memory"); }
-
-// 8 fp32 -> (hi, lo) bf16x8 chunks
-__device__ __forceinline__ void split8(const float* x, uint4& hi, uint4& lo) {
-  uint32_t h[4], l[4];
-#pragma unroll
-  for (int i = 0; i < 4; ++i) {
-    const __nv_bfloat16 h0 = __float2bfloat16_rn(x[2 * i]), h1 = __float2bfloat16_rn(x[2 * i + 1]);
-    const float r0 = x[2 * i] - __bfloat162float(h0), r1 = x[2 * i + 1] - __bfloat162float(h1);
-    h[i] = static_cast<uint32_t>(__bfloat16_as_ushort(h0)) | (static_cast<uint32_t>(__bfloat16_as_ushort(h1)) << 16);
-    l[i] = pack_bf16x2(r0, r1);
-  }
-  hi = make_uint4(h[0], h[1], h[2], h[3]);
-  lo = make_uint4(l[0], l[1], l[2], l[3]);
-}
-__device__ __forceinline__ float bf16lo(uint32_t u) { return __uint_as_float(u << 16); }
-__device__ __forceinline__ float bf16hi(uint32_t u) { return __uint_as_float(u & 0xFFFF0000u); }
 
 // attention tile address of (row tile rt, head h) inside the per-side [B][H][tp][16 KB] buffers
 __device__ __forceinline__ size_t attn_tile_offset(const LinearParams& p, int rt, int h, int& side) {
@@ -104,10 +111,13 @@ __device__ __forceinline__ size_t attn_tile_offset(const LinearParams& p, int rt
   return ((static_cast<size_t>(b) * p.H + h) * tp + t) * static_cast<size_t>(kHalfAtom);
 }
 
-template <int kNt, int kEpi>
+template <int kNt, int kEpi, int kCtas>
 __global__ void __launch_bounds__(kLinThreads, 1) linear_kernel(const LinearParams p) {
   constexpr int kWAtom = kNt * 256;                       // hi | lo of one K atom of the weight tile
-  constexpr int kStage = kSplitAtom + kWAtom;
+  constexpr int kWPart = kNt * 128 / kCtas;               // this CTA's rows of the hi (or lo) half
+  constexpr int kStage = linear_stage_bytes<kNt, kEpi, kCtas>();
+  constexpr int kLinStages = linear_stages<kNt, kEpi, kCtas>();
+  static_assert(kLinStages >= 2, "ring needs two stages");
   extern __shared__ uint8_t smem_raw[];
   uint8_t* base = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
   uint8_t* ring = base;
@@ -118,17 +128,28 @@ __global__ void __launch_bounds__(kLinThreads, 1) linear_kernel(const LinearPara
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int k_atoms = p.a0_atoms + p.a1_atoms;
-  const int items = p.row_tiles * p.n_tiles;
+  // work item = (unit of kCtas adjacent row tiles, n tile); the pair walks the same item list
+  const int items = (p.row_tiles / kCtas) * p.n_tiles;
+  const uint32_t rank = kCtas == 2 ? cluster_ctarank() : 0;
+  const int first = blockIdx.x / kCtas, stride = gridDim.x / kCtas;
 
   if (threadIdx.x == 0) {
-    for (int s = 0; s < kLinStages; ++s) { mbar_init(&bar->full[s], 1); mbar_init(&bar->empty[s], 1); }
-    for (int i = 0; i < 2; ++i) { mbar_init(&bar->acc_full[i], 1); mbar_init(&bar->acc_empty[i], 128); }
+    for (int s = 0; s < kLinStages; ++s) {
+      mbar_init(&bar->full[s], 1);
+      mbar_init(&bar->peer_full[s], 1);
+      mbar_init(&bar->empty[s], 1);
+    }
+    for (int i = 0; i < 2; ++i) { mbar_init(&bar->acc_full[i], 1); mbar_init(&bar->acc_empty[i], kCtas == 2 ? 128 + 4 : 128); }
     mbar_init(&bar->aux_full, 1);
     fence_mbar_init();
   }
-  if (warp == 5) tmem_alloc<512>(&bar->tmem_base);
+  if (warp == 5) {
+    if (kCtas == 2) tmem_alloc_pair<512>(&bar->tmem_base);
+    else tmem_alloc<512>(&bar->tmem_base);
+  }
   tc_fence_before();
-  __syncthreads();
+  if (kCtas == 2) cluster_sync_all();  // peer barriers are initialised before any remote arrive / multicast commit
+  else __syncthreads();
   tc_fence_after();
   const uint32_t tmem = bar->tmem_base;
 
@@ -136,9 +157,10 @@ __global__ void __launch_bounds__(kLinThreads, 1) linear_kernel(const LinearPara
     // ------------------------------------------------------------------ producer
     if (lane == 0) {
       uint32_t it = 0;
-      for (int item = blockIdx.x; item < items; item += gridDim.x) {
-        const int rt = item / p.n_tiles, nt = item - rt * p.n_tiles;
-        const uint8_t* gw = p.w + static_cast<size_t>(nt) * k_atoms * kWAtom;
+      for (int item = first; item < items; item += stride) {
+        const int unit = item / p.n_tiles, nt = item - unit * p.n_tiles;
+        const int rt = unit * kCtas + rank;
+        const uint8_t* gw = p.w + static_cast<size_t>(nt) * k_atoms * kWAtom + rank * kWPart;
         for (int ka = 0; ka < k_atoms; ++ka, ++it) {
           const int s = it % kLinStages;
           if (it >= kLinStages) mbar_wait(&bar->empty[s], ((it / kLinStages) - 1) & 1);
@@ -148,42 +170,69 @@ __global__ void __launch_bounds__(kLinThreads, 1) linear_kernel(const LinearPara
                                   : p.a1 + (static_cast<size_t>(rt) * p.a1_atoms + (ka - p.a0_atoms)) *
                                                (hi_only ? kHalfAtom : kSplitAtom);
           const uint32_t a_bytes = hi_only ? kHalfAtom : kSplitAtom;
-          mbar_arrive_expect_tx(&bar->full[s], a_bytes + kWAtom);
+          mbar_arrive_expect_tx(&bar->full[s], a_bytes + 2 * kWPart);
           bulk_g2s(ring + s * kStage, ga, a_bytes, &bar->full[s]);
-          bulk_g2s(ring + s * kStage + kSplitAtom, gw + static_cast<size_t>(ka) * kWAtom, kWAtom, &bar->full[s]);
+          if (kCtas == 1) {
+            bulk_g2s(ring + s * kStage + kSplitAtom, gw + static_cast<size_t>(ka) * kWAtom, kWAtom, &bar->full[s]);
+          } else {  // this CTA's half of the output columns: rows [rank * Nt/2, +Nt/2) of the hi and of the lo block
+            bulk_g2s(ring + s * kStage + kSplitAtom, gw + static_cast<size_t>(ka) * kWAtom, kWPart, &bar->full[s]);
+            bulk_g2s(ring + s * kStage + kSplitAtom + kWPart, gw + static_cast<size_t>(ka) * kWAtom + kNt * 128, kWPart,
+                     &bar->full[s]);
+          }
         }
       }
     }
   } else if (warp == 5) {
     // ------------------------------------------------------------------ MMA issuer
-    {
-      const bool leader = elect_one();  // all lanes run the loop (operands stay uniform); one lane issues
-      constexpr uint32_t idesc = umma_idesc(kFmtBF16, 128, kNt);
+    const bool leader = elect_one();  // all lanes run the loop (operands stay uniform); one lane issues
+    if (kCtas == 2 && rank != 0) {
+      // odd CTA of the pair: relay "my stage has landed" to the even CTA, which issues the MMAs for both
+      uint32_t it = 0;
+      for (int item = first; item < items; item += stride) {
+        for (int ka = 0; ka < k_atoms; ++ka, ++it) {
+          const int s = it % kLinStages;
+          mbar_wait(&bar->full[s], (it / kLinStages) & 1);
+          if (leader) mbar_arrive_remote(&bar->peer_full[s], 0);
+          __syncwarp();
+        }
+      }
+    } else {
+      constexpr uint32_t idesc = umma_idesc(kFmtBF16, 128 * kCtas, kNt);
       const uint32_t ring_a = smem_u32(ring);
       uint32_t it = 0;
       int local = 0;
-      for (int item = blockIdx.x; item < items; item += gridDim.x, ++local) {
+      for (int item = first; item < items; item += stride, ++local) {
         const int buf = local & 1;
-        if (local >= 2) { mbar_wait(&bar->acc_empty[buf], ((local >> 1) - 1) & 1); tc_fence_after(); }
+        if (local >= 2) {
+          mbar_wait(&bar->acc_empty[buf], ((local >> 1) - 1) & 1);
+          tc_fence_after();
+        }
         const uint32_t acc = tmem + buf * 256;
         for (int ka = 0; ka < k_atoms; ++ka, ++it) {
           const int s = it % kLinStages;
           mbar_wait(&bar->full[s], (it / kLinStages) & 1);
+          if (kCtas == 2) mbar_wait(&bar->peer_full[s], (it / kLinStages) & 1);
           tc_fence_after();
           const bool hi_only = ka >= p.a0_atoms && p.a1_hi_only;
           const uint32_t a_hi = ring_a + s * kStage, a_lo = a_hi + kHalfAtom;
-          const uint32_t w_hi = a_hi + kSplitAtom, w_lo = w_hi + kNt * 128;
+          const uint32_t w_hi = a_hi + kSplitAtom, w_lo = w_hi + kWPart;
           const uint64_t dah = umma_desc_kmajor_sw128(a_hi), dal = umma_desc_kmajor_sw128(a_lo);
           const uint64_t dwh = umma_desc_kmajor_sw128(w_hi), dwl = umma_desc_kmajor_sw128(w_lo);
 #pragma unroll
           for (int kk = 0; kk < 4; ++kk) {  // 64 bf16 per atom = 4 x K16, 32 B per step
-            if (leader && !hi_only) umma_bf16_ss(acc, dal + 2 * kk, dwh + 2 * kk, idesc, (ka > 0 || kk > 0));
-            if (leader) umma_bf16_ss(acc, dah + 2 * kk, dwl + 2 * kk, idesc, hi_only ? (ka > 0 || kk > 0) : 1);
-            if (leader) umma_bf16_ss(acc, dah + 2 * kk, dwh + 2 * kk, idesc, 1);
+            if (kCtas == 2) {
+              if (leader && !hi_only) umma_bf16_ss_pair(acc, dal + 2 * kk, dwh + 2 * kk, idesc, (ka > 0 || kk > 0));
+              if (leader) umma_bf16_ss_pair(acc, dah + 2 * kk, dwl + 2 * kk, idesc, hi_only ? (ka > 0 || kk > 0) : 1);
+              if (leader) umma_bf16_ss_pair(acc, dah + 2 * kk, dwh + 2 * kk, idesc, 1);
+            } else {
+              if (leader && !hi_only) umma_bf16_ss(acc, dal + 2 * kk, dwh + 2 * kk, idesc, (ka > 0 || kk > 0));
+              if (leader) umma_bf16_ss(acc, dah + 2 * kk, dwl + 2 * kk, idesc, hi_only ? (ka > 0 || kk > 0) : 1);
+              if (leader) umma_bf16_ss(acc, dah + 2 * kk, dwh + 2 * kk, idesc, 1);
+            }
           }
-          if (leader) umma_commit(&bar->empty[s]);
+          if (leader) { if (kCtas == 2) umma_commit_pair(&bar->empty[s]); else umma_commit(&bar->empty[s]); }
         }
-        if (leader) umma_commit(&bar->acc_full[buf]);
+        if (leader) { if (kCtas == 2) umma_commit_pair(&bar->acc_full[buf]); else umma_commit(&bar->acc_full[buf]); }
       }
     }
   } else {
@@ -194,8 +243,9 @@ __global__ void __launch_bounds__(kLinThreads, 1) linear_kernel(const LinearPara
     uint32_t v[32];
     float f[32];
     int local = 0;
-    for (int item = blockIdx.x; item < items; item += gridDim.x, ++local) {
-      const int rt = item / p.n_tiles, nt = item - rt * p.n_tiles;
+    for (int item = first; item < items; item += stride, ++local) {
+      const int unit = item / p.n_tiles, nt = item - unit * p.n_tiles;
+      const int rt = unit * kCtas + rank;
       const int buf = local & 1;
       const uint32_t tacc = tmem + (static_cast<uint32_t>(warp * 32) << 16) + buf * 256;
       const float* bias = p.bias + nt * kNt;
@@ -228,7 +278,7 @@ __global__ void __launch_bounds__(kLinThreads, 1) linear_kernel(const LinearPara
           }
         }
         tc_fence_before();
-        mbar_arrive(&bar->acc_empty[buf]);
+        acc_release(&bar->acc_empty[buf], rank);
       } else if (kEpi == kEpiSplit) {
         const int out_atoms = p.n_tiles * (kNt / 64);
 #pragma unroll 1
@@ -247,7 +297,7 @@ __global__ void __launch_bounds__(kLinThreads, 1) linear_kernel(const LinearPara
           for (int cbh = 0; cbh < 2; ++cbh) {
             tmem_ld32(tacc + j * 64 + cbh * 32, v);
             tmem_wait_ld();
-            if (j == kNt / 64 - 1 && cbh == 1) { tc_fence_before(); mbar_arrive(&bar->acc_empty[buf]); }
+            if (j == kNt / 64 - 1 && cbh == 1) { tc_fence_before(); acc_release(&bar->acc_empty[buf], rank); }
 #pragma unroll
             for (int q = 0; q < 4; ++q) {
               uint8_t* at = stg + sw128_offset(r, cbh * 4 + q);
@@ -291,7 +341,7 @@ __global__ void __launch_bounds__(kLinThreads, 1) linear_kernel(const LinearPara
           for (int cbh = 0; cbh < 2; ++cbh) {
             tmem_ld32(tacc + part * 64 + cbh * 32, v);
             tmem_wait_ld();
-            if (part == kParts - 1 && cbh == 1) { tc_fence_before(); mbar_arrive(&bar->acc_empty[buf]); }
+            if (part == kParts - 1 && cbh == 1) { tc_fence_before(); acc_release(&bar->acc_empty[buf], rank); }
 #pragma unroll
             for (int i = 0; i < 32; ++i) f[i] = __uint_as_float(v[i]) + __ldg(bias + part * 64 + cbh * 32 + i);
             if (kEpi == kEpiQkvSelf && kind < 2) {
@@ -344,8 +394,13 @@ __global__ void __launch_bounds__(kLinThreads, 1) linear_kernel(const LinearPara
     if (leader) bulk_wait_all();
   }
   tc_fence_before();
-  __syncthreads();
-  if (warp == 5) tmem_dealloc<512>(tmem);
+  if (kCtas == 2) {
+    cluster_sync_all();  // neither CTA leaves (or frees TMEM) while the pair's MMAs / remote arrivals are in flight
+    if (warp == 5) tmem_dealloc_pair<512>(tmem);
+  } else {
+    __syncthreads();
+    if (warp == 5) tmem_dealloc<512>(tmem);
+  }
 }
 
 }  // namespace lg
@@ -491,19 +546,48 @@ static int sm_count() {
   return n;
 }
 
-template <int kNt, int kEpi>
-static int launch_linear(const LinearParams& p, cudaStream_t stream) {
-  constexpr int smem = linear_smem_bytes<kNt, kEpi>();
+template <int kNt, int kEpi, int kCtas>
+static int launch_linear_n(const LinearParams& p, cudaStream_t stream) {
+  constexpr int smem = linear_smem_bytes<kNt, kEpi, kCtas>();
+  static_assert(smem <= kLinSmemMax, "shared memory budget");
   static bool attr_done = false;
   if (!attr_done) {
-    cudaError_t e = cudaFuncSetAttribute(linear_kernel<kNt, kEpi>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
+    cudaError_t e =
+        cudaFuncSetAttribute(linear_kernel<kNt, kEpi, kCtas>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
     if (e != cudaSuccess) return static_cast<int>(e);
     attr_done = true;
   }
-  const int items = p.row_tiles * p.n_tiles;
-  const int grid = items < sm_count() ? items : sm_count();
-  linear_kernel<kNt, kEpi><<<grid, kLinThreads, smem, stream>>>(p);
-  return static_cast<int>(cudaGetLastError());
+  const int items = (p.row_tiles / kCtas) * p.n_tiles;
+  const int slots = sm_count() / kCtas;  // persistent: one CTA (or CTA pair) per SM (or TPC)
+  cudaLaunchConfig_t cfg = {};
+  cfg.gridDim = dim3(static_cast<unsigned>((items < slots ? items : slots) * kCtas));
+  cfg.blockDim = dim3(kLinThreads);
+  cfg.dynamicSmemBytes = smem;
+  cfg.stream = stream;
+  cudaLaunchAttribute attr[1];
+  attr[0].id = cudaLaunchAttributeClusterDimension;
+  attr[0].val.clusterDim.x = kCtas;
+  attr[0].val.clusterDim.y = 1;
+  attr[0].val.clusterDim.z = 1;
+  cfg.attrs = attr;
+  cfg.numAttrs = 1;
+  return static_cast<int>(cudaLaunchKernelEx(&cfg, linear_kernel<kNt, kEpi, kCtas>, p));
+}
+
+// LG_LINEAR_PAIR=0 in the environment forces the single-CTA kernels (A/B measurements)
+static bool pair_enabled() {
+  static int v = -1;
+  if (v < 0) {
+    const char* e = getenv("LG_LINEAR_PAIR");
+    v = (e && e[0] == '0') ? 0 : 1;
+  }
+  return v != 0;
+}
+
+template <int kNt, int kEpi>
+static int launch_linear(const LinearParams& p, cudaStream_t stream) {
+  if ((p.row_tiles & 1) == 0 && pair_enabled()) return launch_linear_n<kNt, kEpi, 2>(p, stream);
+  return launch_linear_n<kNt, kEpi, 1>(p, stream);
 }
 
 }  // namespace lg

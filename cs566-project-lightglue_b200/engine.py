@@ -10,9 +10,8 @@ processed as ONE activation matrix: rows = [image-0 batch (B*tp0 tiles) | image-
 Per block (self or cross):
     1. lg_linear_qkv_{self,cross}   x -> bf16 attention operand tiles (head split, rotary fused)
     2. lg_attention_tiles x2        context of image 0 / image 1 -> split tiles (K atom = head)
-    3. lg_linear_f32                [x | ctx] . W0'^T + b0' -> pre-LayerNorm h (f32 rows)
-    4. lg_ln_gelu_tiles             LayerNorm + GELU -> split tiles
-    5. lg_linear_split              x + h . W3^T + b3 -> next x (split tiles)
+    3. lg_ffn_ln_gelu               GELU(LayerNorm([x | ctx] . W0'^T + b0')) -> split tiles (one fused launch)
+    4. lg_linear_split              x + h . W3^T + b3 -> next x (split tiles)
 Step 3 uses the out_proj / to_out projection folded into ffn.0 (exact algebra, done once in fp64):
     ffn0(cat[x, Wo ctx + bo]) = W0x x + (W0m Wo) ctx + (W0m bo + b0)          (lightglue.py:190-191,246-248)
 """
@@ -86,7 +85,6 @@ class TileEngine:
         self.x_alt = C.alloc_split(self.rt, 256, device)
         self.ctx = C.alloc_split(self.rt, 256, device)
         self.h = C.alloc_split(self.rt, 512, device)
-        self.hpre = torch.empty(self.rt * C.TILE, 512, device=device, dtype=torch.float32)
         self.rot = torch.empty(self.rt, C.SPLIT_ATOM, device=device, dtype=torch.uint8)
         self.qkv = [tuple(C.alloc_tiles(B, heads, n, device) for _ in range(3)) for n in (M, N)]
         # CUDA-graph state of the layer stack (run_layers): static length buffers, the captured graph
@@ -120,8 +118,7 @@ class TileEngine:
 
     # ------------------------------------------------------------------ one transformer layer
     def _ffn(self, blk):
-        C.linear_f32(self.x, blk["w0"], blk["b0"], 512, a1=self.ctx, out=self.hpre)
-        C.ln_gelu_tiles(self.hpre, blk["ln_g"], blk["ln_b"], blk["eps"], out=self.h)
+        C.ffn_ln_gelu(self.x, blk["w0"], blk["b0"], blk["ln_g"], blk["ln_b"], blk["eps"], a1=self.ctx, out=self.h)
         C.linear_split(self.h, blk["w3"], blk["b3"], 256, resid=self.x, out=self.x_alt)
         self.x, self.x_alt = self.x_alt, self.x
 
@@ -142,7 +139,7 @@ class TileEngine:
         self._ffn(blk_c)
 
     def run_layers(self, n_layers: int, len0=None, len1=None, use_graph: bool = True):
-        """All transformer layers.  The 12 x n_layers launches are captured once per engine into a CUDA graph
+        """All transformer layers.  The 10 x n_layers launches are captured once per engine into a CUDA graph
         (streams + graphs instead of a tracing compiler) and replayed: the layer stack only touches this
         engine's own buffers, so the graph is valid for every later batch of the same shape."""
         if len0 is not None:

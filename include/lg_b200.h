@@ -82,6 +82,15 @@ int lg_rotary_tiles(const float* cos_t, const float* sin_t, void* rot_tiles, int
 int lg_ln_gelu_tiles(const float* h, const float* gamma, const float* beta, float eps, void* tiles, int rows,
                      cudaStream_t stream);
 
+/* Fused first half of the block MLP (lightglue.py:171-174 with :190-191 / :246-247 folded in):
+ *     out = GELU(LayerNorm([a0 | a1] . w^T + bias; gamma, beta, eps))        512 outputs, LayerNorm over them
+ * a0 / a1 split tiles as for lg_linear_*; w = lg_pack_weight(W (512, K), nt=256); out: split tiles
+ * [row_tiles][8][32 KB].  One CTA pair per row tile (each CTA 256 of the 512 columns, row statistics exchanged
+ * through distributed shared memory); equals lg_linear_f32 followed by lg_ln_gelu_tiles up to fp32 rounding. */
+int lg_ffn_ln_gelu(const void* a0, int a0_atoms, const void* a1, int a1_atoms, const void* w, const float* bias,
+                   const float* gamma, const float* beta, float eps, void* out_tiles, int row_tiles,
+                   cudaStream_t stream);
+
 /* y = [a0 | a1] . w^T + bias as a 3-term split-bf16 tcgen05 GEMM (nn.Linear, lightglue.py:171-176,190,246,310).
  * a0 / a1: split tiles with a0_atoms / a1_atoms K atoms (a1 NULL, 0 = none: torch.cat([x, msg], -1) of
  * lightglue.py:191,247 without the copy); a1_hi_only != 0: a1 holds plain bf16 tiles [row_tiles][a1_atoms][16 KB]

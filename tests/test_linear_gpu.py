@@ -117,6 +117,36 @@ def test_ln_gelu_tiles(C):
     assert (got - ref).abs().max() < 5e-5
 
 
+@pytest.mark.parametrize("row_tiles", [1, 2, 7, 160])
+def test_ffn_ln_gelu_fused(C, row_tiles):
+    """lg_ffn_ln_gelu == GELU(LayerNorm([x | ctx] W^T + b)) in fp64, and == the two-kernel path it replaces, on
+    rows with very different scales / offsets (exercises the cross-CTA merge of the row statistics)."""
+    g = _gen(40 + row_tiles)
+    rows = row_tiles * 128
+    scale = torch.logspace(-2, 1.5, rows)[torch.randperm(rows, generator=g)][:, None]
+    x = torch.randn(rows, 256, generator=g) * scale
+    ctx = torch.randn(rows, 256, generator=g) * scale + 0.5 * scale
+    w = torch.randn(512, 512, generator=g) * 0.06
+    w[:256] += 0.02                      # the two column halves get different means
+    b = torch.randn(512, generator=g)
+    gamma, beta = torch.randn(512, generator=g), torch.randn(512, generator=g)
+    xt = C.rows_to_tiles(x[None].cuda(), row_tiles)
+    ct = C.rows_to_tiles(ctx[None].cuda(), row_tiles)
+    wp = C.pack_weight(w.cuda())
+    got_t = C.ffn_ln_gelu(xt, wp, b.cuda(), gamma.cuda(), beta.cuda(), 1e-5, a1=ct)
+    got = C.tiles_to_rows(got_t, 1, rows, 512, row_tiles)[0].cpu()
+    # inputs as the kernel sees them (hi + lo of the split tiles), so the reference isolates the kernel's own error
+    xs = C.tiles_to_rows(xt, 1, rows, 256, row_tiles)[0].cpu().double()
+    cs = C.tiles_to_rows(ct, 1, rows, 256, row_tiles)[0].cpu().double()
+    ws = C.tiles_to_rows(C.rows_to_tiles(w[None].cuda(), 4), 1, 512, 512, 4)[0].cpu().double()
+    h = torch.cat([xs, cs], 1) @ ws.t() + b.double()
+    ref = F.gelu(F.layer_norm(h, (512,), gamma.double(), beta.double(), 1e-5))
+    assert (got.double() - ref).abs().max() < 2e-4, (got.double() - ref).abs().max()
+    two = C.ln_gelu_tiles(C.linear_f32(xt, wp, b.cuda(), 512, a1=ct), gamma.cuda(), beta.cuda(), 1e-5)
+    two = C.tiles_to_rows(two, 1, rows, 512, row_tiles)[0].cpu()
+    assert (got - two).abs().max() < 2e-4
+
+
 def _perm_qkv_self(H=4):
     """reference row h*192 + d*3 + part (lightglue.py:185) -> packed row h*192 + part*64 + d."""
     idx = torch.empty(H * 192, dtype=torch.long)
