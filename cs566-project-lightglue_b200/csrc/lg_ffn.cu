@@ -67,13 +67,29 @@ __device__ __forceinline__ void st_async_peer(void* local_slot, float value, uin
       : "memory");
 }
 
-__device__ __forceinline__ float gelu_erf(float z) { return 0.5f * z * (1.f + erff(z * 0.70710678118654752f)); }
+// GELU(z) = z/2 (1 + erf(z / sqrt 2)), erf by Abramowitz-Stegun 7.1.26 (|err| <= 1.5e-7) with the 1/sqrt 2 folded
+// into the constants: branch-free, 2 MUFU + 12 FP32 instructions.  Max abs error against fp64 GELU over [-9, 9]:
+// 4.7e-7 (torch's own fp32 erf GELU: 1.2e-6) -- below the 2^-17 relative step of the hi|lo bf16 output format.
+__device__ __forceinline__ float gelu_fast(float z) {
+  const float az = fabsf(z);
+  float t, e;
+  asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(t) : "f"(fmaf(az, 0.23164189f, 1.f)));
+  float pl = fmaf(1.061405429f, t, -1.453152027f);
+  pl = fmaf(pl, t, 1.421413741f);
+  pl = fmaf(pl, t, -0.284496736f);
+  pl = fmaf(pl, t, 0.254829592f);
+  pl *= t;
+  asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(e) : "f"(z * z * -0.72134752044448170f));
+  const float er = copysignf(fmaf(-pl, e, 1.f), z);
+  const float hz = 0.5f * z;
+  return fmaf(hz, er, hz);
+}
 
 __global__ void __launch_bounds__(kFfnThreads, 1) ffn_ln_gelu_kernel(const FfnParams p) {
   extern __shared__ __align__(1024) uint8_t smem[];
   uint8_t* ring = smem;
   uint8_t* stg = ring + kFfnStages * kFfnStage;                  // one split atom of output
-  float2* xchg = reinterpret_cast<float2*>(stg + kSplitAtom);   // [2][128]
+  float2* xchg = reinterpret_cast<float2*>(stg + kSplitAtom);   // [2][128] peer CTA's (mean, M2) per buffer
   FfnBarriers* bar = reinterpret_cast<FfnBarriers*>(stg + kSplitAtom + kFfnXchgBytes);
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
@@ -163,7 +179,8 @@ __global__ void __launch_bounds__(kFfnThreads, 1) ffn_ln_gelu_kernel(const FfnPa
       mbar_wait(&bar->acc_full[buf], par);
       tc_fence_after();
 
-      // ---- statistics of this CTA's 256 columns (both threads of a row compute them), shifted by the first element
+      // ---- statistics of this CTA's 256 columns, shifted by the first element.  Both threads of a row compute them
+      //      (an exchange inside the CTA would need 2 KB more shared memory than the 227 KB budget leaves)
       float shift = 0.f, s1 = 0.f, s2 = 0.f;
 #pragma unroll 1
       for (int cb = 0; cb < 8; ++cb) {
@@ -198,11 +215,19 @@ __global__ void __launch_bounds__(kFfnThreads, 1) ffn_ln_gelu_kernel(const FfnPa
       const float nmr = -mean * rstd;
 
       // ---- normalise, GELU, split, stage, store: 4 atoms of 64 columns; this thread's 32 columns of each
+      tmem_ld32(tacc + g * 32, v);
 #pragma unroll 1
       for (int j = 0; j < 4; ++j) {
-        tmem_ld32(tacc + j * 64 + g * 32, v);
+        uint32_t u[32];
         tmem_wait_ld();
-        if (j == 3) { tc_fence_before(); mbar_arrive(&bar->acc_empty[buf]); }
+#pragma unroll
+        for (int i = 0; i < 32; ++i) u[i] = v[i];
+        if (j < 3) {
+          tmem_ld32(tacc + (j + 1) * 64 + g * 32, v);  // next atom's columns, in flight under this atom's math
+        } else {
+          tc_fence_before();
+          mbar_arrive(&bar->acc_empty[buf]);
+        }
         uint4 hi[4], lo[4];
 #pragma unroll
         for (int c = 0; c < 4; ++c) {
@@ -216,9 +241,9 @@ __global__ void __launch_bounds__(kFfnThreads, 1) ffn_ln_gelu_kernel(const FfnPa
             const float bb[4] = {b4.x, b4.y, b4.z, b4.w}, gg[4] = {g4.x, g4.y, g4.z, g4.w}, tt[4] = {t4.x, t4.y, t4.z, t4.w};
 #pragma unroll
             for (int e = 0; e < 4; ++e) {
-              const float x = __uint_as_float(v[c * 8 + h2 * 4 + e]) + bb[e];
+              const float x = __uint_as_float(u[c * 8 + h2 * 4 + e]) + bb[e];
               const float z = fmaf(fmaf(x, rstd, nmr), gg[e], tt[e]);
-              y[h2 * 4 + e] = gelu_erf(z);
+              y[h2 * 4 + e] = gelu_fast(z);
             }
           }
           split8(y, hi[c], lo[c]);
