@@ -34,6 +34,9 @@ constexpr uint32_t kColS = 0, kColO = 384;  // TMEM column map: 3 rotating S buf
 #ifndef LG_SUMLIMIT
 #define LG_SUMLIMIT 1.152921504606846976e18f  // 2^60
 #endif
+#ifndef LG_SWEEP
+#define LG_SWEEP 2  // 0: pair-by-pair source order, 1: staged over the 32-column chunk, 2: software-pipelined groups
+#endif
 #ifndef LG_POLYEXP
 #define LG_POLYEXP 1  // 0: none, 1: 25 %, 2: 37.5 %, 3: 50 %, 4: 75 % of the exponentials on the FMA pipe
 #endif
@@ -93,8 +96,8 @@ __device__ __forceinline__ void reg_dec() { asm volatile("setmaxnreg.dec.sync.al
 #ifdef LG_ATTN_TRACE
 __device__ unsigned long long g_trace[8192];
 __device__ __forceinline__ unsigned long long gtime() {
-  unsigned long long t;
-  asm volatile("mov.u64 %0, %globaltimer;" : "=l"(t));
+  unsigned long long t;  // SM cycle counter: every traced thread lives in one CTA, reading it costs a few cycles
+  asm volatile("mov.u64 %0, %clock64;" : "=l"(t));
   return t;
 }
 #define TRACE(slot, idx) do { if (blockIdx.x == 5 && (idx) < 256) g_trace[(slot) * 256 + (idx)] = gtime(); } while (0)
@@ -211,41 +214,66 @@ __global__ void __launch_bounds__(kAttnThreads, 1) attention_kernel(const AttnPa
       const bool leader = elect_one();  // all lanes run the loop (uniform operands); one lane issues
       constexpr uint32_t idesc_qk = umma_idesc(kFmtBF16, 128, 128);
       constexpr uint32_t idesc_pv = umma_idesc(kFmtBF16, 128, 64);
-      const uint32_t aQ = smem_u32(sQ), aKV = smem_u32(sKV);
+      // Descriptors differ only in their 14-bit (address >> 4) field, which cannot carry out for addresses below
+      // 256 KB: one descriptor per operand array, plain 64-bit adds per step (the MMA warp's instruction count per
+      // step bounds how early the next similarity can be queued -- keep this loop lean).
+      const uint64_t dQ0 = umma_desc_kmajor_sw128(smem_u32(sQ));
+      const uint64_t dK0 = umma_desc_kmajor_sw128(smem_u32(sKV));
+      const uint64_t dV0 = umma_desc_kmajor_sw128(smem_u32(sKV) + kTileBytes);
 
       // Similarity cursor: runs three global steps ahead of the PV cursor, across item boundaries.
       // Global step G = (key block, query tile) pairs in issue order; S buffer = G % 3.
       int qw = blockIdx.x, q_n = 0, q_cnt = 0, q_nkt = 0;
       bool q_loaded = false;
       uint32_t q_kv = 0, G_q = 0;
-      auto issue_next_qk = [&]() {
+      // The similarity of step G+3 is issued right behind the PV of step G and BEFORE any commit: a tcgen05.commit
+      // holds the issuing thread until the queued MMAs have drained (measured ~200 cycles each), and the softmax
+      // warpgroup of the other tile is waiting for exactly this similarity.  Everything the issue needs (item
+      // decode, Q / K arrival, descriptors) is resolved by prepare_qk() before the wait for P.
+      bool qk_ready = false, qk_last = false;
+      uint64_t qk_da = 0, qk_db = 0;
+      uint32_t qk_sb = 0;
+      auto prepare_qk = [&]() {
+        qk_ready = false;
         while (!q_loaded) {
           if (qw >= p.items) return;
           const AttnItem it = attn_item(p, qw);
           if (it.skip) { qw += gridDim.x; continue; }
           q_nkt = it.nkt; q_n = 0; q_loaded = true;
           mbar_wait(&bar->q_full[q_cnt & 1], (q_cnt >> 1) & 1);
-          tc_fence_after();
         }
         const int t = q_n & 1;
-        const uint32_t kvi = q_kv + (q_n >> 1), s = kvi % kStages, sb = G_q % 3;
-        if (t == 0) { mbar_wait(&bar->kv_full[s], (kvi / kStages) & 1); tc_fence_after(); }
-        const uint64_t da = umma_desc_kmajor_sw128(aQ + ((q_cnt & 1) * 2 + t) * kTileBytes);
-        const uint64_t db = umma_desc_kmajor_sw128(aKV + s * 2 * kTileBytes);
+        const uint32_t kvi = q_kv + (q_n >> 1), s = kvi % kStages;
+        if (t == 0) mbar_wait(&bar->kv_full[s], (kvi / kStages) & 1);
+        qk_sb = G_q % 3;
+        qk_da = dQ0 + static_cast<uint64_t>(((q_cnt & 1) * 2 + t) * (kTileBytes >> 4));
+        qk_db = dK0 + static_cast<uint64_t>(s * (2 * kTileBytes >> 4));
+        qk_last = q_n + 1 == 2 * q_nkt;
+        qk_ready = true;
+      };
+      auto issue_qk = [&]() {  // MMAs only
+        if (!qk_ready) return;
 #pragma unroll
         for (int kk = 0; kk < 4; ++kk)  // K = 64 = 4 x 16, 32 B per step inside the 128 B swizzle row
-          if (leader) umma_bf16_ss(tmem + kColS + sb * 128, da + 2 * kk, db + 2 * kk, idesc_qk, kk > 0);
-        if (leader) umma_commit(&bar->s_full[sb]);
+          if (leader) umma_bf16_ss(tmem + kColS + qk_sb * 128, qk_da + 2 * kk, qk_db + 2 * kk, idesc_qk, kk > 0);
+      };
+      auto commit_qk = [&]() {
+        if (!qk_ready) return;
+        if (leader) umma_commit(&bar->s_full[qk_sb]);
         ++G_q;
-        if (++q_n == 2 * q_nkt) {  // last similarity of the item: its Q buffer is free once these retire
+        ++q_n;
+        if (qk_last) {  // last similarity of the item: its Q buffer is free once these retire
           if (leader) umma_commit(&bar->q_empty[q_cnt & 1]);
           q_kv += q_nkt; ++q_cnt; q_loaded = false; qw += gridDim.x;
         }
       };
 
-      issue_next_qk();
-      issue_next_qk();
-      issue_next_qk();
+      for (int i = 0; i < 3; ++i) {
+        prepare_qk();
+        tc_fence_after();
+        issue_qk();
+        commit_qk();
+      }
       uint32_t p_kv = 0, G_p = 0;
       int p_cnt = 0;
       for (int w = blockIdx.x; w < p.items; w += gridDim.x) {
@@ -254,22 +282,26 @@ __global__ void __launch_bounds__(kAttnThreads, 1) attention_kernel(const AttnPa
         for (int n = 0; n < 2 * it.nkt; ++n, ++G_p) {
           const int t = n & 1, j = n >> 1;
           const uint32_t kvi = p_kv + j, s = kvi % kStages;
+          // P sits in the first 64 columns of S buffer G % 3 as packed bf16 (A operand from TMEM)
+          const uint32_t tP = tmem + kColS + (G_p % 3) * 128;
+          const uint64_t dv = dV0 + static_cast<uint64_t>(s * (2 * kTileBytes >> 4));
+          prepare_qk();                         // step G+3: recycles S buffer G % 3 behind this PV
           mbar_wait(&bar->p_full[t], kvi & 1);  // P_t(j) stored in its S buffer
           if (leader) TRACE(6, G_p);
           if (j == 0 && p_cnt > 0) mbar_wait(&bar->o_free[t], (p_cnt - 1) & 1);  // previous item's O_t was read out
           tc_fence_after();
-          // P sits in the first 64 columns of S buffer G % 3 as packed bf16 (A operand from TMEM)
-          const uint32_t tP = tmem + kColS + (G_p % 3) * 128;
 #pragma unroll
           for (int kk = 0; kk < 8; ++kk) {  // K = 128 keys = 8 x 16: 8 TMEM columns / 32 B of a V^T row per step
-            const uint32_t offB = kTileBytes + (kk >> 2) * (kTileBytes / 2) + (kk & 3) * 32;
             if (leader)
-              umma_bf16_ts(tmem + kColO + t * 64, tP + kk * 8, umma_desc_kmajor_sw128(aKV + s * 2 * kTileBytes + offB),
-                           idesc_pv, (j > 0 || kk > 0));
+              umma_bf16_ts(tmem + kColO + t * 64, tP + kk * 8,
+                           dv + static_cast<uint64_t>((kk >> 2) * (kTileBytes / 2 >> 4) + (kk & 3) * 2), idesc_pv,
+                           (j > 0 || kk > 0));
           }
-          if (leader) umma_commit(&bar->pv_done[t]);
+          issue_qk();  // same-thread MMAs execute in order: the similarity overwrites the buffer after PV read P
+          if (leader) umma_commit(&bar->pv_done[t]);  // (fires after the similarity too: only the rare rescale
+                                                      // path and the item epilogue wait on it)
           if (leader && t == 1) umma_commit(&bar->kv_empty[s]);  // K_j and V_j are dead once PV1_j retires
-          issue_next_qk();  // step G+3 recycles this S buffer: same-thread MMAs execute in order
+          commit_qk();
           if (leader) TRACE(7, G_p);
         }
         p_kv += it.nkt;
@@ -370,6 +402,7 @@ __global__ void __launch_bounds__(kAttnThreads, 1) attention_kernel(const AttnPa
           const float2 nms2 = make_float2(-ms, -ms);
           const float cs252 = c * (1.f / 252.f), bs252 = fmaf(-ms, 1.f / 252.f, 0.5f);
           float2 s0 = make_float2(0.f, 0.f), s1 = make_float2(0.f, 0.f);
+#if LG_SWEEP == 0
           auto sweep = [&](uint32_t(&v)[32], const int cb) {
             if (partial) {
 #pragma unroll
@@ -402,6 +435,161 @@ __global__ void __launch_bounds__(kAttnThreads, 1) attention_kernel(const AttnPa
               pk[(cb & 1) * 16 + q * 4 + 3] = pack_bf16x2(e[6], e[7]);
             }
           };
+#else
+          // Same arithmetic, written stage by stage over the whole 32-column chunk (all scale FMAs, the polynomial
+          // pairs advanced in lock step, all MUFUs, then sums / packs) with four sum accumulators: every dependent
+          // pair of instructions is a whole stage apart.
+          float2 s2 = make_float2(0.f, 0.f), s3 = make_float2(0.f, 0.f);
+          auto sweep = [&](uint32_t(&v)[32], const int cb) {
+            if (partial) {
+#pragma unroll
+              for (int i = 0; i < 32; ++i)
+                if (cb * 32 + i >= rem) v[i] = 0xff800000u;  // -inf: exp2 -> 0
+            }
+            constexpr float kMagic126 = 12582912.f - 126.f;
+            const float2 k252 = make_float2(252.f, 252.f), km = make_float2(kMagic126, kMagic126);
+            float2 ee[16], yy[4], rr[4], fr[4], pp[4];
+            // stage A: arguments
+#pragma unroll
+            for (int pr = 0; pr < 16; ++pr) {
+              const float xa = __uint_as_float(v[2 * pr]), xb = __uint_as_float(v[2 * pr + 1]);
+              if ((pr & 3) == 3) {
+                float ya, yb;
+                asm("fma.rn.sat.f32 %0, %1, %2, %3;" : "=f"(ya) : "f"(xa), "f"(cs252), "f"(bs252));
+                asm("fma.rn.sat.f32 %0, %1, %2, %3;" : "=f"(yb) : "f"(xb), "f"(cs252), "f"(bs252));
+                yy[pr >> 2] = make_float2(ya, yb);
+              } else {
+                ee[pr] = __ffma2_rn(make_float2(xa, xb), c2, nms2);
+              }
+            }
+#pragma unroll
+            for (int k = 0; k < 4; ++k) rr[k] = __ffma2_rn(yy[k], k252, km);
+#pragma unroll
+            for (int k = 0; k < 4; ++k) fr[k] = __fadd2_rn(km, make_float2(-rr[k].x, -rr[k].y));
+            // stage B: exponentials (MUFU), polynomial steps in between
+#pragma unroll
+            for (int pr = 0; pr < 4; ++pr)
+              if ((pr & 3) != 3) ee[pr] = make_float2(ex2_approx(ee[pr].x), ex2_approx(ee[pr].y));
+#pragma unroll
+            for (int k = 0; k < 4; ++k) fr[k] = __ffma2_rn(yy[k], k252, fr[k]);
+#pragma unroll
+            for (int pr = 4; pr < 8; ++pr)
+              if ((pr & 3) != 3) ee[pr] = make_float2(ex2_approx(ee[pr].x), ex2_approx(ee[pr].y));
+#pragma unroll
+            for (int k = 0; k < 4; ++k)
+              pp[k] = __ffma2_rn(make_float2(0.0551716685f, 0.0551716685f), fr[k], make_float2(0.2426111251f, 0.2426111251f));
+#pragma unroll
+            for (int pr = 8; pr < 12; ++pr)
+              if ((pr & 3) != 3) ee[pr] = make_float2(ex2_approx(ee[pr].x), ex2_approx(ee[pr].y));
+#pragma unroll
+            for (int k = 0; k < 4; ++k) pp[k] = __ffma2_rn(pp[k], fr[k], make_float2(0.6932609677f, 0.6932609677f));
+#pragma unroll
+            for (int pr = 12; pr < 16; ++pr)
+              if ((pr & 3) != 3) ee[pr] = make_float2(ex2_approx(ee[pr].x), ex2_approx(ee[pr].y));
+#pragma unroll
+            for (int k = 0; k < 4; ++k) pp[k] = __ffma2_rn(pp[k], fr[k], make_float2(0.9999280572f, 0.9999280572f));
+#pragma unroll
+            for (int k = 0; k < 4; ++k)
+              ee[4 * k + 3] = make_float2(__int_as_float((__float_as_int(rr[k].x) << 23) + __float_as_int(pp[k].x)),
+                                          __int_as_float((__float_as_int(rr[k].y) << 23) + __float_as_int(pp[k].y)));
+            // stage C: row sums (four independent chains) and bf16 packing
+#pragma unroll
+            for (int pr = 0; pr < 16; pr += 4) {
+              s0 = __fadd2_rn(s0, ee[pr]);
+              s1 = __fadd2_rn(s1, ee[pr + 1]);
+              s2 = __fadd2_rn(s2, ee[pr + 2]);
+              s3 = __fadd2_rn(s3, ee[pr + 3]);
+            }
+            uint32_t(&pk)[32] = cb < 2 ? pk0 : pk1;  // cb is a compile-time constant after inlining
+#pragma unroll
+            for (int pr = 0; pr < 16; ++pr) pk[(cb & 1) * 16 + pr] = pack_bf16x2(ee[pr].x, ee[pr].y);
+          };
+#endif
+#if LG_SWEEP == 2
+          // Software-pipelined over the 16 groups of 8 columns (3 MUFU pairs + 1 polynomial pair each).  The MUFU
+          // unit takes a warp instruction every 8 cycles; ptxas keeps source order, so the source interleaves every
+          // MUFU of group g with the scale FMAs / polynomial chain of group g+1 and the sums / packs of group g-1.
+          {
+            constexpr float kMagic126 = 12582912.f - 126.f;
+            const float2 k252 = make_float2(252.f, 252.f), km = make_float2(kMagic126, kMagic126);
+            float2 T[16][3], E[16][4], Y[16], RR[16], FR[16], PP[16];
+            float2 s2 = make_float2(0.f, 0.f), s3 = make_float2(0.f, 0.f);
+            auto mask_chunk = [&](uint32_t(&v)[32], const int cb) {
+              if (partial) {
+#pragma unroll
+                for (int i = 0; i < 32; ++i)
+                  if (cb * 32 + i >= rem) v[i] = 0xff800000u;  // -inf: exp2 -> 0
+              }
+            };
+#define LG_V(g, i) __uint_as_float((((g) >> 2) & 1) ? vb[((g) & 3) * 8 + (i)] : va[((g) & 3) * 8 + (i)])
+#define LG_ARGS1(g)                                                                   \
+  T[g][0] = __ffma2_rn(make_float2(LG_V(g, 0), LG_V(g, 1)), c2, nms2);                \
+  T[g][1] = __ffma2_rn(make_float2(LG_V(g, 2), LG_V(g, 3)), c2, nms2);
+#define LG_ARGS2(g)                                                                   \
+  T[g][2] = __ffma2_rn(make_float2(LG_V(g, 4), LG_V(g, 5)), c2, nms2);                \
+  {                                                                                   \
+    float ya, yb;                                                                     \
+    asm("fma.rn.sat.f32 %0, %1, %2, %3;" : "=f"(ya) : "f"(LG_V(g, 6)), "f"(cs252), "f"(bs252)); \
+    asm("fma.rn.sat.f32 %0, %1, %2, %3;" : "=f"(yb) : "f"(LG_V(g, 7)), "f"(cs252), "f"(bs252)); \
+    Y[g] = make_float2(ya, yb);                                                       \
+  }
+#define LG_PA(g) RR[g] = __ffma2_rn(Y[g], k252, km);
+#define LG_PB(g) FR[g] = __fadd2_rn(km, make_float2(-RR[g].x, -RR[g].y));
+#define LG_PC(g) FR[g] = __ffma2_rn(Y[g], k252, FR[g]);
+#define LG_PD(g) PP[g] = __ffma2_rn(make_float2(0.0551716685f, 0.0551716685f), FR[g], make_float2(0.2426111251f, 0.2426111251f));
+#define LG_PE(g) PP[g] = __ffma2_rn(PP[g], FR[g], make_float2(0.6932609677f, 0.6932609677f));
+#define LG_PF(g) PP[g] = __ffma2_rn(PP[g], FR[g], make_float2(0.9999280572f, 0.9999280572f));
+#define LG_PG(g)                                                                                        \
+  E[g][3] = make_float2(__int_as_float((__float_as_int(RR[g].x) << 23) + __float_as_int(PP[g].x)),      \
+                        __int_as_float((__float_as_int(RR[g].y) << 23) + __float_as_int(PP[g].y)));
+#define LG_PK(g, k) (((g) < 8 ? pk0 : pk1)[((g) & 7) * 4 + (k)])
+            tmem_ld32(tS, va);
+            tmem_wait_ld();
+            tmem_ld32(tS + 32, vb);
+            mask_chunk(va, 0);
+            LG_ARGS1(0) LG_ARGS2(0) LG_PA(0) LG_PB(0) LG_PC(0) LG_PD(0) LG_PE(0) LG_PF(0) LG_PG(0)
+#pragma unroll
+            for (int g = 0; g < 16; ++g) {
+              if (g == 3) { tmem_wait_ld(); mask_chunk(vb, 1); }
+              if (g == 7) { tmem_wait_ld(); mask_chunk(va, 2); }
+              if (g == 11) { tmem_wait_ld(); mask_chunk(vb, 3); }
+              E[g][0].x = ex2_approx(T[g][0].x);
+              if (g + 1 < 16) { LG_ARGS1(g + 1) }
+              E[g][0].y = ex2_approx(T[g][0].y);
+              if (g + 1 < 16) { LG_ARGS2(g + 1) }
+              if (g == 3) tmem_ld32(tS + 64, va);   // va is dead: the arguments of group 3 were its last readers
+              if (g == 7) tmem_ld32(tS + 96, vb);
+              E[g][1].x = ex2_approx(T[g][1].x);
+              if (g + 1 < 16) { LG_PA(g + 1) }
+              if (g > 0) { s0 = __fadd2_rn(s0, E[g - 1][0]); LG_PK(g - 1, 0) = pack_bf16x2(E[g - 1][0].x, E[g - 1][0].y); }
+              E[g][1].y = ex2_approx(T[g][1].y);
+              if (g + 1 < 16) { LG_PB(g + 1) }
+              if (g > 0) { s1 = __fadd2_rn(s1, E[g - 1][1]); LG_PK(g - 1, 1) = pack_bf16x2(E[g - 1][1].x, E[g - 1][1].y); }
+              E[g][2].x = ex2_approx(T[g][2].x);
+              if (g + 1 < 16) { LG_PC(g + 1) LG_PD(g + 1) }
+              if (g > 0) { s2 = __fadd2_rn(s2, E[g - 1][2]); LG_PK(g - 1, 2) = pack_bf16x2(E[g - 1][2].x, E[g - 1][2].y); }
+              E[g][2].y = ex2_approx(T[g][2].y);
+              if (g + 1 < 16) { LG_PE(g + 1) LG_PF(g + 1) LG_PG(g + 1) }
+              if (g > 0) { s3 = __fadd2_rn(s3, E[g - 1][3]); LG_PK(g - 1, 3) = pack_bf16x2(E[g - 1][3].x, E[g - 1][3].y); }
+            }
+            s0 = __fadd2_rn(s0, E[15][0]); LG_PK(15, 0) = pack_bf16x2(E[15][0].x, E[15][0].y);
+            s1 = __fadd2_rn(s1, E[15][1]); LG_PK(15, 1) = pack_bf16x2(E[15][1].x, E[15][1].y);
+            s2 = __fadd2_rn(s2, E[15][2]); LG_PK(15, 2) = pack_bf16x2(E[15][2].x, E[15][2].y);
+            s3 = __fadd2_rn(s3, E[15][3]); LG_PK(15, 3) = pack_bf16x2(E[15][3].x, E[15][3].y);
+            tile_sum = ((s0.x + s0.y) + (s1.x + s1.y)) + ((s2.x + s2.y) + (s3.x + s3.y));
+#undef LG_V
+#undef LG_ARGS1
+#undef LG_ARGS2
+#undef LG_PA
+#undef LG_PB
+#undef LG_PC
+#undef LG_PD
+#undef LG_PE
+#undef LG_PF
+#undef LG_PG
+#undef LG_PK
+          }
+#else
           // TMEM loads run one 32-column chunk ahead of the arithmetic
           tmem_ld32(tS, va);
           tmem_wait_ld();
@@ -415,7 +603,12 @@ __global__ void __launch_bounds__(kAttnThreads, 1) attention_kernel(const AttnPa
           sweep(va, 2);
           tmem_wait_ld();
           sweep(vb, 3);
+#if LG_SWEEP == 0
           tile_sum = (s0.x + s0.y) + (s1.x + s1.y);
+#else
+          tile_sum = ((s0.x + s0.y) + (s1.x + s1.y)) + ((s2.x + s2.y) + (s3.x + s3.y));
+#endif
+#endif
           if (first || attempt == 1) break;
           // every P <= row sum: below the limit nothing can have overflowed the bf16 / fp32 ranges
           if (!__any_sync(0xffffffffu, !(tile_sum < kSumLimit))) break;

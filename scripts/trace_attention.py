@@ -26,3 +26,14 @@ for j in range(min(nb, 56)):
 print("item epilogues (per item: start, pv_done, o_free, stored) wg0 | wg1")
 for i in range(0, nb, 16):
     print(f"kv_base={i:3d} wg0 " + " ".join(f"{tr[8 + k, i] - t0:6d}" for k in range(4)) + " | wg1 " + " ".join(f"{tr[12 + k, i] - t0:6d}" for k in range(4)))
+
+if (tr[16] > 0).any():
+    print("wg0 inside a block: gotS | c0 loaded, sweep0, c1 loaded, sweep1, sweep2, c3 loaded, sweep3, P stored | arrive")
+    for j in range(17, 30):
+        print(f"blk={j:3d} gotS={tr[1, j] - t0:6d} | " + " ".join(f"{tr[16 + k, j] - t0:6d}" for k in range(8)) + f" | arr={tr[2, j] - t0:6d}")
+
+if (tr[24] > 0).any():
+    print("mma warp per global step G: wake | fenced | pv issued | committed | qk: kv ready | qk issued | step end")
+    for G in range(34, 60):
+        print(f"G={G:3d} t={G & 1} wake={tr[6, G] - t0:6d} fenced={tr[28, G] - t0:6d} pv={tr[24, G] - t0:6d} commit={tr[25, G] - t0:6d} "
+              f"kvready={tr[26, G] - t0:6d} qk={tr[27, G] - t0:6d} end={tr[7, G] - t0:6d}")
