@@ -73,6 +73,18 @@ __device__ __forceinline__ void mbar_arrive_remote(uint64_t* bar, uint32_t cta) 
       "r"(cta)
       : "memory");
 }
+// 32-bit store into CTA `cta`'s shared memory that completes 4 tx bytes on that CTA's mbarrier (same offsets as the
+// local `slot` / `bar`): a fence-free cross-CTA signal
+__device__ __forceinline__ void st_async_remote(void* slot, uint32_t value, uint64_t* bar, uint32_t cta) {
+  asm volatile(
+      "{\n\t.reg .b32 ra, rb;\n\t"
+      "mapa.shared::cluster.u32 ra, %0, %3;\n\t"
+      "mapa.shared::cluster.u32 rb, %2, %3;\n\t"
+      "st.async.shared::cluster.mbarrier::complete_tx::bytes.u32 [ra], %1, [rb];\n\t}" ::"r"(smem_u32(slot)),
+      "r"(value), "r"(smem_u32(bar)), "r"(cta)
+      : "memory");
+}
+
 // ----------------------------------------------------------------------------- proxies / fences
 // generic-proxy smem writes -> visible to the async proxy (UMMA / bulk copies)
 __device__ __forceinline__ void fence_proxy_async_smem() {

@@ -56,15 +56,8 @@ static_assert(kFfnSmem <= 232448, "227 KB per CTA");
 
 __device__ __forceinline__ void epi_bar_sync_256() { asm volatile("bar.sync 1, 256;" ::: "memory"); }
 
-// 32-bit store into the peer CTA's shared memory that completes 4 tx bytes on the peer's mbarrier
 __device__ __forceinline__ void st_async_peer(void* local_slot, float value, uint64_t* local_bar, uint32_t peer) {
-  asm volatile(
-      "{\n\t.reg .b32 ra, rb;\n\t"
-      "mapa.shared::cluster.u32 ra, %0, %3;\n\t"
-      "mapa.shared::cluster.u32 rb, %2, %3;\n\t"
-      "st.async.shared::cluster.mbarrier::complete_tx::bytes.u32 [ra], %1, [rb];\n\t}" ::"r"(smem_u32(local_slot)),
-      "r"(__float_as_uint(value)), "r"(smem_u32(local_bar)), "r"(peer)
-      : "memory");
+  st_async_remote(local_slot, __float_as_uint(value), local_bar, peer);
 }
 
 // GELU(z) = z/2 (1 + erf(z / sqrt 2)), erf by Abramowitz-Stegun 7.1.26 (|err| <= 1.5e-7) with the 1/sqrt 2 folded

@@ -68,7 +68,9 @@ struct __align__(8) LinearBarriers {
   uint64_t acc_full[2];
   uint64_t acc_empty[2];
   uint64_t aux_full;     // residual atom / rotary table landed
+  uint64_t resid_full[3];  // pair mode: residual atom a landed in buffer a % 3
   uint32_t tmem_base;
+  uint32_t relay_sink[kLinMaxStages];  // target words of the odd CTA's st.async relays
 };
 
 // kCtas == 2: a CTA pair (cluster of 2 on one TPC) computes two row tiles with one 256-row MMA; each CTA stages its
@@ -76,9 +78,14 @@ struct __align__(8) LinearBarriers {
 // leaves room for a deeper ring.
 template <int kNt, int kEpi, int kCtas>
 constexpr int linear_stage_bytes() { return kSplitAtom + kNt * 256 / kCtas; }
+// kEpiSplit with a CTA pair: the half-size weight stage leaves room for a double-buffered residual atom, fetched
+// one atom ahead of the epilogue (single CTA: the residual lands in the output staging buffer on demand).
+template <int kEpi, int kCtas>
+constexpr bool resid_prefetch() { return kEpi == kEpiSplit && kCtas == 2; }
 template <int kNt, int kEpi, int kCtas>
 constexpr int linear_fixed_bytes() {
-  return 1024 + kStageOut + (kEpi == kEpiQkvSelf ? 32768 : 0) + static_cast<int>(sizeof(LinearBarriers));
+  return 1024 + kStageOut + (kEpi == kEpiQkvSelf ? 32768 : 0) + (resid_prefetch<kEpi, kCtas>() ? 2 * kSplitAtom : 0) +
+         static_cast<int>(sizeof(LinearBarriers));
 }
 template <int kNt, int kEpi, int kCtas>
 constexpr int linear_stages() {
@@ -121,10 +128,10 @@ __global__ void __launch_bounds__(kLinThreads, 1) linear_kernel(const LinearPara
   extern __shared__ uint8_t smem_raw[];
   uint8_t* base = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
   uint8_t* ring = base;
-  uint8_t* stg = ring + kLinStages * kStage;              // 32 KB epilogue staging
+  uint8_t* stg = ring + kLinStages * kStage;              // 32 KB epilogue staging (kEpiSplit, pair mode: 3 x 32 KB)
   uint8_t* rot = stg + kStageOut;                         // 32 KB rotary table (kEpiQkvSelf only)
-  LinearBarriers* bar =
-      reinterpret_cast<LinearBarriers*>(stg + kStageOut + (kEpi == kEpiQkvSelf ? 32768 : 0));
+  LinearBarriers* bar = reinterpret_cast<LinearBarriers*>(
+      stg + kStageOut + (kEpi == kEpiQkvSelf ? 32768 : 0) + (resid_prefetch<kEpi, kCtas>() ? 2 * kSplitAtom : 0));
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int k_atoms = p.a0_atoms + p.a1_atoms;
@@ -141,6 +148,7 @@ __global__ void __launch_bounds__(kLinThreads, 1) linear_kernel(const LinearPara
     }
     for (int i = 0; i < 2; ++i) { mbar_init(&bar->acc_full[i], 1); mbar_init(&bar->acc_empty[i], kCtas == 2 ? 128 + 4 : 128); }
     mbar_init(&bar->aux_full, 1);
+    for (int i = 0; i < 3; ++i) mbar_init(&bar->resid_full[i], 1);
     fence_mbar_init();
   }
   if (warp == 5) {
@@ -192,7 +200,9 @@ __global__ void __launch_bounds__(kLinThreads, 1) linear_kernel(const LinearPara
         for (int ka = 0; ka < k_atoms; ++ka, ++it) {
           const int s = it % kLinStages;
           mbar_wait(&bar->full[s], (it / kLinStages) & 1);
-          if (leader) mbar_arrive_remote(&bar->peer_full[s], 0);
+          // st.async + complete_tx on the even CTA's barrier: no fence (a remote mbarrier.arrive carries a
+          // cluster-scope release = MEMBAR.ALL.GPU); the operands themselves were written by the async proxy
+          if (leader) st_async_remote(&bar->relay_sink[s], it, &bar->peer_full[s], 0);
           __syncwarp();
         }
       }
@@ -211,7 +221,10 @@ __global__ void __launch_bounds__(kLinThreads, 1) linear_kernel(const LinearPara
         for (int ka = 0; ka < k_atoms; ++ka, ++it) {
           const int s = it % kLinStages;
           mbar_wait(&bar->full[s], (it / kLinStages) & 1);
-          if (kCtas == 2) mbar_wait(&bar->peer_full[s], (it / kLinStages) & 1);
+          if (kCtas == 2) {
+            if (leader) mbar_arrive_expect_tx(&bar->peer_full[s], 4);  // armed per phase; the relay may land first
+            mbar_wait(&bar->peer_full[s], (it / kLinStages) & 1);
+          }
           tc_fence_after();
           const bool hi_only = ka >= p.a0_atoms && p.a1_hi_only;
           const uint32_t a_hi = ring_a + s * kStage, a_lo = a_hi + kHalfAtom;
@@ -240,6 +253,7 @@ __global__ void __launch_bounds__(kLinThreads, 1) linear_kernel(const LinearPara
     const int r = warp * 32 + lane;
     const bool leader = threadIdx.x == 0;
     uint32_t aux_phase = 0, sbi = 0;  // sbi: running half-buffer index of the bf16 tile staging
+    uint32_t ra = 0;                  // running residual atom index (pair mode prefetch)
     uint32_t v[32];
     float f[32];
     int local = 0;
@@ -281,18 +295,52 @@ __global__ void __launch_bounds__(kLinThreads, 1) linear_kernel(const LinearPara
         acc_release(&bar->acc_empty[buf], rank);
       } else if (kEpi == kEpiSplit) {
         const int out_atoms = p.n_tiles * (kNt / 64);
+        constexpr bool kPrefetch = resid_prefetch<kEpi, kCtas>();
+        const bool has_resid = p.resid_tiles != nullptr;
 #pragma unroll 1
         for (int j = 0; j < kNt / 64; ++j) {
           const size_t goff = (static_cast<size_t>(rt) * out_atoms + nt * (kNt / 64) + j) * kSplitAtom;
-          if (leader) {
-            bulk_wait_read<0>();  // the previous atom's store has drained the staging buffer
-            if (p.resid_tiles) {
-              mbar_arrive_expect_tx(&bar->aux_full, kSplitAtom);
-              bulk_g2s(stg, p.resid_tiles + goff, kSplitAtom, &bar->aux_full);
+          uint8_t* ob = stg;  // buffer of this atom: residual in, result in place, bulk store out
+          if (kPrefetch) {
+            // three 32 KB buffers in rotation (atom ra uses ra % 3): the residual of atom ra + 1 is fetched while atom
+            // ra is computed and atom ra - 1 is still being stored; nobody waits for the store just issued.
+            if (leader) {
+              bulk_wait_read<1>();  // stores up to atom ra - 2 have drained: buffer (ra + 1) % 3 is free
+              if (has_resid) {
+                if (ra == 0) {
+                  mbar_arrive_expect_tx(&bar->resid_full[0], kSplitAtom);
+                  bulk_g2s(stg, p.resid_tiles + goff, kSplitAtom, &bar->resid_full[0]);
+                }
+                size_t next = goff + kSplitAtom;  // next atom of this item, else atom 0 of the next item
+                bool more = true;
+                if (j == kNt / 64 - 1) {
+                  const int item2 = item + stride;
+                  more = item2 < items;
+                  const int unit2 = item2 / p.n_tiles, nt2 = item2 - unit2 * p.n_tiles;
+                  next = (static_cast<size_t>(unit2 * kCtas + rank) * out_atoms + nt2 * (kNt / 64)) * kSplitAtom;
+                }
+                if (more) {
+                  const uint32_t sl = (ra + 1) % 3;
+                  mbar_arrive_expect_tx(&bar->resid_full[sl], kSplitAtom);
+                  bulk_g2s(stg + sl * kSplitAtom, p.resid_tiles + next, kSplitAtom, &bar->resid_full[sl]);
+                }
+              }
             }
+            if (has_resid) mbar_wait(&bar->resid_full[ra % 3], (ra / 3) & 1);
+            else epi_bar_sync();
+            ob = stg + (ra % 3) * kSplitAtom;
+            ++ra;
+          } else {
+            if (leader) {
+              bulk_wait_read<0>();  // the previous atom's store has drained the staging buffer
+              if (has_resid) {
+                mbar_arrive_expect_tx(&bar->aux_full, kSplitAtom);
+                bulk_g2s(stg, p.resid_tiles + goff, kSplitAtom, &bar->aux_full);
+              }
+            }
+            if (has_resid) { mbar_wait(&bar->aux_full, aux_phase); aux_phase ^= 1; }
+            else epi_bar_sync();
           }
-          if (p.resid_tiles) { mbar_wait(&bar->aux_full, aux_phase); aux_phase ^= 1; }
-          else epi_bar_sync();
 #pragma unroll
           for (int cbh = 0; cbh < 2; ++cbh) {
             tmem_ld32(tacc + j * 64 + cbh * 32, v);
@@ -300,12 +348,12 @@ __global__ void __launch_bounds__(kLinThreads, 1) linear_kernel(const LinearPara
             if (j == kNt / 64 - 1 && cbh == 1) { tc_fence_before(); acc_release(&bar->acc_empty[buf], rank); }
 #pragma unroll
             for (int q = 0; q < 4; ++q) {
-              uint8_t* at = stg + sw128_offset(r, cbh * 4 + q);
+              uint8_t* at = ob + sw128_offset(r, cbh * 4 + q);
               float x[8];
 #pragma unroll
               for (int i = 0; i < 8; ++i)
                 x[i] = __uint_as_float(v[8 * q + i]) + __ldg(bias + j * 64 + cbh * 32 + 8 * q + i);
-              if (p.resid_tiles) {
+              if (has_resid) {
                 const uint4 rh = *reinterpret_cast<const uint4*>(at), rl = *reinterpret_cast<const uint4*>(at + kHalfAtom);
                 const uint32_t hh[4] = {rh.x, rh.y, rh.z, rh.w}, ll[4] = {rl.x, rl.y, rl.z, rl.w};
 #pragma unroll
@@ -322,7 +370,7 @@ __global__ void __launch_bounds__(kLinThreads, 1) linear_kernel(const LinearPara
           }
           fence_proxy_async_smem();
           epi_bar_sync();
-          if (leader) { bulk_s2g(p.out_tiles + goff, stg, kSplitAtom); bulk_commit(); }
+          if (leader) { bulk_s2g(p.out_tiles + goff, ob, kSplitAtom); bulk_commit(); }
         }
       } else {
         // ---------------------------------------------------------------- attention operand tiles
