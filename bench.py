@@ -237,9 +237,14 @@ def run_b200(a):
         pass
     peak = float(peaks.get("bf16_tflops_sustained", 1400.0))  # kernel timed inside a long step
     achieved = attn_flops / (attn_ms / 1e3) / 1e12
+    traffic = None  # DRAM bytes per launch of this kernel from the committed ncu --set full capture
+    try:
+        traffic = json.load(open(os.path.join(ROOT, "profiles", "r1_attention_traffic.json")))["dram_bytes_per_launch"]
+    except Exception:
+        pass
     roofline = {"kernel": "attention_kernel (tcgen05 flash attention, self + cross)", "bound": "tensor",
                 "flops": "algorithmic: 4*64*nq*nk per self launch, 3*64*nq*nk per cross direction (S counted once)",
-                "achieved": achieved, "peak": peak, "unit": "TFLOP/s", "frac": achieved / peak, "traffic": None,
+                "achieved": achieved, "peak": peak, "unit": "TFLOP/s", "frac": achieved / peak, "traffic": traffic,
                 "peak_source": "MEASURED_PEAKS.json bf16_tflops_sustained" if peaks else "fallback 1.4 PFLOP/s sustained",
                 "launches_timed": len(ev), "avg_launch_ms": attn_ms / max(len(ev), 1),
                 "share_of_step": attn_ms / max(min(a.steps, 3), 1) / (ms / a.steps)}
