@@ -44,6 +44,8 @@ SIGNATURES = {
     "lg_linear_qkv_cross": (_I, [_P, _P, _P, _P, _P, _P, _P, _I, _I, _I, _I, _P]),
     "lg_attention_tiles": (_I, [_P, _P, _P, _P, _I, _P, _P, _I, _I, _I, _I, _I, _I, _F, _P]),
     "lg_filter_matches": (_I, [_P, _L, _P, _P, _F, _P, _P, _P, _P, _P, _I, _I, _I, _P]),
+    "lg_assign_keys": (_I, [_P, _P, _P, _P, _P, _P, _F, _P, _P, _P, _I, _I, _I, _P]),
+    "lg_filter_from_keys": (_I, [_P, _P, _P, _F, _P, _P, _P, _P, _I, _I, _I, _P]),
 }
 
 _lib = None
@@ -207,6 +209,30 @@ def filter_matches(scores, th: float, m_len=None, n_len=None):
                                    _ptr(m1), _ptr(ms0), _ptr(ms1), _ptr(ws), B, M, N, _stream()), "lg_filter_matches")
     _count(2)
     return m0, m1, ms0, ms1
+
+
+def assign_and_filter(md0, md1, z0, z1, th: float, m_len=None, n_len=None, prescale=0.25):
+    """lg_assign_keys + lg_filter_from_keys: log assignment (B,M+1,N+1) and the filter_matches outputs, with the row /
+    column argmax gathered inside the assignment kernel (no second pass over the matrix)."""
+    B, M, D = md0.shape
+    N = md1.shape[1]
+    assert D == 256 and md1.shape[2] == 256
+    dev = md0.device
+    scores = torch.empty(B, M + 1, N + 1, device=dev, dtype=torch.float32)
+    ws = torch.empty(lib().lg_assign_ws_bytes(B, M, N), device=dev, dtype=torch.uint8)
+    keys = torch.empty(lib().lg_filter_ws_bytes(B, M, N), device=dev, dtype=torch.uint8)
+    ml, nl = _i32(m_len), _i32(n_len)
+    _check(lib().lg_assign_keys(_ptr(_f32c(md0, "md0")), _ptr(_f32c(md1, "md1")), _ptr(_f32c(z0, "z0")),
+                                _ptr(_f32c(z1, "z1")), _ptr(ml), _ptr(nl), float(prescale), _ptr(scores), _ptr(ws),
+                                _ptr(keys), B, M, N, _stream()), "lg_assign_keys")
+    m0 = torch.empty(B, M, device=dev, dtype=torch.int64)
+    m1 = torch.empty(B, N, device=dev, dtype=torch.int64)
+    ms0 = torch.empty(B, M, device=dev, dtype=torch.float32)
+    ms1 = torch.empty(B, N, device=dev, dtype=torch.float32)
+    _check(lib().lg_filter_from_keys(_ptr(keys), _ptr(ml), _ptr(nl), float(th), _ptr(m0), _ptr(m1), _ptr(ms0),
+                                     _ptr(ms1), B, M, N, _stream()), "lg_filter_from_keys")
+    _count(6)
+    return scores, (m0, m1, ms0, ms1)
 
 
 def token_scores(desc, w_tok, b_tok, w_match, b_match, lens=None):

@@ -64,8 +64,7 @@ def forward_adaptive(model, eng, cs0, cs1):
         elif do_point_pruning:  # nothing dropped: only the prune counters advance (lightglue.py:540,547)
             prune0[:, ind0[0]] += 1
             prune1[:, ind1[0]] += 1
-    scores = model._assign(last, eng, desc0, desc1, None, None)
-    m0, m1, ms0, ms1 = C.filter_matches(scores, conf.filter_threshold)
+    scores, (m0, m1, ms0, ms1) = model._assign(last, eng, desc0, desc1, None, None, th=conf.filter_threshold)
     if do_point_pruning:  # scatter back through ind0 / ind1 (lightglue.py:553-562)
         m0_ = torch.full((b, m), -1, device=dev, dtype=m0.dtype)
         m1_ = torch.full((b, n), -1, device=dev, dtype=m1.dtype)

@@ -17,6 +17,7 @@
 //                   shared-memory transpose so every warp stores whole 128-byte row segments.
 // Output row pitch is N+1 floats (odd): rows are not 16 B aligned, hence 4-byte coalesced stores.
 #include "lg_common.cuh"
+#include "lg_keys.cuh"
 #include "lg_b200.h"
 
 namespace lg {
@@ -70,6 +71,8 @@ struct AssignParams {
   const float* row_ls;      // pass 2: logsigmoid(z0) [B][M]
   const float* col_ls;      // pass 2: logsigmoid(z1) [B][N]
   float* scores;            // pass 2: (B, M+1, N+1)
+  unsigned long long* rowkey;  // pass 2, optional: [B][M] best (score, column) key of every row (lg_keys.cuh)
+  unsigned long long* colkey;  // pass 2, optional: [B][N] best (score, row) key of every column
   int B, M, N, rt, ct;      // sizes, tile counts
 };
 
@@ -83,7 +86,7 @@ struct __align__(8) AssignBarriers {
 
 constexpr int kTransposeBytes = (kTile * kStagePitch * 4 + 1023) & ~1023;
 constexpr int kLenCache = 1024;  // per-pair lengths of the first kLenCache pairs are cached in shared memory
-constexpr int kAssignSmem = 1024 + kAssignStages * 2 * kOperandStage + kTransposeBytes + 2 * kTile * 4 +
+constexpr int kAssignSmem = 1024 + kAssignStages * 2 * kOperandStage + kTransposeBytes + 2 * kTile * 4 + kTile * 8 +
                             2 * kLenCache * 4 + static_cast<int>(sizeof(AssignBarriers));
 
 // One similarity tile of the (b, rtile, ctile) grid, linearised with ctile fastest.
@@ -123,7 +126,8 @@ __global__ void __launch_bounds__(kAssignThreads, 1) assign_tile_kernel(const As
   uint8_t* ring = base;
   float* stage = reinterpret_cast<float*>(base + kAssignStages * 2 * kOperandStage);
   float* s_rowterm = reinterpret_cast<float*>(base + kAssignStages * 2 * kOperandStage + kTransposeBytes);  // [2][128]
-  int* s_len = reinterpret_cast<int*>(s_rowterm + 2 * kTile);                                            // [kLenCache][2]
+  unsigned long long* s_colkey = reinterpret_cast<unsigned long long*>(s_rowterm + 2 * kTile);          // [128]
+  int* s_len = reinterpret_cast<int*>(s_colkey + kTile);                                                 // [kLenCache][2]
   AssignBarriers* bar = reinterpret_cast<AssignBarriers*>(s_len + 2 * kLenCache);
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
@@ -237,7 +241,7 @@ __global__ void __launch_bounds__(kAssignThreads, 1) assign_tile_kernel(const As
       mbar_wait(&bar->acc_full, done & 1);
       tc_fence_after();
       asm volatile("bar.sync 1, 128;" ::: "memory");  // every warp is done with the previous tile's transpose buffer
-      if (kPass == 2) { s_rowterm[r] = rl; s_rowterm[kTile + r] = ra; }
+      if (kPass == 2) { s_rowterm[r] = rl; s_rowterm[kTile + r] = ra; s_colkey[r] = 0ull; }
       uint32_t v[32], w0[32], w1[32], w2[32];
       float rmax = -INFINITY, rsum = 0.f;
 #pragma unroll
@@ -296,18 +300,46 @@ __global__ void __launch_bounds__(kAssignThreads, 1) assign_tile_kernel(const As
           lb[q] = ok ? p.col_ls[static_cast<size_t>(b) * p.N + col0 + c] : 0.f;
         }
         const int rows_here = min(kTile, p.M - row0);
+        const bool keys = p.rowkey != nullptr;
+        // filter_matches (lightglue.py:321-337) needs the best column of every row and the best row of every column of
+        // the valid block: gathered here, while the scores are on chip, instead of re-reading the matrix from HBM
+        float cbv[4] = {-INFINITY, -INFINITY, -INFINITY, -INFINITY};
+        uint32_t cbi[4] = {0xFFFFFFFFu, 0xFFFFFFFFu, 0xFFFFFFFFu, 0xFFFFFFFFu};
 #pragma unroll 4
         for (int i = warp; i < rows_here; i += 4) {  // a warp stores one 512 B row segment per iteration
           const float rli = s_rowterm[i], rai = s_rowterm[kTile + i];
+          float rv = -INFINITY;
+          uint32_t rc = 0xFFFFFFFFu;
 #pragma unroll
           for (int q = 0; q < 4; ++q) {
             const int c = q * 32 + lane;
             if (col0 + c < p.N) {
               const float s = stage[i * kStagePitch + c];
-              const float val = (i < vrows && c < vcols) ? ((s - rli) + (s - lc[q])) + (rai + lb[q]) : -INFINITY;
+              const bool in = i < vrows && c < vcols;
+              const float val = in ? ((s - rli) + (s - lc[q])) + (rai + lb[q]) : -INFINITY;
               out[static_cast<int64_t>(row0 + i) * pitch + col0 + c] = val;
+              if (keys && in) {  // strict > keeps the lowest index on ties: columns ascend with q, rows with i
+                if (val > rv || rc == 0xFFFFFFFFu) { rv = val; rc = col0 + c; }
+                if (val > cbv[q] || cbi[q] == 0xFFFFFFFFu) { cbv[q] = val; cbi[q] = row0 + i; }
+              }
             }
           }
+          if (keys && i < vrows) {
+            unsigned long long k = rc == 0xFFFFFFFFu ? 0ull : make_key(rv, rc);
+#pragma unroll
+            for (int o = 16; o > 0; o >>= 1) {
+              const unsigned long long other = __shfl_xor_sync(0xffffffffu, k, o);
+              k = other > k ? other : k;
+            }
+            if (lane == 0) atomicMax(p.rowkey + static_cast<size_t>(b) * p.M + row0 + i, k);
+          }
+        }
+        if (keys) {
+#pragma unroll
+          for (int q = 0; q < 4; ++q)
+            if (cbi[q] != 0xFFFFFFFFu) atomicMax(&s_colkey[q * 32 + lane], make_key(cbv[q], cbi[q]));
+          asm volatile("bar.sync 1, 128;" ::: "memory");
+          if (r < vcols) atomicMax(p.colkey + static_cast<size_t>(b) * p.N + col0 + r, s_colkey[r]);
         }
       }
     }
@@ -380,9 +412,9 @@ extern "C" size_t lg_assign_ws_bytes(int B, int M, int N) {
   return bytes;
 }
 
-extern "C" int lg_assign(const float* md0, const float* md1, const float* z0, const float* z1, const int* m_len,
-                         const int* n_len, float prescale, float* scores, void* ws, int B, int M, int N,
-                         cudaStream_t stream) {
+static int assign_impl(const float* md0, const float* md1, const float* z0, const float* z1, const int* m_len,
+                       const int* n_len, float prescale, float* scores, void* ws, unsigned long long* rowkey,
+                       unsigned long long* colkey, int B, int M, int N, cudaStream_t stream) {
   if (!md0 || !md1 || !z0 || !z1 || !scores || !ws) return LG_ERR_NULL;
   if (B <= 0 || M <= 0 || N <= 0) return LG_ERR_SHAPE;
   const int rt = (M + 127) / 128, ct = (N + 127) / 128;
@@ -408,7 +440,7 @@ extern "C" int lg_assign(const float* md0, const float* md1, const float* z0, co
   lg::assign_pack_kernel<<<dim3(rt, B), 1024, 0, stream>>>(md0, m_len, a_tiles, M, rt, prescale);
   lg::assign_pack_kernel<<<dim3(ct, B), 1024, 0, stream>>>(md1, n_len, b_tiles, N, ct, prescale);
   lg::AssignParams p{a_tiles, b_tiles, m_len, n_len, row_part, col_part, row_lse, col_lse, row_ls, col_ls, scores,
-                     B, M, N, rt, ct};
+                     rowkey, colkey, B, M, N, rt, ct};
   int sms = 0, dev = 0;
   cudaGetDevice(&dev);
   cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
@@ -423,4 +455,22 @@ extern "C" int lg_assign(const float* md0, const float* md1, const float* z0, co
                                                                           N, rt, ct);
   lg::assign_tile_kernel<2><<<grid, lg::kAssignThreads, lg::kAssignSmem, stream>>>(p);
   return static_cast<int>(cudaGetLastError());
+}
+
+extern "C" int lg_assign(const float* md0, const float* md1, const float* z0, const float* z1, const int* m_len,
+                         const int* n_len, float prescale, float* scores, void* ws, int B, int M, int N,
+                         cudaStream_t stream) {
+  return assign_impl(md0, md1, z0, z1, m_len, n_len, prescale, scores, ws, nullptr, nullptr, B, M, N, stream);
+}
+
+extern "C" int lg_assign_keys(const float* md0, const float* md1, const float* z0, const float* z1, const int* m_len,
+                              const int* n_len, float prescale, float* scores, void* ws, void* keys_ws, int B, int M,
+                              int N, cudaStream_t stream) {
+  if (!keys_ws) return LG_ERR_NULL;
+  if (B <= 0 || M <= 0 || N <= 0) return LG_ERR_SHAPE;
+  cudaError_t e = cudaMemsetAsync(keys_ws, 0, lg_filter_ws_bytes(B, M, N), stream);
+  if (e != cudaSuccess) return static_cast<int>(e);
+  auto* rowkey = static_cast<unsigned long long*>(keys_ws);
+  return assign_impl(md0, md1, z0, z1, m_len, n_len, prescale, scores, ws, rowkey, rowkey + static_cast<size_t>(B) * M,
+                     B, M, N, stream);
 }

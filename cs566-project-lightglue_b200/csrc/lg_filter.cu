@@ -9,22 +9,10 @@
 // Pass 2 (tiny) decodes the keys, checks mutuality, applies expf + threshold, writes int64.
 // HBM-bound: algorithmic bytes = (M+1)(N+1)*4 read + (M+N)*12 written per pair.
 #include "lg_common.cuh"
+#include "lg_keys.cuh"
 #include "lg_b200.h"
 
 namespace lg {
-
-__device__ __forceinline__ unsigned long long make_key(float v, uint32_t idx) {
-  v += 0.0f;  // -0 -> +0 so that signed zeros tie like torch
-  uint32_t u = __float_as_uint(v);
-  u = (u & 0x80000000u) ? ~u : (u | 0x80000000u);
-  return (static_cast<unsigned long long>(u) << 32) | (0xFFFFFFFFu - idx);
-}
-__device__ __forceinline__ void decode_key(unsigned long long k, float& v, uint32_t& idx) {
-  uint32_t u = static_cast<uint32_t>(k >> 32);
-  u = (u & 0x80000000u) ? (u & 0x7FFFFFFFu) : ~u;
-  v = __uint_as_float(u);
-  idx = 0xFFFFFFFFu - static_cast<uint32_t>(k & 0xFFFFFFFFu);
-}
 
 constexpr int kFilterWarps = 4;
 
@@ -151,6 +139,18 @@ extern "C" int lg_filter_matches(const float* scores, int64_t pitch, const int* 
       scores, pitch, static_cast<int64_t>(M + 1) * pitch, m_len, n_len, rowkey, colkey, M, N, nsplit);
   e = cudaGetLastError();
   if (e != cudaSuccess) return static_cast<int>(e);
+  const int pts = M > N ? M : N;
+  lg::filter_finalize_kernel<<<dim3((pts + 255) / 256, B), 256, 0, stream>>>(rowkey, colkey, m_len, n_len, th, m0, m1,
+                                                                            ms0, ms1, M, N);
+  return static_cast<int>(cudaGetLastError());
+}
+
+extern "C" int lg_filter_from_keys(const void* keys_ws, const int* m_len, const int* n_len, float th, int64_t* m0,
+                                   int64_t* m1, float* ms0, float* ms1, int B, int M, int N, cudaStream_t stream) {
+  if (!keys_ws || !m0 || !m1 || !ms0 || !ms1) return LG_ERR_NULL;
+  if (B <= 0 || M <= 0 || N <= 0) return LG_ERR_SHAPE;
+  const auto* rowkey = static_cast<const unsigned long long*>(keys_ws);
+  const auto* colkey = rowkey + static_cast<size_t>(B) * M;
   const int pts = M > N ? M : N;
   lg::filter_finalize_kernel<<<dim3((pts + 255) / 256, B), 256, 0, stream>>>(rowkey, colkey, m_len, n_len, th, m0, m1,
                                                                             ms0, ms1, M, N);

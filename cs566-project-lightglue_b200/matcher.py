@@ -202,14 +202,18 @@ class LightGlue(nn.Module):
             cache.pop(next(iter(cache)))
         return eng
 
-    def _assign(self, i, eng, d0, d1, len0, len1):
+    def _assign(self, i, eng, d0, d1, len0, len1, th=None):
         """MatchAssignment.forward (lightglue.py:306-315): final_proj on tcgen05, matchability logits, then
-        the fused similarity + double log-softmax kernel."""
+        the fused similarity + double log-softmax kernel.  With `th` the same launch also gathers the row / column
+        argmax keys and filter_matches (lightglue.py:321-337) is finished from them: returns (scores, matches)."""
         head = self.log_assignment[i]
         md0, md1 = eng.final_proj(i)
         z0 = F.linear(d0, head.matchability.weight, head.matchability.bias).squeeze(-1).contiguous()
         z1 = F.linear(d1, head.matchability.weight, head.matchability.bias).squeeze(-1).contiguous()
-        return C.assign(md0, md1, z0, z1, len0, len1, prescale=self.conf.descriptor_dim ** -0.25)
+        prescale = self.conf.descriptor_dim ** -0.25
+        if th is None:
+            return C.assign(md0, md1, z0, z1, len0, len1, prescale=prescale)
+        return C.assign_and_filter(md0, md1, z0, z1, th, len0, len1, prescale=prescale)
 
     @staticmethod
     def _image_size(data, view, like):
@@ -270,8 +274,7 @@ class LightGlue(nn.Module):
         L = conf.n_layers
         eng.run_layers(L, len0, len1, use_graph=bool(conf.b200.cuda_graph))
         desc0, desc1 = eng.rows()
-        scores = self._assign(L - 1, eng, desc0, desc1, len0, len1)
-        m0, m1, ms0, ms1 = C.filter_matches(scores, conf.filter_threshold, len0, len1)
+        scores, (m0, m1, ms0, ms1) = self._assign(L - 1, eng, desc0, desc1, len0, len1, th=conf.filter_threshold)
         return {
             "matches0": m0, "matches1": m1,
             "matching_scores0": ms0, "matching_scores1": ms1,

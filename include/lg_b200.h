@@ -138,6 +138,17 @@ size_t lg_filter_ws_bytes(int B, int M, int N);
 int lg_filter_matches(const float* scores, int64_t pitch, const int* m_len, const int* n_len, float th, int64_t* m0,
                       int64_t* m1, float* ms0, float* ms1, void* ws, int B, int M, int N, cudaStream_t stream);
 
+/* (3)+(4) fused: lg_assign that also gathers, while the scores are still on chip, the best column of every row
+ * and the best row of every column of the valid block as order-preserving keys (largest score, lowest index on
+ * ties -- torch.max's choice, lightglue.py:323-324) into keys_ws (lg_filter_ws_bytes(B,M,N) bytes, zeroed by the
+ * call); lg_filter_from_keys then finishes filter_matches (mutual check, exp, threshold :325-336) without reading
+ * the (M+1)x(N+1) matrix again.  Results are bit-identical to lg_assign + lg_filter_matches. */
+int lg_assign_keys(const float* md0, const float* md1, const float* z0, const float* z1, const int* m_len,
+                   const int* n_len, float prescale, float* scores, void* ws, void* keys_ws, int B, int M, int N,
+                   cudaStream_t stream);
+int lg_filter_from_keys(const void* keys_ws, const int* m_len, const int* n_len, float th, int64_t* m0, int64_t* m1,
+                        float* ms0, float* ms1, int B, int M, int N, cudaStream_t stream);
+
 /* (5) adaptive depth / width (lightglue.py:527-547).
  * lg_token_scores: conf (B,N) = sigmoid(w_tok.desc + b_tok) (TokenConfidence.forward :102-107; w_tok NULL
  *   => skipped) and match (B,N) = sigmoid(w_match.desc + b_match) (get_matchability :317-318), one read

@@ -286,3 +286,29 @@ def test_token_scores_and_gather(C):
         want = prune[b].clone()
         want[ind[b].index_select(0, sel)] += 1
         assert torch.equal(pr[b].cpu(), want)
+
+
+@pytest.mark.parametrize("B,M,N,varlen", [(1, 300, 200, False), (2, 257, 640, True), (1, 128, 128, False), (2, 97, 130, True)])
+def test_assign_keys_equals_assign_plus_filter(B, M, N, varlen):
+    """lg_assign_keys + lg_filter_from_keys == lg_assign + lg_filter_matches, bit for bit (scores and all four
+    filter outputs), including ties (duplicated descriptors) and variable-length batches."""
+    C = pkg("_cabi")
+    g = torch.Generator().manual_seed(B * 1000 + M + N)
+    md0 = torch.randn(B, M, 256, generator=g)
+    md1 = torch.randn(B, N, 256, generator=g)
+    md1[:, 5] = md1[:, 3]            # equal columns -> ties in every row
+    md0[:, 7] = md0[:, 2]            # equal rows -> ties in every column
+    md1[:, : min(M, N) // 2] += 2.0 * md0[:, : min(M, N) // 2]   # real matches
+    z0, z1 = torch.randn(B, M, generator=g), torch.randn(B, N, generator=g)
+    z1[:, 5] = z1[:, 3]
+    z0[:, 7] = z0[:, 2]
+    ml = torch.tensor([M, max(1, M - 70)][:B], dtype=torch.int32).cuda() if varlen else None
+    nl = torch.tensor([max(1, N - 150), N][:B], dtype=torch.int32).cuda() if varlen else None
+    args = (md0.cuda(), md1.cuda(), z0.cuda(), z1.cuda())
+    s_ref = C.assign(*args, ml, nl)
+    f_ref = C.filter_matches(s_ref, 0.05, ml, nl)
+    s_new, f_new = C.assign_and_filter(*args, 0.05, ml, nl)
+    assert torch.equal(s_ref, s_new)
+    for a, b in zip(f_ref, f_new):
+        assert torch.equal(a, b)
+    assert (f_new[0] >= 0).sum() > 0
