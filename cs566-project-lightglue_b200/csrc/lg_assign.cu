@@ -325,13 +325,13 @@ __global__ void __launch_bounds__(kAssignThreads, 1) assign_tile_kernel(const As
             }
           }
           if (keys && i < vrows) {
-            unsigned long long k = rc == 0xFFFFFFFFu ? 0ull : make_key(rv, rc);
-#pragma unroll
-            for (int o = 16; o > 0; o >>= 1) {
-              const unsigned long long other = __shfl_xor_sync(0xffffffffu, k, o);
-              k = other > k ? other : k;
-            }
-            if (lane == 0) atomicMax(p.rowkey + static_cast<size_t>(b) * p.M + row0 + i, k);
+            // warp argmax in two redux steps: largest value, then the lowest column among the lanes that hold it
+            const uint32_t u = rc == 0xFFFFFFFFu ? 0u : orderable_f32(rv);
+            const uint32_t um = __reduce_max_sync(0xffffffffu, u);
+            const uint32_t cm = __reduce_min_sync(0xffffffffu, u == um ? rc : 0xFFFFFFFFu);
+            if (lane == 0 && cm != 0xFFFFFFFFu)
+              atomicMax(p.rowkey + static_cast<size_t>(b) * p.M + row0 + i,
+                        (static_cast<unsigned long long>(um) << 32) | (0xFFFFFFFFu - cm));
           }
         }
         if (keys) {

@@ -6,11 +6,13 @@
 
 namespace lg {
 
-__device__ __forceinline__ unsigned long long make_key(float v, uint32_t idx) {
+__device__ __forceinline__ uint32_t orderable_f32(float v) {  // monotone float -> uint32 map
   v += 0.0f;  // -0 -> +0 so that signed zeros tie like torch
-  uint32_t u = __float_as_uint(v);
-  u = (u & 0x80000000u) ? ~u : (u | 0x80000000u);
-  return (static_cast<unsigned long long>(u) << 32) | (0xFFFFFFFFu - idx);
+  const uint32_t u = __float_as_uint(v);
+  return (u & 0x80000000u) ? ~u : (u | 0x80000000u);
+}
+__device__ __forceinline__ unsigned long long make_key(float v, uint32_t idx) {
+  return (static_cast<unsigned long long>(orderable_f32(v)) << 32) | (0xFFFFFFFFu - idx);
 }
 __device__ __forceinline__ void decode_key(unsigned long long k, float& v, uint32_t& idx) {
   uint32_t u = static_cast<uint32_t>(k >> 32);
