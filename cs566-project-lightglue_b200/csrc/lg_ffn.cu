@@ -54,6 +54,18 @@ constexpr int kFfnXchgBytes = 2 * kTile * 8;  // [buf][row] (mean, M2)
 constexpr int kFfnSmem = kFfnStages * kFfnStage + kSplitAtom + kFfnXchgBytes + static_cast<int>(sizeof(FfnBarriers));
 static_assert(kFfnSmem <= 232448, "227 KB per CTA");
 
+#ifdef LG_FFN_TRACE
+__device__ unsigned long long g_ffn_trace[16 * 64];
+__device__ __forceinline__ unsigned long long ffn_clock() {
+  unsigned long long t;
+  asm volatile("mov.u64 %0, %%clock64;" : "=l"(t));
+  return t;
+}
+#define FTRACE(slot, idx) do { if (blockIdx.x == 8 && (idx) < 64) g_ffn_trace[(slot) * 64 + (idx)] = ffn_clock(); } while (0)
+#else
+#define FTRACE(slot, idx) do {} while (0)
+#endif
+
 __device__ __forceinline__ void epi_bar_sync_256() { asm volatile("bar.sync 1, 256;" ::: "memory"); }
 
 __device__ __forceinline__ void st_async_peer(void* local_slot, float value, uint64_t* local_bar, uint32_t peer) {
@@ -76,6 +88,29 @@ __device__ __forceinline__ float gelu_fast(float z) {
   const float er = copysignf(fmaf(-pl, e, 1.f), z);
   const float hz = 0.5f * z;
   return fmaf(hz, er, hz);
+}
+
+// two elements at a time: the FP32 part as packed f32x2 instructions
+__device__ __forceinline__ float2 gelu_fast2(float2 z) {
+  const float2 d = __ffma2_rn(make_float2(fabsf(z.x), fabsf(z.y)), make_float2(0.23164189f, 0.23164189f),
+                              make_float2(1.f, 1.f));
+  float2 t, e;
+  asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(t.x) : "f"(d.x));
+  asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(t.y) : "f"(d.y));
+  // -(polynomial): the sign of 1 - pl * e is folded into the coefficients
+  float2 pl = __ffma2_rn(make_float2(-1.061405429f, -1.061405429f), t, make_float2(1.453152027f, 1.453152027f));
+  pl = __ffma2_rn(pl, t, make_float2(-1.421413741f, -1.421413741f));
+  pl = __ffma2_rn(pl, t, make_float2(0.284496736f, 0.284496736f));
+  pl = __ffma2_rn(pl, t, make_float2(-0.254829592f, -0.254829592f));
+  pl = __fmul2_rn(pl, t);
+  const float2 a = __fmul2_rn(__fmul2_rn(z, z), make_float2(-0.72134752044448170f, -0.72134752044448170f));
+  asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(e.x) : "f"(a.x));
+  asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(e.y) : "f"(a.y));
+  float2 er = __ffma2_rn(pl, e, make_float2(1.f, 1.f));
+  er.x = copysignf(er.x, z.x);
+  er.y = copysignf(er.y, z.y);
+  const float2 hz = __fmul2_rn(z, make_float2(0.5f, 0.5f));
+  return __ffma2_rn(hz, er, hz);
 }
 
 __global__ void __launch_bounds__(kFfnThreads, 1) ffn_ln_gelu_kernel(const FfnParams p) {
@@ -136,6 +171,7 @@ __global__ void __launch_bounds__(kFfnThreads, 1) ffn_ln_gelu_kernel(const FfnPa
       const int buf = local & 1;
       if (local >= 2) { mbar_wait(&bar->acc_empty[buf], ((local >> 1) - 1) & 1); tc_fence_after(); }
       const uint32_t acc = tmem + buf * 256;
+      if (leader) FTRACE(0, local);
       for (int ka = 0; ka < k_atoms; ++ka, ++it) {
         const int s = it % kFfnStages;
         mbar_wait(&bar->full[s], (it / kFfnStages) & 1);
@@ -153,6 +189,7 @@ __global__ void __launch_bounds__(kFfnThreads, 1) ffn_ln_gelu_kernel(const FfnPa
         if (leader) umma_commit(&bar->empty[s]);
       }
       if (leader) umma_commit(&bar->acc_full[buf]);
+      if (leader) FTRACE(1, local);
     }
   } else {
     // ------------------------------------------------------------------ epilogue: 2 threads per row
@@ -169,46 +206,74 @@ __global__ void __launch_bounds__(kFfnThreads, 1) ffn_ln_gelu_kernel(const FfnPa
       const uint32_t par = (local >> 1) & 1;
       const uint32_t tacc = tmem + (static_cast<uint32_t>(q * 32) << 16) + buf * 256;
       if (leader) mbar_arrive_expect_tx(&bar->xchg_full[buf], kTile * 8);
+      if (leader) FTRACE(2, local);
       mbar_wait(&bar->acc_full[buf], par);
       tc_fence_after();
+      if (leader) FTRACE(3, local);
 
-      // ---- statistics of this CTA's 256 columns, shifted by the first element.  Both threads of a row compute them
-      //      (an exchange inside the CTA would need 2 KB more shared memory than the 227 KB budget leaves)
-      float shift = 0.f, s1 = 0.f, s2 = 0.f;
-#pragma unroll 1
-      for (int cb = 0; cb < 8; ++cb) {
-        tmem_ld32(tacc + cb * 32, v);
+      // ---- statistics: each of the two threads of a row reduces 128 of this CTA's 256 columns (shifted by its first
+      //      element, packed f32x2 arithmetic), the halves meet through the idle staging buffer, the CTA's (mean, M2)
+      //      goes to the peer
+      const float* bias_h = bias + g * 128;
+      float shift;
+      float2 s1 = make_float2(0.f, 0.f), s2 = make_float2(0.f, 0.f);
+      {
+        uint32_t u[32];
+        tmem_ld32(tacc + g * 128, v);
         tmem_wait_ld();
-        if (cb == 0) shift = __uint_as_float(v[0]) + __ldg(bias);
+        shift = __uint_as_float(v[0]) + __ldg(bias_h);
+        const float2 nshift = make_float2(-shift, -shift);
+#pragma unroll 1
+        for (int cb = 0; cb < 4; ++cb) {
 #pragma unroll
-        for (int i4 = 0; i4 < 8; ++i4) {
-          const float4 b4 = __ldg(reinterpret_cast<const float4*>(bias + cb * 32) + i4);
-          const float bb[4] = {b4.x, b4.y, b4.z, b4.w};
+          for (int i = 0; i < 32; ++i) u[i] = v[i];
+          if (cb < 3) tmem_ld32(tacc + g * 128 + (cb + 1) * 32, v);
 #pragma unroll
-          for (int e = 0; e < 4; ++e) {
-            const float d = (__uint_as_float(v[4 * i4 + e]) + bb[e]) - shift;
-            s1 += d;
-            s2 = fmaf(d, d, s2);
+          for (int i4 = 0; i4 < 8; ++i4) {
+            const float4 b4 = __ldg(reinterpret_cast<const float4*>(bias_h + cb * 32) + i4);
+            const float2 bs0 = __fadd2_rn(make_float2(b4.x, b4.y), nshift);
+            const float2 bs1 = __fadd2_rn(make_float2(b4.z, b4.w), nshift);
+            const float2 d0 = __fadd2_rn(make_float2(__uint_as_float(u[4 * i4]), __uint_as_float(u[4 * i4 + 1])), bs0);
+            const float2 d1 =
+                __fadd2_rn(make_float2(__uint_as_float(u[4 * i4 + 2]), __uint_as_float(u[4 * i4 + 3])), bs1);
+            s1 = __fadd2_rn(s1, d0);
+            s2 = __ffma2_rn(d0, d0, s2);
+            s1 = __fadd2_rn(s1, d1);
+            s2 = __ffma2_rn(d1, d1, s2);
           }
+          if (cb < 3) tmem_wait_ld();
         }
       }
-      const float dm = s1 * (1.f / 256.f);
-      const float mean_c = shift + dm;
-      const float m2_c = fmaxf(s2 - s1 * dm, 0.f);
+      tmem_ld32(tacc + g * 32, v);  // pass B's first atom, in flight under the exchanges
+      const float s1h = s1.x + s1.y, s2h = s2.x + s2.y;
+      const float dmh = s1h * (1.f / 128.f);
+      const float mean_h = shift + dmh;
+      const float m2_h = fmaxf(s2h - s1h * dmh, 0.f);
+      float2* halves = reinterpret_cast<float2*>(stg);  // [2][128]
+      if (leader) bulk_wait_read<0>();                  // the previous tile's last store has left the buffer
+      epi_bar_sync_256();
+      halves[g * kTile + r] = make_float2(mean_h, m2_h);
+      epi_bar_sync_256();
+      const float2 other = halves[(g ^ 1) * kTile + r];
+      const float dh = mean_h - other.x;
+      const float mean_c = 0.5f * (mean_h + other.x);
+      const float m2_c = m2_h + other.y + dh * dh * 64.f;
       if (g == 0) {
         st_async_peer(&xchg[buf * kTile + r].x, mean_c, &bar->xchg_full[buf], rank ^ 1);
         st_async_peer(&xchg[buf * kTile + r].y, m2_c, &bar->xchg_full[buf], rank ^ 1);
       }
+      if (leader) FTRACE(4, local);
       mbar_wait(&bar->xchg_full[buf], par);
+      if (leader) FTRACE(5, local);
       const float2 peer = xchg[buf * kTile + r];
       const float mean = 0.5f * (mean_c + peer.x);
       const float dmm = mean_c - peer.x;
       const float var = (m2_c + peer.y + dmm * dmm * 128.f) * (1.f / 512.f);
       const float rstd = rsqrtf(var + p.eps);
       const float nmr = -mean * rstd;
+      const float2 rstd2 = make_float2(rstd, rstd), nmr2 = make_float2(nmr, nmr);
 
       // ---- normalise, GELU, split, stage, store: 4 atoms of 64 columns; this thread's 32 columns of each
-      tmem_ld32(tacc + g * 32, v);
 #pragma unroll 1
       for (int j = 0; j < 4; ++j) {
         uint32_t u[32];
@@ -225,19 +290,19 @@ __global__ void __launch_bounds__(kFfnThreads, 1) ffn_ln_gelu_kernel(const FfnPa
 #pragma unroll
         for (int c = 0; c < 4; ++c) {
           const int col = j * 64 + g * 32 + c * 8;
-          float y[8];
+          float2 y[4];
 #pragma unroll
           for (int h2 = 0; h2 < 2; ++h2) {
             const float4 b4 = __ldg(reinterpret_cast<const float4*>(bias + col) + h2);
             const float4 g4 = __ldg(reinterpret_cast<const float4*>(gamma + col) + h2);
             const float4 t4 = __ldg(reinterpret_cast<const float4*>(beta + col) + h2);
-            const float bb[4] = {b4.x, b4.y, b4.z, b4.w}, gg[4] = {g4.x, g4.y, g4.z, g4.w}, tt[4] = {t4.x, t4.y, t4.z, t4.w};
-#pragma unroll
-            for (int e = 0; e < 4; ++e) {
-              const float x = __uint_as_float(u[c * 8 + h2 * 4 + e]) + bb[e];
-              const float z = fmaf(fmaf(x, rstd, nmr), gg[e], tt[e]);
-              y[h2 * 4 + e] = gelu_fast(z);
-            }
+            const uint32_t* uu = u + c * 8 + h2 * 4;
+            const float2 x0 = __fadd2_rn(make_float2(__uint_as_float(uu[0]), __uint_as_float(uu[1])), make_float2(b4.x, b4.y));
+            const float2 x1 = __fadd2_rn(make_float2(__uint_as_float(uu[2]), __uint_as_float(uu[3])), make_float2(b4.z, b4.w));
+            const float2 z0 = __ffma2_rn(__ffma2_rn(x0, rstd2, nmr2), make_float2(g4.x, g4.y), make_float2(t4.x, t4.y));
+            const float2 z1 = __ffma2_rn(__ffma2_rn(x1, rstd2, nmr2), make_float2(g4.z, g4.w), make_float2(t4.z, t4.w));
+            y[h2 * 2] = gelu_fast2(z0);
+            y[h2 * 2 + 1] = gelu_fast2(z1);
           }
           split8(y, hi[c], lo[c]);
         }
@@ -254,6 +319,7 @@ __global__ void __launch_bounds__(kFfnThreads, 1) ffn_ln_gelu_kernel(const FfnPa
         if (leader) {
           bulk_s2g(p.out_tiles + (static_cast<size_t>(rt) * 8 + rank * 4 + j) * kSplitAtom, stg, kSplitAtom);
           bulk_commit();
+          FTRACE(6 + j, local);
         }
       }
     }
@@ -315,3 +381,9 @@ extern "C" int lg_ffn_ln_gelu(const void* a0, int a0_atoms, const void* a1, int 
   cfg.numAttrs = 1;
   return static_cast<int>(cudaLaunchKernelEx(&cfg, lg::ffn_ln_gelu_kernel, p));
 }
+
+#ifdef LG_FFN_TRACE
+extern "C" int lg_debug_ffn_trace(unsigned long long* host_out, int n) {
+  return static_cast<int>(cudaMemcpyFromSymbol(host_out, lg::g_ffn_trace, sizeof(unsigned long long) * n));
+}
+#endif

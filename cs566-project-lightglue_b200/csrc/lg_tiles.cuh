@@ -25,6 +25,18 @@ __device__ __forceinline__ void split8(const float* x, uint4& hi, uint4& lo) {
   hi = make_uint4(h[0], h[1], h[2], h[3]);
   lo = make_uint4(l[0], l[1], l[2], l[3]);
 }
+// the same on 4 packed pairs: 1 F2FP + 2 bit ops + 1 FADD2 + 1 F2FP per pair
+__device__ __forceinline__ void split8(const float2* x, uint4& hi, uint4& lo) {
+  uint32_t h[4], l[4];
+#pragma unroll
+  for (int i = 0; i < 4; ++i) {
+    h[i] = pack_bf16x2(x[i].x, x[i].y);
+    const float2 r = __fadd2_rn(x[i], make_float2(-__uint_as_float(h[i] << 16), -__uint_as_float(h[i] & 0xFFFF0000u)));
+    l[i] = pack_bf16x2(r.x, r.y);
+  }
+  hi = make_uint4(h[0], h[1], h[2], h[3]);
+  lo = make_uint4(l[0], l[1], l[2], l[3]);
+}
 __device__ __forceinline__ float bf16lo(uint32_t u) { return __uint_as_float(u << 16); }
 __device__ __forceinline__ float bf16hi(uint32_t u) { return __uint_as_float(u & 0xFFFF0000u); }
 
