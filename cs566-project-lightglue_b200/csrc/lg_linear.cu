@@ -16,11 +16,12 @@
 // so one flat bulk (TMA engine) copy stages a 32 KB hi|lo atom.  Weights [Nout][K] are packed once
 // as [N tile][K atom][hi | lo][Nt x 128 B] in the same pattern (lg_pack_weight).
 //
-// One persistent CTA per SM, 192 threads:
-//   warp 4 (one lane)  producer: bulk copies A atom (32 KB) + W atom into a 2-stage ring
-//   warp 5 (one lane)  tcgen05.mma issue, 128 x Nt x 16 per instruction, 12 per stage;
+// One persistent CTA per SM (or CTA pair per TPC), 320 threads:
+//   warp 8 (one lane)  producer: bulk copies A atom (32 KB) + W atom into a 2..4-stage ring
+//   warp 9 (one lane)  tcgen05.mma issue, 128 (pair: 256) x Nt x 16 per instruction, 12 per stage;
 //                      two TMEM accumulators (2 x 256 columns) so tile i+1 accumulates while
-//   warps 0-3          the epilogue of tile i runs (thread == row == TMEM lane)
+//   warps 0-7          the epilogue of tile i runs: 2 threads per row (= TMEM lane), 32 of every 64 columns each
+//                      (4 warps were not enough: at K = 256 the epilogue, not the MMA, set the tile period)
 // Epilogues (template): split tiles (+bias, +residual), fp32 rows, and the attention operand
 // producers (self: de-interleaved Wqkv + rotary; cross: to_qk | to_v) that write the bf16
 // Q / K / V^T tiles lg_attention consumes, through shared-memory staging + bulk stores.
@@ -32,7 +33,7 @@
 
 namespace lg {
 
-constexpr int kLinThreads = 192;
+constexpr int kLinThreads = 320;  // warps 0-7 epilogue, 8 producer, 9 MMA issue
 constexpr int kLinMaxStages = 4;
 constexpr int kLinSmemMax = 232448;  // 227 KB per CTA
 constexpr int kStageOut = 32768;    // epilogue staging (one split atom, or two bf16 tiles)
@@ -108,7 +109,7 @@ __device__ __forceinline__ void acc_release(uint64_t* bar, uint32_t rank) {
     if ((threadIdx.x & 31) == 0) mbar_arrive_remote(bar, 0);
   }
 }
-__device__ __forceinline__ void epi_bar_sync() { asm volatile("bar.sync 1, 128;" ::: "memory"); }
+__device__ __forceinline__ void epi_bar_sync() { asm volatile("bar.sync 1, 256;" ::: "memory"); }
 
 // attention tile address of (row tile rt, head h) inside the per-side [B][H][tp][16 KB] buffers
 __device__ __forceinline__ size_t attn_tile_offset(const LinearParams& p, int rt, int h, int& side) {
@@ -146,12 +147,12 @@ __global__ void __launch_bounds__(kLinThreads, 1) linear_kernel(const LinearPara
       mbar_init(&bar->peer_full[s], 1);
       mbar_init(&bar->empty[s], 1);
     }
-    for (int i = 0; i < 2; ++i) { mbar_init(&bar->acc_full[i], 1); mbar_init(&bar->acc_empty[i], kCtas == 2 ? 128 + 4 : 128); }
+    for (int i = 0; i < 2; ++i) { mbar_init(&bar->acc_full[i], 1); mbar_init(&bar->acc_empty[i], kCtas == 2 ? 256 + 8 : 256); }
     mbar_init(&bar->aux_full, 1);
     for (int i = 0; i < 3; ++i) mbar_init(&bar->resid_full[i], 1);
     fence_mbar_init();
   }
-  if (warp == 5) {
+  if (warp == 9) {
     if (kCtas == 2) tmem_alloc_pair<512>(&bar->tmem_base);
     else tmem_alloc<512>(&bar->tmem_base);
   }
@@ -161,7 +162,7 @@ __global__ void __launch_bounds__(kLinThreads, 1) linear_kernel(const LinearPara
   tc_fence_after();
   const uint32_t tmem = bar->tmem_base;
 
-  if (warp == 4) {
+  if (warp == 8) {
     // ------------------------------------------------------------------ producer
     if (lane == 0) {
       uint32_t it = 0;
@@ -190,7 +191,7 @@ __global__ void __launch_bounds__(kLinThreads, 1) linear_kernel(const LinearPara
         }
       }
     }
-  } else if (warp == 5) {
+  } else if (warp == 9) {
     // ------------------------------------------------------------------ MMA issuer
     const bool leader = elect_one();  // all lanes run the loop (operands stay uniform); one lane issues
     if (kCtas == 2 && rank != 0) {
@@ -249,20 +250,23 @@ __global__ void __launch_bounds__(kLinThreads, 1) linear_kernel(const LinearPara
       }
     }
   } else {
-    // ------------------------------------------------------------------ epilogue: thread == row
-    const int r = warp * 32 + lane;
+    // ------------------------------------------------------------------ epilogue: 2 threads per row; thread (r, g)
+    // owns columns [32 g, 32 g + 32) of every 64-column group.  TMEM loads run one group ahead of the arithmetic
+    // (packed f32x2 instructions throughout).
+    const int q = warp & 3, g = warp >> 2;
+    const int r = q * 32 + lane;
     const bool leader = threadIdx.x == 0;
+    constexpr int kGroups = kNt / 64;
     uint32_t aux_phase = 0, sbi = 0;  // sbi: running half-buffer index of the bf16 tile staging
     uint32_t ra = 0;                  // running residual atom index (pair mode prefetch)
-    uint32_t v[32];
-    float f[32];
+    uint32_t v[32], u[32];
     int local = 0;
     for (int item = first; item < items; item += stride, ++local) {
       const int unit = item / p.n_tiles, nt = item - unit * p.n_tiles;
       const int rt = unit * kCtas + rank;
       const int buf = local & 1;
-      const uint32_t tacc = tmem + (static_cast<uint32_t>(warp * 32) << 16) + buf * 256;
-      const float* bias = p.bias + nt * kNt;
+      const uint32_t tacc = tmem + (static_cast<uint32_t>(q * 32) << 16) + buf * 256 + g * 32;
+      const float* bias = p.bias + nt * kNt + g * 32;
 
       if (kEpi == kEpiQkvSelf) {
         // rotary table of this row tile (all reads of the previous table ended before the
@@ -274,32 +278,50 @@ __global__ void __launch_bounds__(kLinThreads, 1) linear_kernel(const LinearPara
       }
       mbar_wait(&bar->acc_full[buf], (local >> 1) & 1);
       tc_fence_after();
+      tmem_ld32(tacc, v);
+      // group j of the accumulator -> u (+ nothing yet); group j + 1 requested; after the last group the buffer is free
+      auto next_group = [&](int j) {
+        tmem_wait_ld();
+#pragma unroll
+        for (int i = 0; i < 32; ++i) u[i] = v[i];
+        if (j + 1 < kGroups) {
+          tmem_ld32(tacc + (j + 1) * 64, v);
+        } else {
+          tc_fence_before();
+          acc_release(&bar->acc_empty[buf], rank);
+        }
+      };
+      // x[0..3] = columns [8 c, 8 c + 8) of this thread's 32 of group j, bias added
+      auto biased8 = [&](int j, int c, float2* x) {
+        const float4 b0 = __ldg(reinterpret_cast<const float4*>(bias + j * 64 + c * 8));
+        const float4 b1 = __ldg(reinterpret_cast<const float4*>(bias + j * 64 + c * 8) + 1);
+        const uint32_t* uu = u + c * 8;
+        x[0] = __fadd2_rn(make_float2(__uint_as_float(uu[0]), __uint_as_float(uu[1])), make_float2(b0.x, b0.y));
+        x[1] = __fadd2_rn(make_float2(__uint_as_float(uu[2]), __uint_as_float(uu[3])), make_float2(b0.z, b0.w));
+        x[2] = __fadd2_rn(make_float2(__uint_as_float(uu[4]), __uint_as_float(uu[5])), make_float2(b1.x, b1.y));
+        x[3] = __fadd2_rn(make_float2(__uint_as_float(uu[6]), __uint_as_float(uu[7])), make_float2(b1.z, b1.w));
+      };
 
       if (kEpi == kEpiF32) {
-        float* dst = p.out_f32 + (static_cast<int64_t>(rt) * kTile + r) * p.ld + nt * kNt;
+        float* dst = p.out_f32 + (static_cast<int64_t>(rt) * kTile + r) * p.ld + nt * kNt + g * 32;
 #pragma unroll 1
-        for (int cb = 0; cb < kNt / 32; ++cb) {
-          tmem_ld32(tacc + cb * 32, v);
-          tmem_wait_ld();
+        for (int j = 0; j < kGroups; ++j) {
+          next_group(j);
 #pragma unroll
-          for (int i = 0; i < 8; ++i) {
-            float4 o;
-            o.x = __uint_as_float(v[4 * i]) + __ldg(bias + cb * 32 + 4 * i);
-            o.y = __uint_as_float(v[4 * i + 1]) + __ldg(bias + cb * 32 + 4 * i + 1);
-            o.z = __uint_as_float(v[4 * i + 2]) + __ldg(bias + cb * 32 + 4 * i + 2);
-            o.w = __uint_as_float(v[4 * i + 3]) + __ldg(bias + cb * 32 + 4 * i + 3);
-            reinterpret_cast<float4*>(dst + cb * 32)[i] = o;
+          for (int c = 0; c < 4; ++c) {
+            float2 x[4];
+            biased8(j, c, x);
+            reinterpret_cast<float4*>(dst + j * 64 + c * 8)[0] = make_float4(x[0].x, x[0].y, x[1].x, x[1].y);
+            reinterpret_cast<float4*>(dst + j * 64 + c * 8)[1] = make_float4(x[2].x, x[2].y, x[3].x, x[3].y);
           }
         }
-        tc_fence_before();
-        acc_release(&bar->acc_empty[buf], rank);
       } else if (kEpi == kEpiSplit) {
-        const int out_atoms = p.n_tiles * (kNt / 64);
+        const int out_atoms = p.n_tiles * kGroups;
         constexpr bool kPrefetch = resid_prefetch<kEpi, kCtas>();
         const bool has_resid = p.resid_tiles != nullptr;
 #pragma unroll 1
-        for (int j = 0; j < kNt / 64; ++j) {
-          const size_t goff = (static_cast<size_t>(rt) * out_atoms + nt * (kNt / 64) + j) * kSplitAtom;
+        for (int j = 0; j < kGroups; ++j) {
+          const size_t goff = (static_cast<size_t>(rt) * out_atoms + nt * kGroups + j) * kSplitAtom;
           uint8_t* ob = stg;  // buffer of this atom: residual in, result in place, bulk store out
           if (kPrefetch) {
             // three 32 KB buffers in rotation (atom ra uses ra % 3): the residual of atom ra + 1 is fetched while atom
@@ -313,11 +335,11 @@ __global__ void __launch_bounds__(kLinThreads, 1) linear_kernel(const LinearPara
                 }
                 size_t next = goff + kSplitAtom;  // next atom of this item, else atom 0 of the next item
                 bool more = true;
-                if (j == kNt / 64 - 1) {
+                if (j == kGroups - 1) {
                   const int item2 = item + stride;
                   more = item2 < items;
                   const int unit2 = item2 / p.n_tiles, nt2 = item2 - unit2 * p.n_tiles;
-                  next = (static_cast<size_t>(unit2 * kCtas + rank) * out_atoms + nt2 * (kNt / 64)) * kSplitAtom;
+                  next = (static_cast<size_t>(unit2 * kCtas + rank) * out_atoms + nt2 * kGroups) * kSplitAtom;
                 }
                 if (more) {
                   const uint32_t sl = (ra + 1) % 3;
@@ -341,32 +363,24 @@ __global__ void __launch_bounds__(kLinThreads, 1) linear_kernel(const LinearPara
             if (has_resid) { mbar_wait(&bar->aux_full, aux_phase); aux_phase ^= 1; }
             else epi_bar_sync();
           }
+          next_group(j);
 #pragma unroll
-          for (int cbh = 0; cbh < 2; ++cbh) {
-            tmem_ld32(tacc + j * 64 + cbh * 32, v);
-            tmem_wait_ld();
-            if (j == kNt / 64 - 1 && cbh == 1) { tc_fence_before(); acc_release(&bar->acc_empty[buf], rank); }
+          for (int c = 0; c < 4; ++c) {
+            uint8_t* at = ob + sw128_offset(r, g * 4 + c);
+            float2 x[4];
+            biased8(j, c, x);
+            if (has_resid) {
+              const uint4 rh = *reinterpret_cast<const uint4*>(at), rl = *reinterpret_cast<const uint4*>(at + kHalfAtom);
+              const uint32_t hh[4] = {rh.x, rh.y, rh.z, rh.w}, ll[4] = {rl.x, rl.y, rl.z, rl.w};
 #pragma unroll
-            for (int q = 0; q < 4; ++q) {
-              uint8_t* at = ob + sw128_offset(r, cbh * 4 + q);
-              float x[8];
-#pragma unroll
-              for (int i = 0; i < 8; ++i)
-                x[i] = __uint_as_float(v[8 * q + i]) + __ldg(bias + j * 64 + cbh * 32 + 8 * q + i);
-              if (has_resid) {
-                const uint4 rh = *reinterpret_cast<const uint4*>(at), rl = *reinterpret_cast<const uint4*>(at + kHalfAtom);
-                const uint32_t hh[4] = {rh.x, rh.y, rh.z, rh.w}, ll[4] = {rl.x, rl.y, rl.z, rl.w};
-#pragma unroll
-                for (int i = 0; i < 4; ++i) {
-                  x[2 * i] = (bf16lo(hh[i]) + bf16lo(ll[i])) + x[2 * i];
-                  x[2 * i + 1] = (bf16hi(hh[i]) + bf16hi(ll[i])) + x[2 * i + 1];
-                }
-              }
-              uint4 hi, lo;
-              split8(x, hi, lo);
-              *reinterpret_cast<uint4*>(at) = hi;
-              *reinterpret_cast<uint4*>(at + kHalfAtom) = lo;
+              for (int i = 0; i < 4; ++i)
+                x[i] = __fadd2_rn(__fadd2_rn(make_float2(bf16lo(hh[i]), bf16hi(hh[i])),
+                                             make_float2(bf16lo(ll[i]), bf16hi(ll[i]))), x[i]);
             }
+            uint4 hi, lo;
+            split8(x, hi, lo);
+            *reinterpret_cast<uint4*>(at) = hi;
+            *reinterpret_cast<uint4*>(at + kHalfAtom) = lo;
           }
           fence_proxy_async_smem();
           epi_bar_sync();
@@ -377,54 +391,52 @@ __global__ void __launch_bounds__(kLinThreads, 1) linear_kernel(const LinearPara
         // kEpiQkvSelf : n tile == head; columns [q 64 | k 64 | v 64]; rotary on q, k
         // kEpiQkvCross: n tile 0 = qk of the 4 heads, n tile 1 = v of the 4 heads
         if (kEpi == kEpiQkvSelf) { mbar_wait(&bar->aux_full, aux_phase); aux_phase ^= 1; }
-        constexpr int kParts = kEpi == kEpiQkvSelf ? 3 : 4;
 #pragma unroll 1
-        for (int part = 0; part < kParts; ++part) {
+        for (int part = 0; part < kGroups; ++part) {
           const int h = kEpi == kEpiQkvSelf ? nt : part;
           const int kind = kEpi == kEpiQkvSelf ? part : (nt == 0 ? 0 : 2);  // 0 q, 1 k, 2 v
           uint8_t* sb = stg + (sbi++ & 1) * kHalfAtom;
           if (leader) bulk_wait_read<1>();  // the store issued two parts ago has drained this half
           epi_bar_sync();
+          next_group(part);
+          float2 f[16];
 #pragma unroll
-          for (int cbh = 0; cbh < 2; ++cbh) {
-            tmem_ld32(tacc + part * 64 + cbh * 32, v);
-            tmem_wait_ld();
-            if (part == kParts - 1 && cbh == 1) { tc_fence_before(); acc_release(&bar->acc_empty[buf], rank); }
+          for (int c = 0; c < 4; ++c) biased8(part, c, f + 4 * c);
+          if (kEpi == kEpiQkvSelf && kind < 2) {
 #pragma unroll
-            for (int i = 0; i < 32; ++i) f[i] = __uint_as_float(v[i]) + __ldg(bias + part * 64 + cbh * 32 + i);
-            if (kEpi == kEpiQkvSelf && kind < 2) {
+            for (int c = 0; c < 4; ++c) {  // 4 frequencies per 16-byte table chunk
+              const uint32_t off = r * 128 + (((g * 4 + c) ^ (r & 7)) << 4);
+              const float4 c4 = *reinterpret_cast<const float4*>(rot + off);
+              const float4 s4 = *reinterpret_cast<const float4*>(rot + kHalfAtom + off);
+              const float cc[4] = {c4.x, c4.y, c4.z, c4.w}, ss[4] = {s4.x, s4.y, s4.z, s4.w};
 #pragma unroll
-              for (int q = 0; q < 4; ++q) {  // 4 frequencies per 16-byte table chunk
-                const uint32_t off = r * 128 + (((cbh * 4 + q) ^ (r & 7)) << 4);
-                const float4 c4 = *reinterpret_cast<const float4*>(rot + off);
-                const float4 s4 = *reinterpret_cast<const float4*>(rot + kHalfAtom + off);
-                const float cc[4] = {c4.x, c4.y, c4.z, c4.w}, ss[4] = {s4.x, s4.y, s4.z, s4.w};
-#pragma unroll
-                for (int e = 0; e < 4; ++e) {
-                  // (t*cos) + (rot(t)*sin), reference rounding sequence (lightglue.py:36-43)
-                  const float x0 = f[8 * q + 2 * e], x1 = f[8 * q + 2 * e + 1];
-                  f[8 * q + 2 * e] = __fadd_rn(__fmul_rn(x0, cc[e]), __fmul_rn(-x1, ss[e]));
-                  f[8 * q + 2 * e + 1] = __fadd_rn(__fmul_rn(x1, cc[e]), __fmul_rn(x0, ss[e]));
-                }
+              for (int e = 0; e < 4; ++e) {
+                // (t*cos) + (rot(t)*sin), reference rounding sequence (lightglue.py:36-43): two roundings of the
+                // products, one of the sum (the packed multiplies / add are never contracted)
+                const float2 x = f[4 * c + e];
+                f[4 * c + e] = __fadd2_rn(__fmul2_rn(x, make_float2(cc[e], cc[e])),
+                                          __fmul2_rn(make_float2(-x.y, x.x), make_float2(ss[e], ss[e])));
               }
             }
-            if (kind < 2) {
+          }
+          if (kind < 2) {
 #pragma unroll
-              for (int q = 0; q < 4; ++q) {
-                uint4 o;
-                o.x = pack_bf16x2(f[8 * q], f[8 * q + 1]); o.y = pack_bf16x2(f[8 * q + 2], f[8 * q + 3]);
-                o.z = pack_bf16x2(f[8 * q + 4], f[8 * q + 5]); o.w = pack_bf16x2(f[8 * q + 6], f[8 * q + 7]);
-                *reinterpret_cast<uint4*>(sb + sw128_offset(r, cbh * 4 + q)) = o;
-              }
-            } else {
-              // V^T: element (dh d, point r) of 2 atoms x [64 dh][64 points]
-              uint8_t* col = sb + (r >> 6) * 8192 + (r & 7) * 2;
-              const uint32_t pc = (r & 63) >> 3;
+            for (int c = 0; c < 4; ++c) {
+              uint4 o;
+              o.x = pack_bf16x2(f[4 * c].x, f[4 * c].y); o.y = pack_bf16x2(f[4 * c + 1].x, f[4 * c + 1].y);
+              o.z = pack_bf16x2(f[4 * c + 2].x, f[4 * c + 2].y); o.w = pack_bf16x2(f[4 * c + 3].x, f[4 * c + 3].y);
+              *reinterpret_cast<uint4*>(sb + sw128_offset(r, g * 4 + c)) = o;
+            }
+          } else {
+            // V^T: element (dh d, point r) of 2 atoms x [64 dh][64 points]
+            uint8_t* col = sb + (r >> 6) * 8192 + (r & 7) * 2;
+            const uint32_t pc = (r & 63) >> 3;
 #pragma unroll
-              for (int i = 0; i < 32; ++i) {
-                const int d = cbh * 32 + i;
-                *reinterpret_cast<__nv_bfloat16*>(col + d * 128 + ((pc ^ (d & 7)) << 4)) = __float2bfloat16_rn(f[i]);
-              }
+            for (int i = 0; i < 16; ++i) {
+              const int d = g * 32 + 2 * i;
+              *reinterpret_cast<__nv_bfloat16*>(col + d * 128 + ((pc ^ (d & 7)) << 4)) = __float2bfloat16_rn(f[i].x);
+              *reinterpret_cast<__nv_bfloat16*>(col + (d + 1) * 128 + ((pc ^ ((d + 1) & 7)) << 4)) =
+                  __float2bfloat16_rn(f[i].y);
             }
           }
           fence_proxy_async_smem();
@@ -444,10 +456,10 @@ __global__ void __launch_bounds__(kLinThreads, 1) linear_kernel(const LinearPara
   tc_fence_before();
   if (kCtas == 2) {
     cluster_sync_all();  // neither CTA leaves (or frees TMEM) while the pair's MMAs / remote arrivals are in flight
-    if (warp == 5) tmem_dealloc_pair<512>(tmem);
+    if (warp == 9) tmem_dealloc_pair<512>(tmem);
   } else {
     __syncthreads();
-    if (warp == 5) tmem_dealloc<512>(tmem);
+    if (warp == 9) tmem_dealloc<512>(tmem);
   }
 }
 
@@ -689,7 +701,7 @@ static int check_linear(const void* a0, int a0_atoms, const void* a1, int a1_ato
   if (!a0 || !w || !bias) return LG_ERR_NULL;
   if ((a1 == nullptr) != (a1_atoms == 0)) return LG_ERR_NULL;
   if (a0_atoms <= 0 || a1_atoms < 0 || row_tiles <= 0 || n_out <= 0 || n_out % nt) return LG_ERR_SHAPE;
-  if (!aligned16(a0) || !aligned16(a1) || !aligned16(w)) return LG_ERR_ALIGN;
+  if (!aligned16(a0) || !aligned16(a1) || !aligned16(w) || !aligned16(bias)) return LG_ERR_ALIGN;
   return 0;
 }
 
