@@ -17,7 +17,21 @@ import sys
 import threading
 import time
 
+if "reference" in sys.argv[1:]:
+    # torchrun exports OMP_NUM_THREADS=1 to every rank; the CPU arm is meant to use all host cores
+    for _k in ("OMP_NUM_THREADS", "MKL_NUM_THREADS"):
+        os.environ[_k] = str(os.cpu_count() or 1)
+
+# stdout carries exactly ONE JSON line: everything else a library prints there (NCCL's version banner under
+# NCCL_DEBUG=VERSION, ...) is sent to stderr by pointing fd 1 at fd 2 until the line is written
+_JSON_FD = os.dup(1)
+os.dup2(2, 1)
+
 import torch
+
+
+def emit(line: dict):
+    os.write(_JSON_FD, (json.dumps(line) + "\n").encode())
 
 ROOT = os.path.dirname(os.path.abspath(__file__))
 sys.path.insert(0, ROOT)
@@ -73,7 +87,7 @@ def run_reference(a):
     t0 = time.perf_counter()
     rate, cores, dt = cpu_forward_rate(a.kpts, a.steps, warm=0)
     sample = f"{a.steps} forwards of 1 pair x {a.kpts} kpts (1/{a.batch} of the step's batch), fp32, {cores} threads"
-    print(json.dumps({
+    emit({
         "impl": "reference", "metric": METRIC, "value": rate, "unit": UNIT, "n_gpus": a.gpus, "steps": a.steps,
         "warmup": a.warmup, "ms_per_step": 1e3 * dt / a.steps, "higher_is_better": True, "scaling": "weak",
         "vs_baseline": None, "dtype": "f32", "data": "synthetic",
@@ -81,7 +95,7 @@ def run_reference(a):
         "cpu_baseline": {"value": rate, "unit": UNIT, "cores": cores, "kind": "port", "sample": sample},
         "e2e": {"value": rate, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "gpu_launches": 0,
-    }), flush=True)
+    })
 
 
 # ----------------------------------------------------------------------------- clocks sampler
@@ -250,7 +264,11 @@ def run_b200(a):
                 "share_of_step": attn_ms / max(min(a.steps, 3), 1) / (ms / a.steps)}
 
     if rank == 0:
-        cpu_rate, cores, cpu_dt = cpu_forward_rate(a.kpts, a.cpu_pairs)
+        cpu = None  # timed at N=1 only (under torchrun the other ranks' host threads would share the cores)
+        if world == 1:
+            cpu_rate, cores, cpu_dt = cpu_forward_rate(a.kpts, a.cpu_pairs)
+            cpu = {"value": cpu_rate, "unit": UNIT, "cores": cores, "kind": "port",
+                   "sample": f"{a.cpu_pairs} forwards of 1 pair x {a.kpts} kpts ({cpu_dt:.1f} s), fp32 torch CPU"}
         line = {
             "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": a.steps, "warmup": max(a.warmup, 3),
             "ms_per_step": ms / a.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
@@ -264,11 +282,10 @@ def run_b200(a):
                     "unpipelined_ms_per_step": ms_e2e_sync / a.steps},
             "gpu_launches": launches,
             "roofline": roofline,
-            "cpu_baseline": {"value": cpu_rate, "unit": UNIT, "cores": cores, "kind": "port",
-                             "sample": f"{a.cpu_pairs} forwards of 1 pair x {a.kpts} kpts ({cpu_dt:.1f} s), fp32 torch CPU"},
+            "cpu_baseline": cpu,
             "clocks": sampler.summary(),
         }
-        print(json.dumps(line), flush=True)
+        emit(line)
     if distributed:
         dist.barrier()
         dist.destroy_process_group()
