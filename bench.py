@@ -272,7 +272,7 @@ def run_b200(a):
         line = {
             "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": a.steps, "warmup": max(a.warmup, 3),
             "ms_per_step": ms / a.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
-            "dtype": "bf16 attention operands, 3-term split-bf16 linears, tf32x3 assignment, f32 accumulate / softmax / LayerNorm", "data": "synthetic",
+            "dtype": "bf16 attention operands, 3-term split-bf16 linears and assignment, f32 accumulate / softmax / LayerNorm", "data": "synthetic",
             "config": {"workload": workload_name(a), "pairs_per_gpu": a.batch, "keypoints": a.kpts,
                        "l2": "inputs+activations per step (>4 GB) exceed the 126 MB L2; no flush needed",
                        "parallelism": f"pairs sharded over {world} GPU(s), no data-path collective"},

@@ -46,6 +46,9 @@ SIGNATURES = {
     "lg_filter_matches": (_I, [_P, _L, _P, _P, _F, _P, _P, _P, _P, _P, _I, _I, _I, _P]),
     "lg_assign_keys": (_I, [_P, _P, _P, _P, _P, _P, _F, _P, _P, _P, _I, _I, _I, _P]),
     "lg_filter_from_keys": (_I, [_P, _P, _P, _F, _P, _P, _P, _P, _I, _I, _I, _P]),
+    "lg_assign_tiles_ws_bytes": (_c.c_size_t, [_I, _I, _I]),
+    "lg_assign_tiles": (_I, [_P, _P, _I, _I, _P, _P, _P, _P, _F, _P, _P, _P, _I, _I, _I, _P]),
+    "lg_logit_rows": (_I, [_P, _P, _P, _P, _L, _P]),
 }
 
 _lib = None
@@ -232,6 +235,42 @@ def assign_and_filter(md0, md1, z0, z1, th: float, m_len=None, n_len=None, presc
     _check(lib().lg_filter_from_keys(_ptr(keys), _ptr(ml), _ptr(nl), float(th), _ptr(m0), _ptr(m1), _ptr(ms0),
                                      _ptr(ms1), B, M, N, _stream()), "lg_filter_from_keys")
     _count(6)
+    return scores, (m0, m1, ms0, ms1)
+
+
+def logit_rows(x, w, bias):
+    """x (..., 256) f32 -> <x, w> + bias over the last axis (the matchability logits, lightglue.py:313-314)."""
+    assert x.shape[-1] == 256
+    out = torch.empty(x.shape[:-1], device=x.device, dtype=torch.float32)
+    _check(lib().lg_logit_rows(_ptr(_f32c(x, "x")), _ptr(_f32c(w, "w")), _ptr(bias), _ptr(out), out.numel(), _stream()),
+           "lg_logit_rows")
+    _count(1)
+    return out
+
+
+def assign_tiles(a_tiles, b_tiles, tpa, tpb, z0, z1, th=None, m_len=None, n_len=None, scale=1.0 / 16):
+    """lg_assign_tiles: split tiles of final_proj(desc0 / desc1) (image b at row tile b*tpa / b*tpb), z0 (B,M), z1 (B,N)
+    -> log assignment (B,M+1,N+1); with `th` also the filter_matches outputs (keys gathered in pass 2)."""
+    B, M = z0.shape
+    N = z1.shape[1]
+    dev = z0.device
+    scores = torch.empty(B, M + 1, N + 1, device=dev, dtype=torch.float32)
+    ws = torch.empty(lib().lg_assign_tiles_ws_bytes(B, M, N), device=dev, dtype=torch.uint8)
+    keys = None if th is None else torch.empty(lib().lg_filter_ws_bytes(B, M, N), device=dev, dtype=torch.uint8)
+    ml, nl = _i32(m_len), _i32(n_len)
+    _check(lib().lg_assign_tiles(_ptr(a_tiles), _ptr(b_tiles), int(tpa), int(tpb), _ptr(_f32c(z0, "z0")),
+                                 _ptr(_f32c(z1, "z1")), _ptr(ml), _ptr(nl), float(scale), _ptr(scores), _ptr(ws),
+                                 _ptr(keys), B, M, N, _stream()), "lg_assign_tiles")
+    _count(3)
+    if th is None:
+        return scores
+    m0 = torch.empty(B, M, device=dev, dtype=torch.int64)
+    m1 = torch.empty(B, N, device=dev, dtype=torch.int64)
+    ms0 = torch.empty(B, M, device=dev, dtype=torch.float32)
+    ms1 = torch.empty(B, N, device=dev, dtype=torch.float32)
+    _check(lib().lg_filter_from_keys(_ptr(keys), _ptr(ml), _ptr(nl), float(th), _ptr(m0), _ptr(m1), _ptr(ms0),
+                                     _ptr(ms1), B, M, N, _stream()), "lg_filter_from_keys")
+    _count(1)
     return scores, (m0, m1, ms0, ms1)
 
 

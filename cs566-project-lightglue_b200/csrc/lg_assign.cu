@@ -400,6 +400,18 @@ __global__ void assign_reduce_kernel(const float2* __restrict__ row_part, const 
 
 static inline size_t align256(size_t x) { return (x + 255) & ~static_cast<size_t>(255); }
 
+namespace lg {
+// host launcher shared with lg_assign_strip.cu (declared in lg_assign.cuh)
+void launch_assign_reduce(const float2* row_part, const float2* col_part, const float* z0, const float* z1,
+                          const int* m_len, const int* n_len, float* row_lse, float* col_lse, float* row_ls,
+                          float* col_ls, float* scores, int B, int M, int N, int rt, int ct, cudaStream_t stream) {
+  const int pts = (M > N ? M : N);
+  assign_reduce_kernel<<<dim3((pts + 255) / 256, B), 256, 0, stream>>>(row_part, col_part, z0, z1, m_len, n_len,
+                                                                      row_lse, col_lse, row_ls, col_ls, scores, M, N,
+                                                                      rt, ct);
+}
+}  // namespace lg
+
 extern "C" size_t lg_assign_ws_bytes(int B, int M, int N) {
   if (B <= 0 || M <= 0 || N <= 0) return 0;
   const size_t rt = (M + 127) / 128, ct = (N + 127) / 128;

@@ -52,6 +52,25 @@ __global__ void __launch_bounds__(256) token_scores_kernel(const float* __restri
   }
 }
 
+// warp per row: one 256-long dot product + bias (matchability logits for the assignment, lightglue.py:313-314)
+__global__ void __launch_bounds__(256) logit_rows_kernel(const float* __restrict__ x, const float* __restrict__ w,
+                                                         const float* __restrict__ bias, float* __restrict__ out,
+                                                         int64_t rows) {
+  const int lane = threadIdx.x & 31;
+  const int64_t n = static_cast<int64_t>(blockIdx.x) * 8 + (threadIdx.x >> 5);
+  if (n >= rows) return;
+  const float4* row = reinterpret_cast<const float4*>(x + n * 256);
+  float acc = 0.f;
+#pragma unroll
+  for (int h = 0; h < 2; ++h) {
+    const float4 v = __ldg(row + h * 32 + lane);
+    const float4 ww = __ldg(reinterpret_cast<const float4*>(w) + h * 32 + lane);
+    acc += v.x * ww.x + v.y * ww.y + v.z * ww.z + v.w * ww.w;
+  }
+  acc = warp_sum(acc);
+  if (lane == 0) out[n] = acc + bias[0];
+}
+
 // one block per image: keep flags -> exclusive scan -> ascending list of kept positions.
 // counts[b] = {kept, number of tokens with conf < thr (0 if conf == null)}
 __global__ void __launch_bounds__(1024) prune_plan_kernel(const float* __restrict__ conf, const float* __restrict__ match,
@@ -150,5 +169,14 @@ extern "C" int lg_prune_gather(const float* desc, const float* cos_t, const floa
   if (B <= 0 || N <= 0 || N_out <= 0 || N_orig < N) return LG_ERR_SHAPE;
   lg::prune_gather_kernel<<<dim3((N + 3) / 4, B), 256, 0, stream>>>(desc, cos_t, sin_t, ind, keep_idx, counts, desc_o,
                                                                     cos_o, sin_o, ind_o, prune, N, N_out, N_orig);
+  return static_cast<int>(cudaGetLastError());
+}
+
+extern "C" int lg_logit_rows(const float* x, const float* w, const float* bias, float* out, int64_t rows,
+                             cudaStream_t stream) {
+  if (!x || !w || !bias || !out) return LG_ERR_NULL;
+  if (rows <= 0 || rows > (static_cast<int64_t>(1) << 33)) return LG_ERR_SHAPE;
+  if ((reinterpret_cast<uintptr_t>(x) | reinterpret_cast<uintptr_t>(w)) & 15) return LG_ERR_ALIGN;
+  lg::logit_rows_kernel<<<static_cast<unsigned>((rows + 7) / 8), 256, 0, stream>>>(x, w, bias, out, rows);
   return static_cast<int>(cudaGetLastError());
 }

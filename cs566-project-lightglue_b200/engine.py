@@ -176,6 +176,15 @@ class TileEngine:
         return (C.tiles_to_rows(self.x[: self.rt0], self.B, self.M, 256, self.tp0),
                 C.tiles_to_rows(self.x[self.rt0:], self.B, self.N, 256, self.tp1))
 
+    def final_proj_tiles(self, i: int):
+        """MatchAssignment.final_proj of head i (lightglue.py:310) as split tiles, the operand format of lg_assign_tiles:
+        -> (tiles of image side 0, tiles of side 1), image b at row tile b*tp0 / b*tp1."""
+        w, b = self.pk.final[i]
+        if getattr(self, "md", None) is None:
+            self.md = C.alloc_split(self.rt, 256, self.dev)
+        C.linear_split(self.x, w, b, 256, out=self.md)
+        return self.md[: self.rt0], self.md[self.rt0:]
+
     def final_proj(self, i: int):
         """MatchAssignment.final_proj of head i (lightglue.py:310) -> md0 (B,M,256), md1 (B,N,256) f32."""
         w, b = self.pk.final[i]

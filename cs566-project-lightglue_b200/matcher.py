@@ -18,7 +18,6 @@ from pathlib import Path
 
 import numpy as np
 import torch
-import torch.nn.functional as F
 from torch import nn
 
 from . import _cabi as C
@@ -203,17 +202,17 @@ class LightGlue(nn.Module):
         return eng
 
     def _assign(self, i, eng, d0, d1, len0, len1, th=None):
-        """MatchAssignment.forward (lightglue.py:306-315): final_proj on tcgen05, matchability logits, then
-        the fused similarity + double log-softmax kernel.  With `th` the same launch also gathers the row / column
-        argmax keys and filter_matches (lightglue.py:321-337) is finished from them: returns (scores, matches)."""
+        """MatchAssignment.forward (lightglue.py:306-315): final_proj on tcgen05 straight into split tiles, the
+        matchability logits, then the fused similarity + double log-softmax kernel on those tiles.  With `th` the
+        same launch also gathers the row / column argmax keys and filter_matches (lightglue.py:321-337) is finished
+        from them: returns (scores, matches)."""
         head = self.log_assignment[i]
-        md0, md1 = eng.final_proj(i)
-        z0 = F.linear(d0, head.matchability.weight, head.matchability.bias).squeeze(-1).contiguous()
-        z1 = F.linear(d1, head.matchability.weight, head.matchability.bias).squeeze(-1).contiguous()
-        prescale = self.conf.descriptor_dim ** -0.25
-        if th is None:
-            return C.assign(md0, md1, z0, z1, len0, len1, prescale=prescale)
-        return C.assign_and_filter(md0, md1, z0, z1, th, len0, len1, prescale=prescale)
+        a_tiles, b_tiles = eng.final_proj_tiles(i)
+        wm = head.matchability.weight.reshape(-1)
+        z0 = C.logit_rows(d0, wm, head.matchability.bias)
+        z1 = C.logit_rows(d1, wm, head.matchability.bias)
+        scale = float(self.conf.descriptor_dim) ** -0.5  # d^-1/4 on both operands (lightglue.py:311-312)
+        return C.assign_tiles(a_tiles, b_tiles, eng.tp0, eng.tp1, z0, z1, th, len0, len1, scale=scale)
 
     @staticmethod
     def _image_size(data, view, like):

@@ -149,6 +149,23 @@ int lg_assign_keys(const float* md0, const float* md1, const float* z0, const fl
 int lg_filter_from_keys(const void* keys_ws, const int* m_len, const int* n_len, float th, int64_t* m0, int64_t* m1,
                         float* ms0, float* ms1, int B, int M, int N, cudaStream_t stream);
 
+/* (3)+(4) from split tiles: the same MatchAssignment (lightglue.py:306-315) + sigmoid_log_double_softmax
+ * (:284-296) (+ filter keys when keys_ws != NULL, lg_filter_ws_bytes(B,M,N) bytes, zeroed by the call), but the
+ * operands are the split-bf16 row tiles lg_linear_split writes for final_proj (image b of side 0 starts at row
+ * tile b*tpa of a_tiles, side 1 at b*tpb of b_tiles; 256 columns = 4 atoms): no fp32 rows, no pack pass, the
+ * row tile of image 0 stays resident in shared memory while the column tiles stream.  similarity =
+ * scale * <a_row, b_row> (scale = d^-1/2 for the reference's two d^-1/4 factors, lightglue.py:311-312), 3-term
+ * split-bf16 products (~1e-5 abs on |sim| ~ 10; lg_assign keeps the TF32x3 variant).  z0 (B,M), z1 (B,N) =
+ * matchability logits (lg_logit_rows).  ws: lg_assign_tiles_ws_bytes(B,M,N) bytes. */
+size_t lg_assign_tiles_ws_bytes(int B, int M, int N);
+int lg_assign_tiles(const void* a_tiles, const void* b_tiles, int tpa, int tpb, const float* z0, const float* z1,
+                    const int* m_len, const int* n_len, float scale, float* scores, void* ws, void* keys_ws, int B,
+                    int M, int N, cudaStream_t stream);
+
+/* Linear(256 -> 1) logits of every row: out[i] = <x[i,:], w> + bias[0]  (MatchAssignment.matchability,
+ * lightglue.py:304,313-314, before the log-sigmoid).  x (rows, 256) f32 contiguous. */
+int lg_logit_rows(const float* x, const float* w, const float* bias, float* out, int64_t rows, cudaStream_t stream);
+
 /* (5) adaptive depth / width (lightglue.py:527-547).
  * lg_token_scores: conf (B,N) = sigmoid(w_tok.desc + b_tok) (TokenConfidence.forward :102-107; w_tok NULL
  *   => skipped) and match (B,N) = sigmoid(w_match.desc + b_match) (get_matchability :317-318), one read

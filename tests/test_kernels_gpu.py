@@ -215,6 +215,73 @@ def test_assign_vs_oracle(C, B, M, N):
     assert got[:, -1, -1].abs().max() == 0
 
 
+def _split_tiles(C, md):
+    B, N, _ = md.shape
+    tp = C.tiles_pad(N)
+    return C.rows_to_tiles(md.cuda().contiguous(), tp), tp
+
+
+@pytest.mark.parametrize("B,M,N", [(1, 128, 128), (2, 200, 333), (1, 1024, 1024), (2, 2048, 2048), (1, 1, 700), (3, 129, 1)])
+def test_assign_tiles_vs_oracle(C, B, M, N):
+    """lg_assign_tiles (split-bf16 strips, the matcher's path) against the fp64 evaluation of
+    sigmoid_log_double_softmax (lightglue.py:284-296): 3-term split-bf16 products, measured 1.3e-4 abs on these
+    |sim| ~ 10 operands (the TF32x3 kernel: 1.3e-5), bound 3e-4 (the bf16-path budget on log_assignment is 2e-2)."""
+    g = _gen(M + 3 * N)
+    md0 = torch.randn(B, M, 256, generator=g) * 1.5
+    md1 = torch.randn(B, N, 256, generator=g) * 1.5
+    z0, z1 = torch.randn(B, M, 1, generator=g) * 2, torch.randn(B, N, 1, generator=g) * 2
+    sim = torch.einsum("bmd,bnd->bmn", (md0 / 4).double(), (md1 / 4).double())
+    ref64 = O.sigmoid_log_double_softmax(sim, z0.double(), z1.double())
+    a, tpa = _split_tiles(C, md0)
+    b, tpb = _split_tiles(C, md1)
+    got = C.assign_tiles(a, b, tpa, tpb, z0[..., 0].contiguous().cuda(), z1[..., 0].contiguous().cuda()).cpu()
+    assert torch.isfinite(got).all()
+    assert (got.double() - ref64).abs().max().item() < 3e-4
+    assert got[:, -1, -1].abs().max() == 0
+
+
+@pytest.mark.parametrize("B,M,N,varlen", [(1, 300, 200, False), (2, 257, 640, True), (1, 128, 128, False),
+                                          (2, 97, 130, True), (3, 1500, 1100, True)])
+def test_assign_tiles_keys_equal_filter_scan(C, B, M, N, varlen):
+    """keys gathered in pass 2 of lg_assign_tiles + lg_filter_from_keys == lg_filter_matches (one scan of the matrix)
+    on the same scores, bit for bit, including ties and variable-length batches; padding is -inf."""
+    g = torch.Generator().manual_seed(B * 1000 + M + N)
+    md0 = torch.randn(B, M, 256, generator=g)
+    md1 = torch.randn(B, N, 256, generator=g)
+    md1[:, 5] = md1[:, 3]
+    md0[:, 7] = md0[:, 2]
+    md1[:, : min(M, N) // 2] += 2.0 * md0[:, : min(M, N) // 2]
+    z0, z1 = torch.randn(B, M, generator=g), torch.randn(B, N, generator=g)
+    z1[:, 5] = z1[:, 3]
+    z0[:, 7] = z0[:, 2]
+    mls = [M, max(1, M - 70), max(1, M // 3)][:B]
+    nls = [max(1, N - 150), N, max(1, N // 5)][:B]
+    ml = torch.tensor(mls, dtype=torch.int32).cuda() if varlen else None
+    nl = torch.tensor(nls, dtype=torch.int32).cuda() if varlen else None
+    a, tpa = _split_tiles(C, md0)
+    b, tpb = _split_tiles(C, md1)
+    s_plain = C.assign_tiles(a, b, tpa, tpb, z0.cuda(), z1.cuda(), None, ml, nl)
+    s_keys, f_keys = C.assign_tiles(a, b, tpa, tpb, z0.cuda(), z1.cuda(), 0.05, ml, nl)
+    assert torch.equal(s_plain, s_keys)
+    f_scan = C.filter_matches(s_keys, 0.05, ml, nl)
+    for x, y in zip(f_scan, f_keys):
+        assert torch.equal(x, y)
+    assert (f_keys[0] >= 0).sum() > 0
+    # against the TF32x3 tile kernel on the same operands: same padding pattern, values within the split error
+    s_ref = C.assign(md0.cuda(), md1.cuda(), z0.cuda(), z1.cuda(), ml, nl)
+    fin = torch.isfinite(s_ref)
+    assert torch.equal(fin, torch.isfinite(s_keys))
+    assert (s_ref[fin] - s_keys[fin]).abs().max() < 3e-4
+
+
+def test_logit_rows(C):
+    g = _gen(5)
+    x, w, b = torch.randn(3, 77, 256, generator=g), torch.randn(256, generator=g), torch.randn(1, generator=g)
+    got = C.logit_rows(x.cuda(), w.cuda(), b.cuda()).cpu()
+    assert got.shape == (3, 77)
+    assert (got - (x @ w + b)).abs().max() < 2e-5
+
+
 def test_assign_varlen(C):
     g = _gen(77)
     B, M, N = 3, 300, 260
