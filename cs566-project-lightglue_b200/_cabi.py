@@ -298,10 +298,12 @@ def prune_plan(conf, match, thr: float, min_match: float, lens=None):
     return keep_idx, counts
 
 
-def prune_gather(desc, cos, sin, ind, keep_idx, counts, prune):
-    """Gather kept rows into fresh (B,N,..) buffers (rows >= counts[b,0] are unspecified)."""
+def prune_gather(desc, cos, sin, ind, keep_idx, counts, prune, zero=False):
+    """Gather kept rows into fresh (B,N,..) buffers (rows >= counts[b,0] are unspecified, or zero with zero=True:
+    batches whose pairs keep different counts feed those rows to the layer kernels as padding)."""
     B, N, _ = desc.shape
-    desc_o, cos_o, sin_o, ind_o = torch.empty_like(desc), torch.empty_like(cos), torch.empty_like(sin), torch.empty_like(ind)
+    new = torch.zeros_like if zero else torch.empty_like
+    desc_o, cos_o, sin_o, ind_o = new(desc), new(cos), new(sin), new(ind)
     assert ind.dtype == torch.int64 and prune.dtype == torch.int64
     _check(lib().lg_prune_gather(_ptr(_f32c(desc, "desc")), _ptr(_f32c(cos, "cos")), _ptr(_f32c(sin, "sin")), _ptr(ind),
                                  _ptr(keep_idx), _ptr(counts), _ptr(desc_o), _ptr(cos_o), _ptr(sin_o), _ptr(ind_o),

@@ -89,3 +89,179 @@ def forward_adaptive(model, eng, cs0, cs1):
         pred["ref_descriptors0"] = desc0.new_zeros((b, 0, desc0.shape[1], desc0.shape[2]))
         pred["ref_descriptors1"] = desc1.new_zeros((b, 0, desc1.shape[1], desc1.shape[2]))
     return pred
+
+
+class PrunedAssignments:
+    """log_assignment of a batched adaptive forward: pair b has its own kept counts, so entry b is the reference's
+    (1, M'_b + 1, N'_b + 1) matrix over the kept points (lightglue.py:550).  Entries are cut
+    out of the padded per-exit-group score tensors on access (len() == batch size)."""
+
+    def __init__(self, n):
+        self._where = [None] * n
+
+    def _set(self, b, scores, j, a, c):
+        self._where[b] = (scores, j, a, c)
+
+    def __len__(self):
+        return len(self._where)
+
+    def __getitem__(self, b):
+        scores, j, a, c = self._where[b]
+        M, N = scores.shape[1] - 1, scores.shape[2] - 1
+        dev = scores.device
+        rows = torch.cat([torch.arange(a, device=dev), torch.tensor([M], device=dev)])
+        cols = torch.cat([torch.arange(c, device=dev), torch.tensor([N], device=dev)])
+        return scores[j].index_select(0, rows).index_select(1, cols)[None]
+
+
+def forward_adaptive_batched(model, eng, cs0, cs1, len0=None, len1=None):
+    """Early exit + token pruning for a BATCH of pairs (the reference asserts b == 1, lightglue.py:528,533; SURVEY.md
+    8(f) N2 / config 3).  Every pair follows exactly the reference's per-pair rules -- same thresholds, same stop test
+    on its own kept tokens over its own original m + n (lightglue.py:595-606), same order-preserving compaction
+    (:536-547) -- while the kernels run on the whole active set: pruned pairs are compacted to the front of their rows
+    and carried as valid lengths (the attention / assignment kernels mask by length), pairs that exit are assigned with
+    the head of their exit layer and leave the batch, and the survivors are re-tiled to the longest kept length.
+    One small device->host read per layer (kept / unconfident counts), like the reference's per-layer Python `if`."""
+    conf = model.conf
+    B, m, n = eng.B, eng.M, eng.N
+    dev = eng.dev
+    L = conf.n_layers
+    do_early_stop = conf.depth_confidence > 0
+    do_point_pruning = conf.width_confidence > 0
+    min_match = float(np.float32(1 - conf.width_confidence))
+    th = conf.filter_threshold
+
+    ids = torch.arange(B, device=dev)                       # original pair id of every active row
+    l0h = [m] * B if len0 is None else [int(v) for v in len0.tolist()]
+    l1h = [n] * B if len1 is None else [int(v) for v in len1.tolist()]
+    denom = [a + c for a, c in zip(l0h, l1h)]               # check_if_stop: ORIGINAL point count of the pair
+    l0, l1 = len0, len1
+    ind0 = ind1 = pr0 = pr1 = None
+    if do_point_pruning:
+        ind0 = torch.arange(m, device=dev)[None].repeat(B, 1)
+        ind1 = torch.arange(n, device=dev)[None].repeat(B, 1)
+        pr0 = torch.zeros(B, m, device=dev, dtype=torch.int64)
+        pr1 = torch.zeros(B, n, device=dev, dtype=torch.int64)
+        ar0, ar1 = torch.arange(m, device=dev)[None], torch.arange(n, device=dev)[None]
+        pr0 += 1 if l0 is None else (ar0 < l0[:, None]).long()  # prune counters start at 1 on real keypoints
+        pr1 += 1 if l1 is None else (ar1 < l1[:, None]).long()
+    out_m0 = torch.full((B, m + 1), -1, device=dev, dtype=torch.int64)
+    out_m1 = torch.full((B, n + 1), -1, device=dev, dtype=torch.int64)
+    out_s0 = torch.zeros((B, m + 1), device=dev)
+    out_s1 = torch.zeros((B, n + 1), device=dev)
+    out_p0 = torch.zeros(B, m, device=dev, dtype=torch.int64) if do_point_pruning else None
+    out_p1 = torch.zeros(B, n, device=dev, dtype=torch.int64) if do_point_pruning else None
+    exit_layer = torch.full((B,), L - 1, dtype=torch.int64)
+    assignments = PrunedAssignments(B)
+
+    def finalize(layer, e, sel, d0, d1, k0, k1):
+        """Assignment + filter of the active rows `sel` (None = all) with the head of `layer`, scattered back to the
+        original keypoint indices of their pairs (lightglue.py:549-562)."""
+        if sel is None:
+            ee, d0e, d1e, l0e, l1e, i0e, i1e, ide = e, d0, d1, l0, l1, ind0, ind1, ids
+        else:
+            pick = lambda t: None if t is None else t.index_select(0, sel)
+            d0e, d1e, l0e, l1e, i0e, i1e, ide = map(pick, (d0, d1, l0, l1, ind0, ind1, ids))
+            ee = model._engine(d0e.shape[0], d0e.shape[1], d1e.shape[1], dev)
+            ee.load_rows(d0e, d1e)
+        scores, (f0, f1, fs0, fs1) = model._assign(layer, ee, d0e, d1e, l0e, l1e, th=th)
+        rows = ide[:, None]
+        if do_point_pruning:
+            mc, nc = d0e.shape[1], d1e.shape[1]
+            t0, t1 = i0e, i1e
+            if l0e is not None:  # padding rows land in the spare column
+                t0 = torch.where(torch.arange(mc, device=dev)[None] < l0e[:, None], i0e, m)
+                t1 = torch.where(torch.arange(nc, device=dev)[None] < l1e[:, None], i1e, n)
+            out_m0[rows, t0] = torch.where(f0 == -1, -1, i1e.gather(1, f0.clamp(min=0)))
+            out_m1[rows, t1] = torch.where(f1 == -1, -1, i0e.gather(1, f1.clamp(min=0)))
+            out_s0[rows, t0] = fs0
+            out_s1[rows, t1] = fs1
+        else:
+            out_m0[ide, : f0.shape[1]] = f0
+            out_m1[ide, : f1.shape[1]] = f1
+            out_s0[ide, : f0.shape[1]] = fs0
+            out_s1[ide, : f1.shape[1]] = fs1
+        for j, b in enumerate(ide.tolist()):
+            assignments._set(b, scores, j, k0[j], k1[j])
+            exit_layer[b] = layer
+
+    for i in range(L):
+        eng.layer(i, l0, l1)
+        d0, d1 = eng.rows()
+        if i == L - 1:
+            finalize(i, eng, None, d0, d1, l0h, l1h)
+            if do_point_pruning:
+                out_p0[ids], out_p1[ids] = pr0, pr1
+            break
+        thr = float(model.confidence_thresholds[i])
+        head = model.log_assignment[i].matchability
+        tok = model.token_confidence[i].token[0] if do_early_stop else None
+        wt = None if tok is None else tok.weight.reshape(-1)
+        bt = None if tok is None else tok.bias
+        conf0, match0 = C.token_scores(d0, wt, bt, head.weight.reshape(-1), head.bias, l0)
+        conf1, match1 = C.token_scores(d1, wt, bt, head.weight.reshape(-1), head.bias, l1)
+        keep0, cnt0 = C.prune_plan(conf0, match0, thr, min_match, l0)
+        keep1, cnt1 = C.prune_plan(conf1, match1, thr, min_match, l1)
+        counts = torch.cat([cnt0, cnt1], 1).tolist()  # the one host sync of this layer: (kept0, unconf0, kept1, unconf1)
+        nact = len(counts)
+        stop = [False] * nact
+        if do_early_stop:  # check_if_stop (lightglue.py:595-606) per pair, fp32 arithmetic
+            idl = ids.tolist()
+            for j, (k0, u0, k1, u1) in enumerate(counts):
+                ratio = np.float32(1.0) - np.float32(u0 + u1) / np.float32(denom[idl[j]])
+                stop[j] = bool(ratio > np.float32(conf.depth_confidence))
+        E = [j for j in range(nact) if stop[j]]
+        R = [j for j in range(nact) if not stop[j]]
+        if E:
+            sel = None if not R else torch.tensor(E, device=dev)
+            finalize(i, eng, sel, d0, d1, [l0h[j] for j in E], [l1h[j] for j in E])
+            if do_point_pruning:
+                ide = ids if sel is None else ids.index_select(0, sel)
+                out_p0[ide] = pr0 if sel is None else pr0.index_select(0, sel)
+                out_p1[ide] = pr1 if sel is None else pr1.index_select(0, sel)
+        if not R:
+            break
+        if E:  # the survivors stay, in order
+            sel = torch.tensor(R, device=dev)
+            pick = lambda t: None if t is None else t.index_select(0, sel)
+            d0, d1, l0, l1, ind0, ind1, ids, pr0, pr1, keep0, keep1, cnt0, cnt1 = map(
+                pick, (d0, d1, l0, l1, ind0, ind1, ids, pr0, pr1, keep0, keep1, cnt0, cnt1))
+            cs0, cs1 = (pick(cs0[0]), pick(cs0[1])), (pick(cs1[0]), pick(cs1[1]))
+            l0h, l1h = [l0h[j] for j in R], [l1h[j] for j in R]
+        if do_point_pruning:
+            k0 = [counts[j][0] for j in R]
+            k1 = [counts[j][2] for j in R]
+            if min(k0) == 0 or min(k1) == 0:
+                raise RuntimeError("every keypoint of one image was pruned (the reference's max() would raise too)")
+            dropped = any(a < b for a, b in zip(k0, l0h)) or any(a < b for a, b in zip(k1, l1h))
+            # order-preserving compaction of every pair + prune[ind] += 1 on the kept points (lightglue.py:536-547)
+            g0 = C.prune_gather(d0, cs0[0], cs0[1], ind0, keep0, cnt0, pr0, zero=True)
+            g1 = C.prune_gather(d1, cs1[0], cs1[1], ind1, keep1, cnt1, pr1, zero=True)
+            if dropped or E:
+                mk, nk = max(k0), max(k1)
+                cut = lambda t, k: t[:, :k].contiguous()
+                d0, cs0, ind0 = cut(g0[0], mk), (cut(g0[1], mk), cut(g0[2], mk)), cut(g0[3], mk)
+                d1, cs1, ind1 = cut(g1[0], nk), (cut(g1[1], nk), cut(g1[2], nk)), cut(g1[3], nk)
+                l0h, l1h = k0, k1
+                l0 = torch.tensor(k0, device=dev, dtype=torch.int32)
+                l1 = torch.tensor(k1, device=dev, dtype=torch.int32)
+                eng = model._engine(len(R), mk, nk, dev)
+                eng.load_rows(d0, d1, cs0, cs1)
+        elif E:
+            eng = model._engine(len(R), d0.shape[1], d1.shape[1], dev)
+            eng.load_rows(d0.contiguous(), d1.contiguous(), cs0, cs1)
+
+    pred = {
+        "matches0": out_m0[:, :m].contiguous(), "matches1": out_m1[:, :n].contiguous(),
+        "matching_scores0": out_s0[:, :m].contiguous(), "matching_scores1": out_s1[:, :n].contiguous(),
+        "log_assignment": assignments, "exit_layer": exit_layer,
+    }
+    if do_point_pruning:
+        pred["prune0"], pred["prune1"] = out_p0, out_p1
+    else:
+        pred["prune0"] = torch.ones_like(pred["matching_scores0"]) * L
+        pred["prune1"] = torch.ones_like(pred["matching_scores1"]) * L
+    # descriptors of the last layer exist only for pairs that ran all layers: left out of the batched contract
+    pred["ref_descriptors0"] = out_s0.new_zeros((B, 0, m, conf.descriptor_dim))
+    pred["ref_descriptors1"] = out_s1.new_zeros((B, 0, n, conf.descriptor_dim))
+    return pred

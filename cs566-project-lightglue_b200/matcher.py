@@ -266,9 +266,11 @@ class LightGlue(nn.Module):
         eng.load(desc0, desc1, cs0, cs1)
 
         if do_early_stop or do_point_pruning:
-            from .adaptive import forward_adaptive
+            from .adaptive import forward_adaptive, forward_adaptive_batched
 
-            return forward_adaptive(self, eng, cs0, cs1)
+            if b == 1 and len0 is None:
+                return forward_adaptive(self, eng, cs0, cs1)
+            return forward_adaptive_batched(self, eng, cs0, cs1, len0, len1)
 
         L = conf.n_layers
         eng.run_layers(L, len0, len1, use_graph=bool(conf.b200.cuda_graph))

@@ -126,6 +126,79 @@ def test_adaptive_forward_vs_golden(name):
         assert abs(la.shape[2] - meta["la_shape"][2]) <= 0.01 * meta["la_shape"][2] + 1
 
 
+def _slice_pair(data, b):
+    return {k: ({kk: vv[b:b + 1] for kk, vv in v.items()} if isinstance(v, dict) else v[b:b + 1]) for k, v in data.items()}
+
+
+@pytest.mark.parametrize("name", ["adaptive_both_512x400", "adaptive_width_300x400", "adaptive_depth_300x400"])
+def test_adaptive_batched_copies_vs_golden(name):
+    """the batched adaptive forward on a batch made of copies of the golden pair must
+    give, for every copy, what the reference gave for the single pair."""
+    meta, g = load_golden("fwd_" + name)
+    conf, sd, data = _golden_inputs(meta)
+    data = {k: ({kk: vv.repeat(3, 1) for kk, vv in v.items()} if isinstance(v, dict) else v.repeat(3, 1, 1))
+            for k, v in data.items()}
+    pred = _model(conf, sd)(_cuda(data))
+    assert len(pred["log_assignment"]) == 3 and pred["matches0"].shape == (3, meta["m"])
+    for b in range(3):
+        la = pred["log_assignment"][b].cpu().numpy()
+        p0 = pred["prune0"][b:b + 1].cpu().numpy()
+        assert p0.dtype == g["prune0"].dtype and (p0 == g["prune0"]).mean() > 0.99
+        if list(la.shape) == meta["la_shape"]:
+            assert np.abs(la - g["log_assignment"]).max() < BF16_TOL
+            assert (pred["matches0"][b:b + 1].cpu().numpy() == g["matches0"]).mean() > 0.97
+            assert np.abs(pred["matching_scores0"][b:b + 1].cpu().numpy() - g["matching_scores0"]).max() < BF16_TOL
+        else:
+            assert abs(la.shape[1] - meta["la_shape"][1]) <= 0.01 * meta["la_shape"][1] + 1
+
+
+@pytest.mark.parametrize("depth,width", [(0.95, 0.95), (-1, 0.95), (0.95, -1)])
+def test_adaptive_batched_vs_single_and_oracle(depth, width):
+    """A batch of DIFFERENT pairs (and one with fewer valid keypoints): every pair must get the exit layer, prune
+    counters and matches it gets when run alone through the same kernels, and pair 0 those of the oracle."""
+    conf = {"filter_threshold": 0.1, "depth_confidence": depth, "width_confidence": width}
+    sd = W.make_state_dict(conf, seed=0, adaptive_fixture=True)
+    data = W.make_inputs(4, 384, 300, seed=11, image_size=(640, 480), correlated=0.7)
+    model = _model(conf, sd)
+    pred = model(_cuda(data))
+    exits = pred["exit_layer"].tolist()
+    kept = [tuple(pred["log_assignment"][b].shape[1:]) for b in range(4)]
+    print(f"depth={depth} width={width}: exit layers {exits}, kept {kept}")
+    for b in range(4):
+        one = model(_cuda(_slice_pair(data, b)))
+        assert int(one["exit_layer"]) == exits[b]
+        assert torch.equal(one["prune0"], pred["prune0"][b:b + 1]) and torch.equal(one["prune1"], pred["prune1"][b:b + 1])
+        assert one["log_assignment"].shape == pred["log_assignment"][b].shape
+        assert (one["log_assignment"] - pred["log_assignment"][b]).abs().max() < 1e-3
+        assert (one["matches0"] == pred["matches0"][b:b + 1]).float().mean() > 0.995
+        assert (one["matching_scores1"] - pred["matching_scores1"][b:b + 1]).abs().max() < 1e-3
+    ref = O.forward(sd, conf, _slice_pair(data, 0))
+    la = pred["log_assignment"][0].cpu()
+    if la.shape == ref["log_assignment"].shape:
+        assert (la - ref["log_assignment"]).abs().max() < BF16_TOL
+        assert (pred["matches0"][0:1].cpu() == ref["matches0"]).float().mean() > 0.97
+    assert (pred["prune0"][0:1].cpu() == ref["prune0"]).float().mean() > 0.99
+
+
+def test_adaptive_batched_varlen_self_consistent():
+    """Adaptive + variable keypoint counts in one batch: pair b equals the same pair run alone with the same padding."""
+    conf = {"filter_threshold": 0.1, "depth_confidence": 0.95, "width_confidence": 0.95}
+    sd = W.make_state_dict(conf, seed=0, adaptive_fixture=True)
+    data = _cuda(W.make_inputs(3, 320, 260, seed=12, image_size=(640, 480), correlated=0.7))
+    lens0, lens1 = [320, 200, 131], [260, 260, 97]
+    data["num_keypoints0"], data["num_keypoints1"] = torch.tensor(lens0).cuda(), torch.tensor(lens1).cuda()
+    model = _model(conf, sd)
+    pred = model(data)
+    for b in range(3):
+        one_data = _slice_pair({k: v for k, v in data.items()}, b)
+        one = model(one_data)
+        assert one["exit_layer"].tolist() == pred["exit_layer"][b:b + 1].tolist()
+        assert torch.equal(one["prune0"], pred["prune0"][b:b + 1])
+        assert one["log_assignment"][0].shape == pred["log_assignment"][b].shape
+        assert (one["matches0"] == pred["matches0"][b:b + 1]).float().mean() > 0.995
+        assert (pred["matches0"][b, lens0[b]:] == -1).all() and (pred["prune0"][b, lens0[b]:] == 0).all()
+
+
 def test_cuda_graph_replay_matches_eager():
     """Same shape called repeatedly: eager first call, graph capture on the second, replay afterwards.
     Every call must give bit-identical results to a graph-free model on the same inputs."""
