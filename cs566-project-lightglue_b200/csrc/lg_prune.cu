@@ -18,57 +18,77 @@ namespace lg {
 
 __device__ __forceinline__ float sigmoidf(float x) { return 1.f / (1.f + expf(-x)); }
 
-// warp per token: two 256-long dot products from ONE read of the row
-// grid (ceil(N/8), B), block 256
+// warp per 4 tokens: two 256-long dot products from ONE read of each row, all eight 16-byte loads of the lane
+// in flight before the first use (the pass is a pure HBM stream of the descriptors)
+// grid (ceil(N/32), B), block 256
+constexpr int kRowsPerWarp = 4;
 __global__ void __launch_bounds__(256) token_scores_kernel(const float* __restrict__ desc,
                                                            const float* __restrict__ w_tok, const float* __restrict__ b_tok,
                                                            const float* __restrict__ w_match,
                                                            const float* __restrict__ b_match, const int* __restrict__ len,
                                                            float* __restrict__ conf, float* __restrict__ match, int N) {
   const int b = blockIdx.y, lane = threadIdx.x & 31;
-  const int n = blockIdx.x * 8 + (threadIdx.x >> 5);
+  const int n0 = (blockIdx.x * 8 + (threadIdx.x >> 5)) * kRowsPerWarp;
   const int nv = len ? min(len[b], N) : N;
-  if (n >= N) return;
-  float st = 0.f, sm = 0.f;
-  if (n < nv) {
-    const float4* row = reinterpret_cast<const float4*>(desc + (static_cast<size_t>(b) * N + n) * 256);
+  if (n0 >= N) return;
+  float4 x[kRowsPerWarp][2];
+#pragma unroll
+  for (int r = 0; r < kRowsPerWarp; ++r) {
+    const bool ok = n0 + r < nv;
+    const float4* row = reinterpret_cast<const float4*>(desc + (static_cast<size_t>(b) * N + (ok ? n0 + r : n0)) * 256);
+#pragma unroll
+    for (int h = 0; h < 2; ++h) x[r][h] = ok ? __ldcs(row + h * 32 + lane) : make_float4(0.f, 0.f, 0.f, 0.f);
+  }
+  float4 wm[2], wt[2];
+#pragma unroll
+  for (int h = 0; h < 2; ++h) {
+    wm[h] = __ldg(reinterpret_cast<const float4*>(w_match) + h * 32 + lane);
+    wt[h] = w_tok ? __ldg(reinterpret_cast<const float4*>(w_tok) + h * 32 + lane) : make_float4(0.f, 0.f, 0.f, 0.f);
+  }
+#pragma unroll
+  for (int r = 0; r < kRowsPerWarp; ++r) {
+    float sm = 0.f, st = 0.f;
 #pragma unroll
     for (int h = 0; h < 2; ++h) {
-      const float4 x = __ldg(row + h * 32 + lane);
-      const float4 wm = __ldg(reinterpret_cast<const float4*>(w_match) + h * 32 + lane);
-      sm += x.x * wm.x + x.y * wm.y + x.z * wm.z + x.w * wm.w;
-      if (w_tok) {
-        const float4 wt = __ldg(reinterpret_cast<const float4*>(w_tok) + h * 32 + lane);
-        st += x.x * wt.x + x.y * wt.y + x.z * wt.z + x.w * wt.w;
-      }
+      sm += x[r][h].x * wm[h].x + x[r][h].y * wm[h].y + x[r][h].z * wm[h].z + x[r][h].w * wm[h].w;
+      st += x[r][h].x * wt[h].x + x[r][h].y * wt[h].y + x[r][h].z * wt[h].z + x[r][h].w * wt[h].w;
     }
-  }
-  sm = warp_sum(sm);
-  st = warp_sum(st);
-  if (lane == 0) {
-    const size_t o = static_cast<size_t>(b) * N + n;
-    match[o] = n < nv ? sigmoidf(sm + b_match[0]) : 0.f;
-    if (conf) conf[o] = (n < nv && w_tok) ? sigmoidf(st + b_tok[0]) : 0.f;
+    sm = warp_sum(sm);
+    st = warp_sum(st);
+    const int n = n0 + r;
+    if (lane == 0 && n < N) {
+      const size_t o = static_cast<size_t>(b) * N + n;
+      match[o] = n < nv ? sigmoidf(sm + b_match[0]) : 0.f;
+      if (conf) conf[o] = (n < nv && w_tok) ? sigmoidf(st + b_tok[0]) : 0.f;
+    }
   }
 }
 
-// warp per row: one 256-long dot product + bias (matchability logits for the assignment, lightglue.py:313-314)
+// warp per 4 rows: one 256-long dot product + bias (matchability logits for the assignment, lightglue.py:313-314)
 __global__ void __launch_bounds__(256) logit_rows_kernel(const float* __restrict__ x, const float* __restrict__ w,
                                                          const float* __restrict__ bias, float* __restrict__ out,
                                                          int64_t rows) {
   const int lane = threadIdx.x & 31;
-  const int64_t n = static_cast<int64_t>(blockIdx.x) * 8 + (threadIdx.x >> 5);
-  if (n >= rows) return;
-  const float4* row = reinterpret_cast<const float4*>(x + n * 256);
-  float acc = 0.f;
+  const int64_t n0 = (static_cast<int64_t>(blockIdx.x) * 8 + (threadIdx.x >> 5)) * kRowsPerWarp;
+  if (n0 >= rows) return;
+  float4 v[kRowsPerWarp][2];
 #pragma unroll
-  for (int h = 0; h < 2; ++h) {
-    const float4 v = __ldg(row + h * 32 + lane);
-    const float4 ww = __ldg(reinterpret_cast<const float4*>(w) + h * 32 + lane);
-    acc += v.x * ww.x + v.y * ww.y + v.z * ww.z + v.w * ww.w;
+  for (int r = 0; r < kRowsPerWarp; ++r) {
+    const float4* row = reinterpret_cast<const float4*>(x + min(n0 + r, rows - 1) * 256);
+#pragma unroll
+    for (int h = 0; h < 2; ++h) v[r][h] = __ldcs(row + h * 32 + lane);
   }
-  acc = warp_sum(acc);
-  if (lane == 0) out[n] = acc + bias[0];
+  float4 ww[2];
+#pragma unroll
+  for (int h = 0; h < 2; ++h) ww[h] = __ldg(reinterpret_cast<const float4*>(w) + h * 32 + lane);
+#pragma unroll
+  for (int r = 0; r < kRowsPerWarp; ++r) {
+    float acc = 0.f;
+#pragma unroll
+    for (int h = 0; h < 2; ++h) acc += v[r][h].x * ww[h].x + v[r][h].y * ww[h].y + v[r][h].z * ww[h].z + v[r][h].w * ww[h].w;
+    acc = warp_sum(acc);
+    if (lane == 0 && n0 + r < rows) out[n0 + r] = acc + bias[0];
+  }
 }
 
 // one block per image: keep flags -> exclusive scan -> ascending list of kept positions.
@@ -147,7 +167,7 @@ extern "C" int lg_token_scores(const float* desc, const float* w_tok, const floa
   if (!desc || !w_match || !b_match || !match) return LG_ERR_NULL;
   if ((w_tok == nullptr) != (b_tok == nullptr) || (w_tok && !conf)) return LG_ERR_NULL;
   if (B <= 0 || N <= 0) return LG_ERR_SHAPE;
-  lg::token_scores_kernel<<<dim3((N + 7) / 8, B), 256, 0, stream>>>(desc, w_tok, b_tok, w_match, b_match, len, conf,
+  lg::token_scores_kernel<<<dim3((N + 31) / 32, B), 256, 0, stream>>>(desc, w_tok, b_tok, w_match, b_match, len, conf,
                                                                     match, N);
   return static_cast<int>(cudaGetLastError());
 }
@@ -177,6 +197,6 @@ extern "C" int lg_logit_rows(const float* x, const float* w, const float* bias, 
   if (!x || !w || !bias || !out) return LG_ERR_NULL;
   if (rows <= 0 || rows > (static_cast<int64_t>(1) << 33)) return LG_ERR_SHAPE;
   if ((reinterpret_cast<uintptr_t>(x) | reinterpret_cast<uintptr_t>(w)) & 15) return LG_ERR_ALIGN;
-  lg::logit_rows_kernel<<<static_cast<unsigned>((rows + 7) / 8), 256, 0, stream>>>(x, w, bias, out, rows);
+  lg::logit_rows_kernel<<<static_cast<unsigned>((rows + 31) / 32), 256, 0, stream>>>(x, w, bias, out, rows);
   return static_cast<int>(cudaGetLastError());
 }

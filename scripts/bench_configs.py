@@ -1,0 +1,73 @@
+"""BASELINE configs 3 and 4 on one GPU; bench.py carries config 2.
+  config 3: adaptive LightGlue, depth_confidence = width_confidence = 0.95, 32 pairs x 2048 kpts, adaptive fixture
+            weights (random init never exits): pairs/s, exit-layer histogram, kept-token counts.
+  config 4: DISK-shaped 128-d descriptors (input_proj), padded to 4096 kpts, per-image valid counts U{2048..4096}.
+Prints one JSON line per config (device-resident inputs, CUDA events, 3 warm-ups)."""
+import collections, importlib, json, os, sys
+import numpy as np
+import torch
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+PKG = "cs566-project-lightglue_b200"
+W = importlib.import_module(PKG + ".weights")
+M = importlib.import_module(PKG + ".matcher")
+
+
+def cuda(data):
+    return {k: ({kk: vv.cuda() for kk, vv in v.items()} if isinstance(v, dict) else v.cuda()) for k, v in data.items()}
+
+
+def timed(model, data, steps, warmup=3):
+    for _ in range(warmup):
+        pred = model(data)
+    torch.cuda.synchronize()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for _ in range(steps):
+        pred = model(data)
+    e1.record()
+    torch.cuda.synchronize()
+    return e0.elapsed_time(e1) / steps, pred
+
+
+def config3(B=32, N=2048, steps=5):
+    conf = {"filter_threshold": 0.1, "depth_confidence": 0.95, "width_confidence": 0.95}
+    sd = W.make_state_dict(conf, seed=0, adaptive_fixture=True)
+    model = M.LightGlue(conf)
+    model.load_state_dict(sd)
+    model = model.cuda()
+    data = cuda(W.make_inputs(B, N, N, seed=1, correlated=0.7))
+    ms, pred = timed(model, data, steps)
+    exits = collections.Counter(pred["exit_layer"].tolist())
+    kept = [tuple(int(x) - 1 for x in pred["log_assignment"][b].shape[1:]) for b in range(B)]
+    one = cuda(W.make_inputs(1, N, N, seed=1, correlated=0.7))
+    ms1, _ = timed(model, one, steps)
+    full = M.LightGlue({"filter_threshold": 0.1})
+    full.load_state_dict(sd)
+    ms_full, _ = timed(full.cuda(), data, steps)
+    print(json.dumps({"config": "3: adaptive depth=width=0.95, %d pairs x %d kpts, adaptive-fixture weights" % (B, N),
+                      "pairs_per_s": B / ms * 1e3, "ms_per_batch": ms, "exit_layer_histogram": dict(sorted(exits.items())),
+                      "kept0_min_mean_max": [min(k[0] for k in kept), float(np.mean([k[0] for k in kept])), max(k[0] for k in kept)],
+                      "kept1_min_mean_max": [min(k[1] for k in kept), float(np.mean([k[1] for k in kept])), max(k[1] for k in kept)],
+                      "one_pair_per_call_pairs_per_s": 1e3 / ms1,
+                      "non_adaptive_same_weights_pairs_per_s": B / ms_full * 1e3}))
+
+
+def config4(B=8, NPAD=4096, steps=5):
+    conf = {"filter_threshold": 0.1, "input_dim": 128}
+    sd = W.make_state_dict(conf, seed=0)
+    model = M.LightGlue(conf)
+    model.load_state_dict(sd)
+    model = model.cuda()
+    data = cuda(W.make_inputs(B, NPAD, NPAD, d_in=128, seed=2, correlated=0.7))
+    rng = np.random.default_rng(4)
+    l0, l1 = rng.integers(2048, NPAD + 1, B), rng.integers(2048, NPAD + 1, B)
+    data["num_keypoints0"], data["num_keypoints1"] = torch.tensor(l0).cuda(), torch.tensor(l1).cuda()
+    ms, pred = timed(model, data, steps)
+    print(json.dumps({"config": "4: DISK-shaped 128-d descriptors, %d pairs padded to %d kpts, valid counts U{2048..%d}" % (B, NPAD, NPAD),
+                      "pairs_per_s": B / ms * 1e3, "ms_per_batch": ms, "valid0": l0.tolist(), "valid1": l1.tolist(),
+                      "matches_per_pair_mean": float((pred["matches0"] >= 0).sum(1).float().mean())}))
+
+
+if __name__ == "__main__":
+    config3()
+    config4()
