@@ -263,6 +263,34 @@ def run_b200(a):
                 "launches_timed": len(ev), "avg_launch_ms": attn_ms / max(len(ev), 1),
                 "share_of_step": attn_ms / max(min(a.steps, 3), 1) / (ms / a.steps)}
 
+    # ---- the HBM-bound pass: assignment + filter on the engine left resident by the last step (final_proj tiles,
+    # matchability logits, strip pass 1, reduce, strip pass 2 with keys, filter).  Algorithmic bytes per pair
+    # (SURVEY.md 8(d)): write (M+1)(N+1)*4 + read 2*N*256*4 of projected descriptors.
+    eng = model._engine(a.batch, a.kpts, a.kpts, dev, cached=True)
+    rows0, rows1 = eng.rows()
+    n_layers = model.conf.n_layers
+
+    def assign_step():
+        model._assign(n_layers - 1, eng, rows0, rows1, None, None, th=model.conf.filter_threshold)
+
+    for _ in range(3):
+        assign_step()
+    torch.cuda.synchronize()
+    ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    ev0.record()
+    for _ in range(10):
+        assign_step()
+    ev1.record()
+    torch.cuda.synchronize()
+    assign_ms = ev0.elapsed_time(ev1) / 10
+    assign_bytes = a.batch * ((a.kpts + 1) ** 2 * 4 + 2 * a.kpts * 256 * 4)
+    hbm_peak = float(peaks.get("hbm_gbs", 6500.0))
+    assign_gbs = assign_bytes / (assign_ms / 1e3) / 1e9
+    roofline_assign = {"kernel": "assign_strip_kernel<1|2> + reduce + filter_finalize (final_proj and logits included)",
+                       "bound": "hbm", "achieved": assign_gbs, "peak": hbm_peak, "unit": "GB/s",
+                       "frac": assign_gbs / hbm_peak, "ms": assign_ms, "algorithmic_bytes": assign_bytes,
+                       "share_of_step": assign_ms / (ms / a.steps)}
+
     if rank == 0:
         cpu = None  # timed at N=1 only (under torchrun the other ranks' host threads would share the cores)
         if world == 1:
@@ -282,6 +310,7 @@ def run_b200(a):
                     "unpipelined_ms_per_step": ms_e2e_sync / a.steps},
             "gpu_launches": launches,
             "roofline": roofline,
+            "roofline_assignment": roofline_assign,
             "cpu_baseline": cpu,
             "clocks": sampler.summary(),
         }
