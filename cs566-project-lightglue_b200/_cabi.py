@@ -49,6 +49,10 @@ SIGNATURES = {
     "lg_assign_tiles_ws_bytes": (_c.c_size_t, [_I, _I, _I]),
     "lg_assign_tiles": (_I, [_P, _P, _I, _I, _P, _P, _P, _P, _F, _P, _P, _P, _I, _I, _I, _P]),
     "lg_logit_rows": (_I, [_P, _P, _P, _P, _L, _P]),
+    "lg_gemm_f32": (_I, [_P, _P, _P, _P, _P, _I, _I, _I, _L, _L, _L, _L, _I, _F, _I, _I, _P, _P, _P, _P]),
+    "lg_softmax_rows_f32": (_I, [_P, _P, _P, _I, _I, _I, _I, _L, _P]),
+    "lg_rotary_rows_f32": (_I, [_P, _P, _P, _L, _L, _I, _I, _I, _P]),
+    "lg_ln_gelu_rows_f32": (_I, [_P, _P, _P, _F, _L, _I, _P]),
 }
 
 _lib = None
@@ -441,4 +445,40 @@ def attention_tiles(q_tiles, k_tiles, v_tiles, out_tiles, rt_base: int, nq, nk, 
     if ATTN_EVENTS is not None:
         e1.record()
         ATTN_EVENTS.append((e0, e1, (3.0 if cross else 4.0) * 64 * nq * nk * B * H))
+    _count(1)
+
+
+# ----------------------------------------------------------------------------- fp32 path (lg_fp32.cu)
+def gemm_f32(A, B, C, M, N, K, lda, ldb, ldc, *, bias=None, resid=None, ldr=0, b_kn=False, alpha=1.0, batch=1, inner=1,
+             strides=(0,) * 8, m_len=None, k_len=None, offs=(0, 0, 0, 0)):
+    """C = alpha * A . op(B) + bias + resid on raw strided views: A, B, C, resid are the BASE tensors (any shape, f32
+    cuda), `offs` = element offsets of (A, B, C, resid) inside them, `strides` = (outer, inner) element strides of the
+    batch index for A, B, C, resid.  See lg_gemm_f32 in include/lg_b200.h."""
+    st = (_c.c_int64 * 8)(*[int(v) for v in strides])
+    pa, pb, pc = A.data_ptr() + 4 * offs[0], B.data_ptr() + 4 * offs[1], C.data_ptr() + 4 * offs[2]
+    pr = None if resid is None else resid.data_ptr() + 4 * offs[3]
+    _check(lib().lg_gemm_f32(pa, pb, pc, _ptr(bias), pr, M, N, K, lda, ldb, ldc, ldr, int(b_kn), float(alpha), batch,
+                             inner, st, _ptr(_i32(m_len)), _ptr(_i32(k_len)), _stream()), "lg_gemm_f32")
+    _count(1)
+
+
+def softmax_rows_f32(s, m_len=None, n_len=None, n=None):
+    """s (B,H,M,pitch) f32, in place over the first n (<= pitch) columns."""
+    B, H, M, pitch = s.shape
+    _check(lib().lg_softmax_rows_f32(_ptr(_f32c(s, "s")), _ptr(_i32(m_len)), _ptr(_i32(n_len)), B, H, M,
+                                     pitch if n is None else n, pitch, _stream()), "lg_softmax_rows_f32")
+    _count(1)
+
+
+def rotary_rows_f32(x, cos, sin, q_off, k_off, heads):
+    rows, ld = x.shape[0] * x.shape[1], x.shape[2]
+    _check(lib().lg_rotary_rows_f32(_ptr(_f32c(x, "x")), _ptr(_f32c(cos, "cos")), _ptr(_f32c(sin, "sin")), rows, ld,
+                                    q_off, k_off, heads, _stream()), "lg_rotary_rows_f32")
+    _count(1)
+
+
+def ln_gelu_rows_f32(x, gamma, beta, eps):
+    width = x.shape[-1]
+    _check(lib().lg_ln_gelu_rows_f32(_ptr(_f32c(x, "x")), _ptr(_f32c(gamma, "gamma")), _ptr(_f32c(beta, "beta")),
+                                     float(eps), x.numel() // width, width, _stream()), "lg_ln_gelu_rows_f32")
     _count(1)

@@ -140,8 +140,8 @@ class LightGlue(nn.Module):
             raise ValueError("the sm_100a kernels are built for descriptor_dim=256, num_heads=4 (no fallback)")
         if conf.add_scale_ori:
             raise NotImplementedError("add_scale_ori (4-d positional input) is not built; SuperPoint/DISK use 2-d")
-        if conf.b200.precision not in ("bf16",):
-            raise ValueError(f"b200.precision={conf.b200.precision!r}: only 'bf16' attention operands are built")
+        if conf.b200.precision not in ("bf16", "fp32"):
+            raise ValueError(f"b200.precision={conf.b200.precision!r}: 'bf16' (tensor-core throughput path) or 'fp32'")
         self.input_proj = nn.Linear(conf.input_dim, d, bias=True) if conf.input_dim != d else nn.Identity()
         self.posenc = _PosEnc(2, (d // h) // 2)
         self.transformers = nn.ModuleList([_Layer(d) for _ in range(L)])
@@ -214,6 +214,34 @@ class LightGlue(nn.Module):
         scale = float(self.conf.descriptor_dim) ** -0.5  # d^-1/4 on both operands (lightglue.py:311-312)
         return C.assign_tiles(a_tiles, b_tiles, eng.tp0, eng.tp1, z0, z1, th, len0, len1, scale=scale)
 
+    def _forward_fp32(self, desc0, desc1, cs0, cs1, len0, len1):
+        """The accuracy mode (engine_fp32.py): IEEE fp32 layer stack, TF32x3 similarity; 1e-4 bound on log_assignment."""
+        from .engine import PackedWeights
+        from .engine_fp32 import Fp32Engine, Fp32Weights, max_pairs
+
+        w = getattr(self, "_w32", None)
+        if w is None or w.signature != PackedWeights.sign(self):
+            w = self._w32 = Fp32Weights(self)
+            w.signature = PackedWeights.sign(self)
+        b, m, n = desc0.shape[0], desc0.shape[1], desc1.shape[1]
+        L, dev = self.conf.n_layers, desc0.device
+        step = min(b, max_pairs(m, n))
+        outs = []
+        for lo in range(0, b, step):
+            hi = min(b, lo + step)
+            cut = lambda t: None if t is None else t[lo:hi].contiguous()
+            eng = Fp32Engine(w, hi - lo, m, n, dev)
+            l0, l1 = cut(len0), cut(len1)
+            d0, d1 = eng.forward(cut(desc0), cut(desc1), (cut(cs0[0]), cut(cs0[1])), (cut(cs1[0]), cut(cs1[1])), l0, l1, L)
+            scores, (m0, m1, ms0, ms1) = eng.assign(L - 1, self.conf.filter_threshold, l0, l1)
+            outs.append((m0, m1, ms0, ms1, d0.clone()[:, None], d1.clone()[:, None], scores))
+        m0, m1, ms0, ms1, r0, r1, scores = (torch.cat(t, 0) if len(outs) > 1 else t[0] for t in zip(*outs))
+        return {
+            "matches0": m0, "matches1": m1, "matching_scores0": ms0, "matching_scores1": ms1,
+            "ref_descriptors0": r0, "ref_descriptors1": r1, "log_assignment": scores,
+            "prune0": torch.ones_like(ms0) * L, "prune1": torch.ones_like(ms1) * L,
+        }
+
     @staticmethod
     def _image_size(data, view, like):
         v = data.get(view)
@@ -262,6 +290,10 @@ class LightGlue(nn.Module):
                        pe.condition_modulation.bias, float(n))
         do_early_stop = conf.depth_confidence > 0
         do_point_pruning = conf.width_confidence > 0
+        if conf.b200.precision == "fp32":
+            if do_early_stop or do_point_pruning:
+                raise NotImplementedError("b200.precision='fp32' runs the full depth (no early exit / pruning)")
+            return self._forward_fp32(desc0, desc1, cs0, cs1, len0, len1)
         eng = self._engine(b, m, n, dev, cached=not (do_early_stop or do_point_pruning))
         eng.load(desc0, desc1, cs0, cs1)
 

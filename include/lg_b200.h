@@ -166,6 +166,28 @@ int lg_assign_tiles(const void* a_tiles, const void* b_tiles, int tpa, int tpb, 
  * lightglue.py:304,313-314, before the log-sigmoid).  x (rows, 256) f32 contiguous. */
 int lg_logit_rows(const float* x, const float* w, const float* bias, float* out, int64_t rows, cudaStream_t stream);
 
+/* fp32 path (b200.precision = "fp32"): IEEE fp32 FMA arithmetic on the CUDA cores for the 1e-4 bound on
+ * log_assignment (the tensor-core path is bounded by 2e-2).
+ * lg_gemm_f32: C = alpha * A . op(B) + bias + resid, strided-batched.  A (M,K) lda; B (N,K) ldb if b_kn == 0
+ *   (Linear layers lightglue.py:168-176,184,203-211,223-228,310,370; q.k^T :151,235) or (K,N) ldb if b_kn == 1
+ *   (P.v :155,241-244); bias (N) / resid (M,N, ldr; may alias C) optional.  Batch index z in [0, batch) maps to
+ *   (outer, inner) = (z / inner, z % inner); element offsets outer*strides[2i] + inner*strides[2i+1] for
+ *   i = A, B, C, resid (strides: 8 host int64).  m_len / k_len: optional valid M / K per OUTER index.
+ * lg_softmax_rows_f32: in-place softmax over the first n_len[b] columns of s (B,H,M,pitch) (others -> 0; rows
+ *   >= m_len[b] -> 0 like the reference's nan_to_num of fully masked rows, :145,149).
+ * lg_rotary_rows_f32: apply_cached_rotary_emb (:36-43) in place on the q block (columns q_off + h*64 ..) and the
+ *   k block (k_off + h*64 ..) of x (rows, ld) with the compact (rows, 32) cos / sin tables of lg_posenc.
+ * lg_ln_gelu_rows_f32: LayerNorm(width, eps, affine) + GELU(erf) in place on x (rows, width) (:173-174). */
+int lg_gemm_f32(const float* A, const float* B, float* C, const float* bias, const float* resid, int M, int N, int K,
+                int64_t lda, int64_t ldb, int64_t ldc, int64_t ldr, int b_kn, float alpha, int batch, int inner,
+                const int64_t* strides, const int* m_len, const int* k_len, cudaStream_t stream);
+int lg_softmax_rows_f32(float* s, const int* m_len, const int* n_len, int B, int H, int M, int N, int64_t pitch,
+                        cudaStream_t stream);
+int lg_rotary_rows_f32(float* x, const float* cos_t, const float* sin_t, int64_t rows, int64_t ld, int q_off, int k_off,
+                       int H, cudaStream_t stream);
+int lg_ln_gelu_rows_f32(float* x, const float* gamma, const float* beta, float eps, int64_t rows, int width,
+                        cudaStream_t stream);
+
 /* (5) adaptive depth / width (lightglue.py:527-547).
  * lg_token_scores: conf (B,N) = sigmoid(w_tok.desc + b_tok) (TokenConfidence.forward :102-107; w_tok NULL
  *   => skipped) and match (B,N) = sigmoid(w_match.desc + b_match) (get_matchability :317-318), one read

@@ -53,6 +53,50 @@ def test_forward_vs_golden(name):
     assert pred["ref_descriptors0"].shape == (meta["batch"], 1, meta["m"], 256)
 
 
+FP32_TOL = 1e-4  # north_star: fp32 path, abs on log_assignment
+
+
+@pytest.mark.parametrize("name", ["sp_b1_192", "sp_b2_160x224", "disk_b1_130x97", "sp_b1_1024"])
+def test_forward_fp32_path_vs_golden(name):
+    """b200.precision = fp32 (csrc/lg_fp32.cu + TF32x3 assignment): log_assignment within 1e-4 of the reference's fp32
+    run, match indices identical up to near-ties."""
+    meta, g = load_golden("fwd_" + name)
+    conf, sd, data = _golden_inputs(meta)
+    pred = _model({**conf, "b200": {"precision": "fp32"}}, sd)(_cuda(data))
+    la = pred["log_assignment"].cpu().numpy()
+    assert list(la.shape) == meta["la_shape"]
+    if "log_assignment" in g:
+        err = np.abs(la - g["log_assignment"]).max()
+    else:
+        err = np.abs(la[:, ::17, ::19] - g["log_assignment_sample"]).max()
+    agree0 = (pred["matches0"].cpu().numpy() == g["matches0"]).mean()
+    serr = np.abs(pred["matching_scores0"].cpu().numpy() - g["matching_scores0"]).max()
+    print(f"fp32 {name}: max|dlog_assignment|={err:.3e} match agreement {agree0:.4f} max|dscore|={serr:.2e}")
+    assert err < FP32_TOL, err
+    assert agree0 > 0.999 and serr < 1e-4
+    assert pred["ref_descriptors0"].shape == (meta["batch"], 1, meta["m"], 256)
+
+
+def test_forward_fp32_path_varlen_vs_golden():
+    meta, g = load_golden("varlen_disk_b3_256")
+    conf = {**meta["conf"], "b200": {"precision": "fp32"}}
+    sd = W.make_state_dict(meta["conf"], seed=meta["weight_seed"])
+    data = _cuda(W.make_inputs(meta["batch"], meta["npad"], meta["npad"], d_in=128, seed=meta["data_seed"],
+                               image_size=tuple(meta["image_size"]), correlated=meta["correlated"]))
+    data["num_keypoints0"] = torch.tensor(meta["len0"]).cuda()
+    data["num_keypoints1"] = torch.tensor(meta["len1"]).cuda()
+    pred = _model(conf, sd)(data)
+    la = pred["log_assignment"].cpu().numpy()
+    M = N = meta["npad"]
+    for p in range(meta["batch"]):
+        a, c = meta["len0"][p], meta["len1"][p]
+        ref = g[f"log_assignment_{p}"][0]
+        assert np.abs(la[p, :a, :c] - ref[:a, :c]).max() < FP32_TOL
+        assert np.abs(la[p, :a, N] - ref[:a, c]).max() < FP32_TOL
+        assert np.abs(la[p, M, :c] - ref[a, :c]).max() < FP32_TOL
+        assert (pred["matches0"][p, :a].cpu().numpy() == g[f"matches0_{p}"][0]).mean() > 0.995
+
+
 def test_forward_varlen_vs_golden():
     meta, g = load_golden("varlen_disk_b3_256")
     conf = meta["conf"]
