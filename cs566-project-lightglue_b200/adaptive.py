@@ -121,7 +121,8 @@ def forward_adaptive_batched(model, eng, cs0, cs1, len0=None, len1=None):
     (:536-547) -- while the kernels run on the whole active set: pruned pairs are compacted to the front of their rows
     and carried as valid lengths (the attention / assignment kernels mask by length), pairs that exit are assigned with
     the head of their exit layer and leave the batch, and the survivors are re-tiled to the longest kept length.
-    One small device->host read per layer (kept / unconfident counts), like the reference's per-layer Python `if`."""
+    One small device->host read per layer (kept / unconfident counts), like the reference's per-layer Python `if`; the
+    compaction for the next layer is queued before that read, so a layer where nobody exits costs the GPU no wait."""
     conf = model.conf
     B, m, n = eng.B, eng.M, eng.N
     dev = eng.dev
@@ -154,20 +155,20 @@ def forward_adaptive_batched(model, eng, cs0, cs1, len0=None, len1=None):
     exit_layer = torch.full((B,), L - 1, dtype=torch.int64)
     assignments = PrunedAssignments(B)
 
-    def finalize(layer, e, sel, d0, d1, k0, k1):
-        """Assignment + filter of the active rows `sel` (None = all) with the head of `layer`, scattered back to the
-        original keypoint indices of their pairs (lightglue.py:549-562)."""
-        if sel is None:
-            ee, d0e, d1e, l0e, l1e, i0e, i1e, ide = e, d0, d1, l0, l1, ind0, ind1, ids
-        else:
+    def finalize(layer, e, sel, d0, d1, l0e, l1e, i0e, i1e, ide, k0, k1):
+        """Assignment + filter of pairs with the head of `layer`, scattered back to the original keypoint indices of
+        their pairs (lightglue.py:549-562).  `e`: an engine whose tiles hold exactly these rows, or None (then the rows
+        `d0, d1` -- after `sel` -- are tiled into a fresh one)."""
+        if sel is not None:
             pick = lambda t: None if t is None else t.index_select(0, sel)
-            d0e, d1e, l0e, l1e, i0e, i1e, ide = map(pick, (d0, d1, l0, l1, ind0, ind1, ids))
-            ee = model._engine(d0e.shape[0], d0e.shape[1], d1e.shape[1], dev)
-            ee.load_rows(d0e, d1e)
-        scores, (f0, f1, fs0, fs1) = model._assign(layer, ee, d0e, d1e, l0e, l1e, th=th)
+            d0, d1, l0e, l1e, i0e, i1e, ide = map(pick, (d0, d1, l0e, l1e, i0e, i1e, ide))
+        if e is None or sel is not None:
+            e = model._engine(d0.shape[0], d0.shape[1], d1.shape[1], dev)
+            e.load_rows(d0.contiguous(), d1.contiguous())
+        scores, (f0, f1, fs0, fs1) = model._assign(layer, e, d0, d1, l0e, l1e, th=th)
         rows = ide[:, None]
         if do_point_pruning:
-            mc, nc = d0e.shape[1], d1e.shape[1]
+            mc, nc = d0.shape[1], d1.shape[1]
             t0, t1 = i0e, i1e
             if l0e is not None:  # padding rows land in the spare column
                 t0 = torch.where(torch.arange(mc, device=dev)[None] < l0e[:, None], i0e, m)
@@ -185,11 +186,13 @@ def forward_adaptive_batched(model, eng, cs0, cs1, len0=None, len1=None):
             assignments._set(b, scores, j, k0[j], k1[j])
             exit_layer[b] = layer
 
+    counts_host = torch.empty(B, 4, dtype=torch.int32).pin_memory()
+    ready = torch.cuda.Event()
     for i in range(L):
         eng.layer(i, l0, l1)
         d0, d1 = eng.rows()
         if i == L - 1:
-            finalize(i, eng, None, d0, d1, l0h, l1h)
+            finalize(i, eng, None, d0, d1, l0, l1, ind0, ind1, ids, l0h, l1h)
             if do_point_pruning:
                 out_p0[ids], out_p1[ids] = pr0, pr1
             break
@@ -202,8 +205,22 @@ def forward_adaptive_batched(model, eng, cs0, cs1, len0=None, len1=None):
         conf1, match1 = C.token_scores(d1, wt, bt, head.weight.reshape(-1), head.bias, l1)
         keep0, cnt0 = C.prune_plan(conf0, match0, thr, min_match, l0)
         keep1, cnt1 = C.prune_plan(conf1, match1, thr, min_match, l1)
-        counts = torch.cat([cnt0, cnt1], 1).tolist()  # the one host sync of this layer: (kept0, unconf0, kept1, unconf1)
-        nact = len(counts)
+        nact = d0.shape[0]
+        counts_host[:nact].copy_(torch.cat([cnt0, cnt1], 1), non_blocking=True)  # (kept0, unconf0, kept1, unconf1)
+        ready.record()
+        g0 = g1 = None
+        if do_point_pruning:
+            # Speculation, queued BEFORE the host waits for the counts: order-preserving compaction of every pair
+            # + prune[ind] += 1 on the kept points (lightglue.py:536-547), into the same tile geometry with the new
+            # lengths on the device.  If nobody exits and no tile pair is freed (the common layer), the next layer
+            # starts right behind it -- the GPU never waits for the host.
+            pr0_prev, pr1_prev = pr0.clone(), pr1.clone()
+            g0 = C.prune_gather(d0, cs0[0], cs0[1], ind0, keep0, cnt0, pr0, zero=True)
+            g1 = C.prune_gather(d1, cs1[0], cs1[1], ind1, keep1, cnt1, pr1, zero=True)
+            l0n, l1n = cnt0[:, 0].contiguous(), cnt1[:, 0].contiguous()
+            eng.load_rows(g0[0], g1[0], (g0[1], g0[2]), (g1[1], g1[2]))
+        ready.synchronize()  # the one host read of this layer
+        counts = counts_host[:nact].tolist()
         stop = [False] * nact
         if do_early_stop:  # check_if_stop (lightglue.py:595-606) per pair, fp32 arithmetic
             idl = ids.tolist()
@@ -212,44 +229,40 @@ def forward_adaptive_batched(model, eng, cs0, cs1, len0=None, len1=None):
                 stop[j] = bool(ratio > np.float32(conf.depth_confidence))
         E = [j for j in range(nact) if stop[j]]
         R = [j for j in range(nact) if not stop[j]]
-        if E:
+        k0 = [counts[j][0] for j in R]
+        k1 = [counts[j][2] for j in R]
+        if do_point_pruning and R and (min(k0) == 0 or min(k1) == 0):
+            raise RuntimeError("every keypoint of one image was pruned (the reference's max() would raise too)")
+        if not E and (not do_point_pruning or (C.tiles_pad(max(k0)) == eng.tp0 and C.tiles_pad(max(k1)) == eng.tp1)):
+            if do_point_pruning:  # the speculated state is the state
+                cs0, cs1, ind0, ind1 = (g0[1], g0[2]), (g1[1], g1[2]), g0[3], g1[3]
+                l0, l1, l0h, l1h = l0n, l1n, k0, k1
+            continue
+        if E:  # exits are assigned from the rows of THIS layer, before its pruning (the reference breaks first)
             sel = None if not R else torch.tensor(E, device=dev)
-            finalize(i, eng, sel, d0, d1, [l0h[j] for j in E], [l1h[j] for j in E])
+            finalize(i, None, sel, d0, d1, l0, l1, ind0, ind1, ids, [l0h[j] for j in E], [l1h[j] for j in E])
             if do_point_pruning:
                 ide = ids if sel is None else ids.index_select(0, sel)
-                out_p0[ide] = pr0 if sel is None else pr0.index_select(0, sel)
-                out_p1[ide] = pr1 if sel is None else pr1.index_select(0, sel)
+                out_p0[ide] = pr0_prev if sel is None else pr0_prev.index_select(0, sel)
+                out_p1[ide] = pr1_prev if sel is None else pr1_prev.index_select(0, sel)
         if not R:
             break
-        if E:  # the survivors stay, in order
-            sel = torch.tensor(R, device=dev)
-            pick = lambda t: None if t is None else t.index_select(0, sel)
-            d0, d1, l0, l1, ind0, ind1, ids, pr0, pr1, keep0, keep1, cnt0, cnt1 = map(
-                pick, (d0, d1, l0, l1, ind0, ind1, ids, pr0, pr1, keep0, keep1, cnt0, cnt1))
+        # survivors, in order: re-tiled to the longest kept length
+        sel = torch.tensor(R, device=dev) if E else None
+        pick = lambda t: t if (t is None or sel is None) else t.index_select(0, sel)
+        ids = pick(ids)
+        if do_point_pruning:
+            mk, nk = max(k0), max(k1)
+            cut = lambda t, k: pick(t)[:, :k].contiguous()
+            d0, cs0, ind0 = cut(g0[0], mk), (cut(g0[1], mk), cut(g0[2], mk)), cut(g0[3], mk)
+            d1, cs1, ind1 = cut(g1[0], nk), (cut(g1[1], nk), cut(g1[2], nk)), cut(g1[3], nk)
+            pr0, pr1, l0, l1, l0h, l1h = pick(pr0), pick(pr1), pick(l0n), pick(l1n), k0, k1
+        else:
+            d0, d1, l0, l1 = pick(d0).contiguous(), pick(d1).contiguous(), pick(l0), pick(l1)
             cs0, cs1 = (pick(cs0[0]), pick(cs0[1])), (pick(cs1[0]), pick(cs1[1]))
             l0h, l1h = [l0h[j] for j in R], [l1h[j] for j in R]
-        if do_point_pruning:
-            k0 = [counts[j][0] for j in R]
-            k1 = [counts[j][2] for j in R]
-            if min(k0) == 0 or min(k1) == 0:
-                raise RuntimeError("every keypoint of one image was pruned (the reference's max() would raise too)")
-            dropped = any(a < b for a, b in zip(k0, l0h)) or any(a < b for a, b in zip(k1, l1h))
-            # order-preserving compaction of every pair + prune[ind] += 1 on the kept points (lightglue.py:536-547)
-            g0 = C.prune_gather(d0, cs0[0], cs0[1], ind0, keep0, cnt0, pr0, zero=True)
-            g1 = C.prune_gather(d1, cs1[0], cs1[1], ind1, keep1, cnt1, pr1, zero=True)
-            if dropped or E:
-                mk, nk = max(k0), max(k1)
-                cut = lambda t, k: t[:, :k].contiguous()
-                d0, cs0, ind0 = cut(g0[0], mk), (cut(g0[1], mk), cut(g0[2], mk)), cut(g0[3], mk)
-                d1, cs1, ind1 = cut(g1[0], nk), (cut(g1[1], nk), cut(g1[2], nk)), cut(g1[3], nk)
-                l0h, l1h = k0, k1
-                l0 = torch.tensor(k0, device=dev, dtype=torch.int32)
-                l1 = torch.tensor(k1, device=dev, dtype=torch.int32)
-                eng = model._engine(len(R), mk, nk, dev)
-                eng.load_rows(d0, d1, cs0, cs1)
-        elif E:
-            eng = model._engine(len(R), d0.shape[1], d1.shape[1], dev)
-            eng.load_rows(d0.contiguous(), d1.contiguous(), cs0, cs1)
+        eng = model._engine(len(R), d0.shape[1], d1.shape[1], dev)
+        eng.load_rows(d0, d1, cs0, cs1)
 
     pred = {
         "matches0": out_m0[:, :m].contiguous(), "matches1": out_m1[:, :n].contiguous(),

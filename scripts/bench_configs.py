@@ -68,6 +68,20 @@ def config4(B=8, NPAD=4096, steps=5):
                       "matches_per_pair_mean": float((pred["matches0"] >= 0).sum(1).float().mean())}))
 
 
+def fp32_path(N=2048, steps=3):
+    conf = {"filter_threshold": 0.1, "b200": {"precision": "fp32"}}
+    sd = W.make_state_dict(conf, seed=0)
+    model = M.LightGlue(conf)
+    model.load_state_dict(sd)
+    model = model.cuda()
+    out = {"config": "fp32 path (b200.precision=fp32), %d kpts" % N}
+    for B in (1, 4):
+        ms, _ = timed(model, cuda(W.make_inputs(B, N, N, seed=1, correlated=0.7)), steps, warmup=1)
+        out["pairs_per_s_B%d" % B] = B / ms * 1e3
+    print(json.dumps(out))
+
+
 if __name__ == "__main__":
     config3()
     config4()
+    fp32_path()

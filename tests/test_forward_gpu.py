@@ -133,6 +133,19 @@ def test_forward_2048_vs_oracle():
     assert err < BF16_TOL and agree > 0.97
 
 
+def test_forward_fp32_path_2048_vs_oracle():
+    """fp32 path at the BASELINE keypoint count (one pair of 2048 x 2048): 1e-4 on log_assignment."""
+    conf = {"filter_threshold": 0.1}
+    sd = W.make_state_dict(conf, seed=0)
+    data = W.make_inputs(1, 2048, 2048, seed=1, correlated=0.7)
+    ref = O.forward(sd, conf, data)
+    pred = _model({**conf, "b200": {"precision": "fp32"}}, sd)(_cuda(data))
+    err = (pred["log_assignment"].cpu() - ref["log_assignment"]).abs().max().item()
+    agree = (pred["matches0"].cpu() == ref["matches0"]).float().mean().item()
+    print(f"fp32 2048: max|dlog_assignment|={err:.3e} match agreement {agree:.4f}")
+    assert err < FP32_TOL and agree > 0.999
+
+
 def test_registry_alias_and_errors():
     import importlib
 
