@@ -49,6 +49,9 @@ SIGNATURES = {
     "lg_assign_tiles_ws_bytes": (_c.c_size_t, [_I, _I, _I]),
     "lg_assign_tiles": (_I, [_P, _P, _I, _I, _P, _P, _P, _P, _F, _P, _P, _P, _I, _I, _I, _P]),
     "lg_logit_rows": (_I, [_P, _P, _P, _P, _L, _P]),
+    "lg_nn_assign": (_I, [_P, _P, _P, _P, _P, _P, _P, _I, _I, _I, _P]),
+    "lg_nn_ws_bytes": (_c.c_size_t, [_I, _I, _I]),
+    "lg_nn_match": (_I, [_P, _P, _P, _F, _F, _I, _P, _P, _P, _P, _P, _I, _I, _I, _P]),
     "lg_gemm_f32": (_I, [_P, _P, _P, _P, _P, _I, _I, _I, _L, _L, _L, _L, _I, _F, _I, _I, _P, _P, _P, _P]),
     "lg_softmax_rows_f32": (_I, [_P, _P, _P, _I, _I, _I, _I, _L, _P]),
     "lg_rotary_rows_f32": (_I, [_P, _P, _P, _L, _L, _I, _I, _I, _P]),
@@ -482,3 +485,35 @@ def ln_gelu_rows_f32(x, gamma, beta, eps):
     _check(lib().lg_ln_gelu_rows_f32(_ptr(_f32c(x, "x")), _ptr(_f32c(gamma, "gamma")), _ptr(_f32c(beta, "beta")),
                                      float(eps), x.numel() // width, width, _stream()), "lg_ln_gelu_rows_f32")
     _count(1)
+
+
+# ----------------------------------------------------------------------------- nearest-neighbour matcher (lg_nn.cu)
+def nn_assign(d0, d1, m_len=None, n_len=None):
+    """d0 (B,M,256), d1 (B,N,256) -> similarity (B,M,N), log_assignment (B,M+1,N+1) (zero dustbins)."""
+    B, M, D = d0.shape
+    N = d1.shape[1]
+    assert D == 256 and d1.shape[2] == 256, "the similarity kernel is built for 256-d descriptors"
+    alloc = torch.zeros if m_len is not None or n_len is not None else torch.empty
+    sim = alloc(B, M, N, device=d0.device, dtype=torch.float32)
+    scores = torch.empty(B, M + 1, N + 1, device=d0.device, dtype=torch.float32)
+    ws = torch.empty(lib().lg_assign_ws_bytes(B, M, N), device=d0.device, dtype=torch.uint8)
+    _check(lib().lg_nn_assign(_ptr(_f32c(d0, "d0")), _ptr(_f32c(d1, "d1")), _ptr(_i32(m_len)), _ptr(_i32(n_len)),
+                              _ptr(sim), _ptr(scores), _ptr(ws), B, M, N, _stream()), "lg_nn_assign")
+    _count(5)
+    return sim, scores
+
+
+def nn_match(sim, ratio_thresh=None, distance_thresh=None, mutual=True, m_len=None, n_len=None):
+    """find_nn both ways + mutual_check on sim (B,M,N) -> m0 (B,M) i64, m1 (B,N) i64, ms0, ms1 f32."""
+    B, M, N = sim.shape
+    dev = sim.device
+    m0 = torch.empty(B, M, device=dev, dtype=torch.int64)
+    m1 = torch.empty(B, N, device=dev, dtype=torch.int64)
+    ms0 = torch.empty(B, M, device=dev, dtype=torch.float32)
+    ms1 = torch.empty(B, N, device=dev, dtype=torch.float32)
+    ws = torch.empty(lib().lg_nn_ws_bytes(B, M, N), device=dev, dtype=torch.uint8)
+    _check(lib().lg_nn_match(_ptr(_f32c(sim, "sim")), _ptr(_i32(m_len)), _ptr(_i32(n_len)), float(ratio_thresh or 0.0),
+                             float(distance_thresh or 0.0), int(bool(mutual)), _ptr(m0), _ptr(m1), _ptr(ms0), _ptr(ms1),
+                             _ptr(ws), B, M, N, _stream()), "lg_nn_match")
+    _count(3)
+    return m0, m1, ms0, ms1

@@ -74,6 +74,7 @@ struct AssignParams {
   unsigned long long* rowkey;  // pass 2, optional: [B][M] best (score, column) key of every row (lg_keys.cuh)
   unsigned long long* colkey;  // pass 2, optional: [B][N] best (score, row) key of every column
   int B, M, N, rt, ct;      // sizes, tile counts
+  float* sim_out;           // pass 2, optional: raw similarity (B, M, N) (NearestNeighborMatcher's "similarity")
 };
 
 struct __align__(8) AssignBarriers {
@@ -318,6 +319,7 @@ __global__ void __launch_bounds__(kAssignThreads, 1) assign_tile_kernel(const As
               const bool in = i < vrows && c < vcols;
               const float val = in ? ((s - rli) + (s - lc[q])) + (rai + lb[q]) : -INFINITY;
               out[static_cast<int64_t>(row0 + i) * pitch + col0 + c] = val;
+              if (p.sim_out) p.sim_out[(static_cast<int64_t>(b) * p.M + row0 + i) * p.N + col0 + c] = s;
               if (keys && in) {  // strict > keeps the lowest index on ties: columns ascend with q, rows with i
                 if (val > rv || rc == 0xFFFFFFFFu) { rv = val; rc = col0 + c; }
                 if (val > cbv[q] || cbi[q] == 0xFFFFFFFFu) { cbv[q] = val; cbi[q] = row0 + i; }
@@ -364,7 +366,7 @@ __global__ void assign_reduce_kernel(const float2* __restrict__ row_part, const 
                                      const int* __restrict__ m_len, const int* __restrict__ n_len,
                                      float* __restrict__ row_lse, float* __restrict__ col_lse,
                                      float* __restrict__ row_ls, float* __restrict__ col_ls,
-                                     float* __restrict__ scores, int M, int N, int rt, int ct) {
+                                     float* __restrict__ scores, int M, int N, int rt, int ct, int plain) {
   const int b = blockIdx.y, i = blockIdx.x * blockDim.x + threadIdx.x;
   const int m = m_len ? min(m_len[b], M) : M, n = n_len ? min(n_len[b], N) : N;
   const int64_t pitch = N + 1;
@@ -376,10 +378,11 @@ __global__ void assign_reduce_kernel(const float2* __restrict__ row_part, const 
       const float2 pr = row_part[(static_cast<size_t>(b) * ct + t) * M + i];
       if (pr.y > 0.f) sum += pr.y * expf(pr.x - mx);
     }
-    const float z = z0[static_cast<size_t>(b) * M + i];
+    // plain: no matchability terms, zero dustbins (NearestNeighborMatcher's log_assignment)
+    const float z = plain ? 0.f : z0[static_cast<size_t>(b) * M + i];
     row_lse[static_cast<size_t>(b) * M + i] = mx + logf(sum);
-    row_ls[static_cast<size_t>(b) * M + i] = log_sigmoid(z);
-    out[i * pitch + N] = i < m ? log_sigmoid(-z) : -INFINITY;
+    row_ls[static_cast<size_t>(b) * M + i] = plain ? 0.f : log_sigmoid(z);
+    out[i * pitch + N] = i < m ? (plain ? 0.f : log_sigmoid(-z)) : -INFINITY;
   }
   if (i < N) {
     float mx = -INFINITY, sum = 0.f;
@@ -388,10 +391,10 @@ __global__ void assign_reduce_kernel(const float2* __restrict__ row_part, const 
       const float2 pr = col_part[(static_cast<size_t>(b) * rt + t) * N + i];
       if (pr.y > 0.f) sum += pr.y * expf(pr.x - mx);
     }
-    const float z = z1[static_cast<size_t>(b) * N + i];
+    const float z = plain ? 0.f : z1[static_cast<size_t>(b) * N + i];
     col_lse[static_cast<size_t>(b) * N + i] = mx + logf(sum);
-    col_ls[static_cast<size_t>(b) * N + i] = log_sigmoid(z);
-    out[static_cast<int64_t>(M) * pitch + i] = i < n ? log_sigmoid(-z) : -INFINITY;
+    col_ls[static_cast<size_t>(b) * N + i] = plain ? 0.f : log_sigmoid(z);
+    out[static_cast<int64_t>(M) * pitch + i] = i < n ? (plain ? 0.f : log_sigmoid(-z)) : -INFINITY;
   }
   if (i == 0) out[static_cast<int64_t>(M) * pitch + N] = 0.f;
 }
@@ -404,11 +407,12 @@ namespace lg {
 // host launcher shared with lg_assign_strip.cu (declared in lg_assign.cuh)
 void launch_assign_reduce(const float2* row_part, const float2* col_part, const float* z0, const float* z1,
                           const int* m_len, const int* n_len, float* row_lse, float* col_lse, float* row_ls,
-                          float* col_ls, float* scores, int B, int M, int N, int rt, int ct, cudaStream_t stream) {
+                          float* col_ls, float* scores, int B, int M, int N, int rt, int ct, cudaStream_t stream,
+                          int plain) {
   const int pts = (M > N ? M : N);
   assign_reduce_kernel<<<dim3((pts + 255) / 256, B), 256, 0, stream>>>(row_part, col_part, z0, z1, m_len, n_len,
                                                                       row_lse, col_lse, row_ls, col_ls, scores, M, N,
-                                                                      rt, ct);
+                                                                      rt, ct, plain);
 }
 }  // namespace lg
 
@@ -426,8 +430,10 @@ extern "C" size_t lg_assign_ws_bytes(int B, int M, int N) {
 
 static int assign_impl(const float* md0, const float* md1, const float* z0, const float* z1, const int* m_len,
                        const int* n_len, float prescale, float* scores, void* ws, unsigned long long* rowkey,
-                       unsigned long long* colkey, int B, int M, int N, cudaStream_t stream) {
-  if (!md0 || !md1 || !z0 || !z1 || !scores || !ws) return LG_ERR_NULL;
+                       unsigned long long* colkey, int B, int M, int N, cudaStream_t stream, float* sim_out = nullptr,
+                       int plain = 0) {
+  if (!md0 || !md1 || !scores || !ws) return LG_ERR_NULL;
+  if (!plain && (!z0 || !z1)) return LG_ERR_NULL;
   if (B <= 0 || M <= 0 || N <= 0) return LG_ERR_SHAPE;
   const int rt = (M + 127) / 128, ct = (N + 127) / 128;
   uint8_t* w = static_cast<uint8_t*>(ws);
@@ -452,7 +458,7 @@ static int assign_impl(const float* md0, const float* md1, const float* z0, cons
   lg::assign_pack_kernel<<<dim3(rt, B), 1024, 0, stream>>>(md0, m_len, a_tiles, M, rt, prescale);
   lg::assign_pack_kernel<<<dim3(ct, B), 1024, 0, stream>>>(md1, n_len, b_tiles, N, ct, prescale);
   lg::AssignParams p{a_tiles, b_tiles, m_len, n_len, row_part, col_part, row_lse, col_lse, row_ls, col_ls, scores,
-                     rowkey, colkey, B, M, N, rt, ct};
+                     rowkey, colkey, B, M, N, rt, ct, sim_out};
   int sms = 0, dev = 0;
   cudaGetDevice(&dev);
   cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
@@ -464,7 +470,7 @@ static int assign_impl(const float* md0, const float* md1, const float* z0, cons
   const int pts = (M > N ? M : N);
   lg::assign_reduce_kernel<<<dim3((pts + 255) / 256, B), 256, 0, stream>>>(row_part, col_part, z0, z1, m_len, n_len,
                                                                           row_lse, col_lse, row_ls, col_ls, scores, M,
-                                                                          N, rt, ct);
+                                                                          N, rt, ct, plain);
   lg::assign_tile_kernel<2><<<grid, lg::kAssignThreads, lg::kAssignSmem, stream>>>(p);
   return static_cast<int>(cudaGetLastError());
 }
@@ -485,4 +491,13 @@ extern "C" int lg_assign_keys(const float* md0, const float* md1, const float* z
   auto* rowkey = static_cast<unsigned long long*>(keys_ws);
   return assign_impl(md0, md1, z0, z1, m_len, n_len, prescale, scores, ws, rowkey, rowkey + static_cast<size_t>(B) * M,
                      B, M, N, stream);
+}
+
+// NearestNeighborMatcher._forward (reference gluefactory/models/matchers/nearest_neighbor_matcher.py:52-72): similarity
+// = d0 . d1^T (TF32x3) written out, log_assignment = log_softmax(sim, -1) + log_softmax(sim, -2) with zero dustbins.
+extern "C" int lg_nn_assign(const float* d0, const float* d1, const int* m_len, const int* n_len, float* sim_out,
+                            float* scores, void* ws, int B, int M, int N, cudaStream_t stream) {
+  if (!sim_out) return LG_ERR_NULL;
+  return assign_impl(d0, d1, nullptr, nullptr, m_len, n_len, 1.0f, scores, ws, nullptr, nullptr, B, M, N, stream,
+                     sim_out, 1);
 }

@@ -166,6 +166,20 @@ int lg_assign_tiles(const void* a_tiles, const void* b_tiles, int tpa, int tpb, 
  * lightglue.py:304,313-314, before the log-sigmoid).  x (rows, 256) f32 contiguous. */
 int lg_logit_rows(const float* x, const float* w, const float* bias, float* out, int64_t rows, cudaStream_t stream);
 
+/* NearestNeighborMatcher (reference gluefactory/models/matchers/nearest_neighbor_matcher.py:52-72).
+ * lg_nn_assign: similarity = d0 . d1^T (TF32x3 on tcgen05, the lg_assign tile kernels) written to sim_out (B,M,N)
+ *   and log_assignment (B,M+1,N+1) = log_softmax(sim,-1) + log_softmax(sim,-2) with zero dustbin row / column (:63-64).
+ *   d0 (B,M,256), d1 (B,N,256) f32; ws: lg_assign_ws_bytes(B,M,N).
+ * lg_nn_match: find_nn (:16-27) along rows and columns of sim (top-2, dist = 2(1-sim), ratio / distance tests; a
+ *   threshold <= 0 disables its test like the reference's None) and mutual_check (:30-39) when `mutual`;
+ *   m0 (B,M) / m1 (B,N) i64 (-1 = unmatched), ms0 / ms1 = (m > -1) as f32 (:65-66).  ws: lg_nn_ws_bytes(B,M,N). */
+int lg_nn_assign(const float* d0, const float* d1, const int* m_len, const int* n_len, float* sim_out, float* scores,
+                 void* ws, int B, int M, int N, cudaStream_t stream);
+size_t lg_nn_ws_bytes(int B, int M, int N);
+int lg_nn_match(const float* sim, const int* m_len, const int* n_len, float ratio_thresh, float distance_thresh,
+                int mutual, int64_t* m0, int64_t* m1, float* ms0, float* ms1, void* ws, int B, int M, int N,
+                cudaStream_t stream);
+
 /* fp32 path (b200.precision = "fp32"): IEEE fp32 FMA arithmetic on the CUDA cores for the 1e-4 bound on
  * log_assignment (the tensor-core path is bounded by 2e-2).
  * lg_gemm_f32: C = alpha * A . op(B) + bias + resid, strided-batched.  A (M,K) lda; B (N,K) ldb if b_kn == 0

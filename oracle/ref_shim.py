@@ -69,9 +69,14 @@ def _install_omegaconf_stub():
         pass
     m = types.ModuleType("omegaconf")
 
+    import contextlib
+
     class OmegaConf:
         merge = staticmethod(_merge)
-        create = staticmethod(_wrap)
+        create = staticmethod(lambda d=None: _wrap({} if d is None else d))
+        # base_model.py:72,83-84 (used by the reference's NearestNeighborMatcher, a BaseModel): no-ops here
+        set_struct = staticmethod(lambda conf, flag: None)
+        set_readonly = staticmethod(lambda conf, flag: None)
 
         @staticmethod
         def to_container(c, resolve=False):
@@ -79,6 +84,8 @@ def _install_omegaconf_stub():
 
     m.OmegaConf = OmegaConf
     m.DictConfig = _Cfg
+    m.read_write = lambda conf: contextlib.nullcontext()
+    m.open_dict = lambda conf: contextlib.nullcontext()
     sys.modules["omegaconf"] = m
 
 
@@ -155,3 +162,12 @@ def run_reference(model, data: dict):
     d.setdefault("view0", {})
     d.setdefault("view1", {})
     return model(d)
+
+
+def load_reference_nn_module():
+    """The reference module `gluefactory.models.matchers.nearest_neighbor_matcher` (find_nn, mutual_check,
+    NearestNeighborMatcher), imported from the read-only tree like the LightGlue module."""
+    load_reference_module()
+    with warnings.catch_warnings():
+        warnings.simplefilter("ignore")
+        return importlib.import_module("gluefactory.models.matchers.nearest_neighbor_matcher")

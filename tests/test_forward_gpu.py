@@ -146,6 +146,40 @@ def test_forward_fp32_path_2048_vs_oracle():
     assert err < FP32_TOL and agree > 0.999
 
 
+def test_forward_edge_shapes_vs_oracle():
+    """SURVEY 8(c) edge fixtures: a single keypoint in one image, keypoint counts that are not multiples of the tile."""
+    conf = {"filter_threshold": 0.0}
+    sd = W.make_state_dict(conf, seed=0)
+    model = _model(conf, sd)
+    for (m, n) in ((129, 1), (1, 1), (257, 383)):
+        data = W.make_inputs(1, m, n, seed=5, image_size=(640, 480), correlated=0.5)
+        ref = O.forward(sd, conf, data)
+        pred = model(_cuda(data))
+        assert pred["log_assignment"].shape == ref["log_assignment"].shape == (1, m + 1, n + 1)
+        assert (pred["log_assignment"].cpu() - ref["log_assignment"]).abs().max() < BF16_TOL
+        assert (pred["matches0"].cpu() == ref["matches0"]).float().mean() > 0.97
+        assert (pred["matching_scores1"].cpu() - ref["matching_scores1"]).abs().max() < BF16_TOL
+
+
+def test_forward_fully_padded_image_in_batch():
+    """A pair whose image has NO valid keypoints inside a variable-length batch: no matches for it, the other pairs
+    are what they are without it (the reference cannot run this case: max() over an empty dimension raises)."""
+    conf = {"filter_threshold": 0.1}
+    sd = W.make_state_dict(conf, seed=0)
+    model = _model(conf, sd)
+    data = _cuda(W.make_inputs(3, 200, 160, seed=9, image_size=(640, 480), correlated=0.7))
+    data["num_keypoints0"] = torch.tensor([200, 0, 150]).cuda()
+    data["num_keypoints1"] = torch.tensor([160, 160, 0]).cuda()
+    pred = model(data)
+    torch.cuda.synchronize()
+    assert (pred["matches0"][1] == -1).all() and (pred["matches1"][1] == -1).all()
+    assert (pred["matches0"][2] == -1).all() and (pred["matches1"][2] == -1).all()
+    assert (pred["matching_scores0"][1:] == 0).all()
+    one = model(_slice_pair(data, 0))
+    assert (one["matches0"] == pred["matches0"][0:1]).float().mean() > 0.995
+    assert torch.isfinite(pred["log_assignment"][0, :200, :160]).all()
+
+
 def test_registry_alias_and_errors():
     import importlib
 
