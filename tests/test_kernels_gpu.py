@@ -379,3 +379,68 @@ def test_assign_keys_equals_assign_plus_filter(B, M, N, varlen):
     for a, b in zip(f_ref, f_new):
         assert torch.equal(a, b)
     assert (f_new[0] >= 0).sum() > 0
+
+
+# ----------------------------------------------------------------------------- out-of-bounds canaries
+def _guarded(nbytes, dtype=torch.uint8, fill=0x5A):
+    """buffer of nbytes with 64 KB guard zones on both sides (compute-sanitizer is not available on the pool)."""
+    g = 65536
+    raw = torch.full((nbytes + 2 * g,), fill, dtype=torch.uint8, device="cuda")
+    return raw, raw[g:g + nbytes], g
+
+
+def _guards_intact(raw, g, fill=0x5A):
+    return bool((raw[:g] == fill).all()) and bool((raw[-g:] == fill).all())
+
+
+@pytest.mark.parametrize("B,M,N,varlen", [(2, 200, 333, False), (3, 129, 257, True), (1, 1, 700, False), (2, 1024, 640, True)])
+def test_assign_tiles_writes_stay_in_bounds(C, B, M, N, varlen):
+    """lg_assign_tiles through the raw C ABI with guard zones around the scores, the workspace and the key buffer."""
+    lib = C.lib()
+    g = _gen(B + M + N)
+    a, tpa = _split_tiles(C, torch.randn(B, M, 256, generator=g))
+    b, tpb = _split_tiles(C, torch.randn(B, N, 256, generator=g))
+    z0, z1 = torch.randn(B, M, generator=g).cuda(), torch.randn(B, N, generator=g).cuda()
+    ml = torch.tensor([M, max(1, M // 2), 1][:B], dtype=torch.int32).cuda() if varlen else None
+    nl = torch.tensor([max(1, N - 130), N, 5][:B], dtype=torch.int32).cuda() if varlen else None
+    raw_s, s, gs = _guarded(B * (M + 1) * (N + 1) * 4)
+    raw_w, w, gw = _guarded(lib.lg_assign_tiles_ws_bytes(B, M, N))
+    raw_k, k, gk = _guarded(lib.lg_filter_ws_bytes(B, M, N))
+    rc = lib.lg_assign_tiles(a.data_ptr(), b.data_ptr(), tpa, tpb, z0.data_ptr(), z1.data_ptr(),
+                             None if ml is None else ml.data_ptr(), None if nl is None else nl.data_ptr(), 1.0 / 16,
+                             s.data_ptr(), w.data_ptr(), k.data_ptr(), B, M, N, torch.cuda.current_stream().cuda_stream)
+    torch.cuda.synchronize()
+    assert rc == 0
+    assert _guards_intact(raw_s, gs) and _guards_intact(raw_w, gw) and _guards_intact(raw_k, gk)
+    got = s.view(torch.float32).view(B, M + 1, N + 1)
+    want = C.assign_tiles(a, b, tpa, tpb, z0, z1, None, ml, nl)
+    assert torch.equal(got, want)
+
+
+def test_gemm_f32_strided_batches_and_bounds(C):
+    """lg_gemm_f32 on strided views with padding columns: values against torch, padding and guard zones untouched."""
+    g = _gen(9)
+    Bt, M, N, K, ldc = 3, 70, 45, 37, 52
+    A = torch.randn(Bt, M, K, generator=g).cuda()
+    Bm = torch.randn(Bt, N, K, generator=g).cuda()
+    bias = torch.randn(N, generator=g).cuda()
+    raw, c, gz = _guarded(Bt * M * ldc * 4)
+    out = c.view(torch.float32).view(Bt, M, ldc)
+    out.fill_(7.0)
+    C.gemm_f32(A, Bm, out, M, N, K, K, K, ldc, bias=bias, alpha=0.5, batch=Bt, inner=1,
+               strides=(M * K, 0, N * K, 0, M * ldc, 0, 0, 0))
+    torch.cuda.synchronize()
+    want = 0.5 * torch.einsum("bmk,bnk->bmn", A.double(), Bm.double()) + bias.double()
+    assert (out[:, :, :N].double() - want).abs().max() < 1e-4
+    assert (out[:, :, N:] == 7.0).all() and _guards_intact(raw, gz)
+    # (K, N) form of B with a valid-K count per batch
+    Bk = torch.randn(Bt, K, N, generator=g).cuda()
+    klen = torch.tensor([K, 5, 20], dtype=torch.int32).cuda()
+    out.fill_(7.0)
+    C.gemm_f32(A, Bk, out, M, N, K, K, N, ldc, b_kn=True, batch=Bt, inner=1,
+               strides=(M * K, 0, K * N, 0, M * ldc, 0, 0, 0), k_len=klen)
+    for b in range(Bt):
+        kk = int(klen[b])
+        want = A[b, :, :kk].double() @ Bk[b, :kk].double()
+        assert (out[b, :, :N].double() - want).abs().max() < 1e-4
+    assert _guards_intact(raw, gz)
