@@ -22,6 +22,7 @@ _P, _I, _F, _L = _c.c_void_p, _c.c_int, _c.c_float, _c.c_int64
 SIGNATURES = {
     "lg_version": (_I, []),
     "lg_posenc": (_I, [_P, _P, _P, _P, _P, _F, _P, _P, _I, _I, _P]),
+    "lg_posenc_scale_ori": (_I, [_P, _P, _P, _P, _P, _P, _P, _F, _P, _P, _I, _I, _P]),
     "lg_keypoint_extent": (_I, [_P, _P, _I, _I, _P]),
     "lg_pack_self_qkv": (_I, [_P, _P, _P, _P, _P, _P, _P, _I, _I, _I, _I, _P]),
     "lg_pack_cross_qkv": (_I, [_P, _P, _P, _P, _P, _I, _I, _I, _I, _P]),
@@ -132,8 +133,9 @@ def version() -> int:
     return lib().lg_version()
 
 
-def posenc(kpts, size, wr, wc, bc, cond: float):
-    """-> (cos, sin) compact tables (B,N,32). size (B,2) f32 or None (extent of the points)."""
+def posenc(kpts, size, wr, wc, bc, cond: float, scales=None, oris=None):
+    """-> (cos, sin) compact tables (B,N,32). size (B,2) f32 or None (extent of the points); scales / oris (B,N):
+    the 4-d positional input of add_scale_ori (wr is then (32,4))."""
     B, N, _ = kpts.shape
     _f32c(kpts, "kpts")
     if size is None:
@@ -141,6 +143,15 @@ def posenc(kpts, size, wr, wc, bc, cond: float):
         _check(lib().lg_keypoint_extent(_ptr(kpts), _ptr(size), B, N, _stream()), "lg_keypoint_extent")
     cos = torch.empty(B, N, 32, device=kpts.device, dtype=torch.float32)
     sin = torch.empty_like(cos)
+    if scales is not None:
+        assert wr.shape == (32, 4) and scales.shape == (B, N) and oris.shape == (B, N)
+        _check(lib().lg_posenc_scale_ori(_ptr(kpts), _ptr(_f32c(scales, "scales")), _ptr(_f32c(oris, "oris")),
+                                         _ptr(_f32c(size, "size")), _ptr(_f32c(wr, "wr")), _ptr(_f32c(wc, "wc")),
+                                         _ptr(_f32c(bc, "bc")), float(cond), _ptr(cos), _ptr(sin), B, N, _stream()),
+               "lg_posenc_scale_ori")
+        _count(1)
+        return cos, sin
+    assert wr.shape == (32, 2)
     _check(lib().lg_posenc(_ptr(kpts), _ptr(_f32c(size, "size")), _ptr(_f32c(wr, "wr")), _ptr(_f32c(wc, "wc")),
                            _ptr(_f32c(bc, "bc")), float(cond), _ptr(cos), _ptr(sin), B, N, _stream()), "lg_posenc")
     _count(1)

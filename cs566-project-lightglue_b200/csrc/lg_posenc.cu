@@ -38,7 +38,9 @@ __global__ void posenc_extent_kernel(const float* __restrict__ kpts, float* __re
 }
 
 // one thread per (b, n, j): 32 consecutive threads write one point's 32 frequencies
-__global__ void posenc_kernel(const float* __restrict__ kpts, const float* __restrict__ size,
+// scales / oris (B,N) non-null: the 4-d positional input of add_scale_ori (lightglue.py:458-476), wr is (32,4)
+__global__ void posenc_kernel(const float* __restrict__ kpts, const float* __restrict__ scales,
+                              const float* __restrict__ oris, const float* __restrict__ size,
                               const float* __restrict__ wr, const float* __restrict__ wc,
                               const float* __restrict__ bc, float cond, float* __restrict__ cos_t,
                               float* __restrict__ sin_t, int B, int N) {
@@ -54,7 +56,14 @@ __global__ void posenc_kernel(const float* __restrict__ kpts, const float* __res
   const float x = __fdiv_rn(__fsub_rn(k.x, __fmul_rn(w, 0.5f)), scale);
   const float y = __fdiv_rn(__fsub_rn(k.y, __fmul_rn(h, 0.5f)), scale);
   // Linear(2->32, no bias): x*w0 + y*w1 accumulated with fma like the CPU GEMV micro-kernel
-  const float proj = __fmaf_rn(y, wr[2 * j + 1], __fmul_rn(x, wr[2 * j]));
+  float proj;
+  if (scales == nullptr) {
+    proj = __fmaf_rn(y, wr[2 * j + 1], __fmul_rn(x, wr[2 * j]));
+  } else {  // Linear(4->32): [x, y, scale, ori] . wr[j, :]
+    proj = __fmaf_rn(y, wr[4 * j + 1], __fmul_rn(x, wr[4 * j]));
+    proj = __fmaf_rn(scales[pt], wr[4 * j + 2], proj);
+    proj = __fmaf_rn(oris[pt], wr[4 * j + 3], proj);
+  }
   // Linear(1->32)(relu(count)): count*w + b
   const float modulated = __fmaf_rn(fmaxf(cond, 0.f), wc[j], bc[j]);
   const float phase = __fadd_rn(proj, modulated);
@@ -72,8 +81,20 @@ extern "C" int lg_posenc(const float* kpts, const float* size, const float* wr, 
   if (B <= 0 || N <= 0) return LG_ERR_SHAPE;
   if (!size) return LG_ERR_NULL;  // size=None branch: call lg_keypoint_extent first
   const size_t total = static_cast<size_t>(B) * N * 32;
-  lg::posenc_kernel<<<static_cast<unsigned>((total + 255) / 256), 256, 0, stream>>>(kpts, size, wr, wc, bc, cond,
-                                                                                   cos_t, sin_t, B, N);
+  lg::posenc_kernel<<<static_cast<unsigned>((total + 255) / 256), 256, 0, stream>>>(kpts, nullptr, nullptr, size, wr, wc,
+                                                                                   bc, cond, cos_t, sin_t, B, N);
+  return static_cast<int>(cudaGetLastError());
+}
+
+// add_scale_ori = True (lightglue.py:458-476): the positional input is [x, y, scale, ori]; wr is (32, 4)
+extern "C" int lg_posenc_scale_ori(const float* kpts, const float* scales, const float* oris, const float* size,
+                                   const float* wr, const float* wc, const float* bc, float cond, float* cos_t,
+                                   float* sin_t, int B, int N, cudaStream_t stream) {
+  if (!kpts || !scales || !oris || !size || !wr || !wc || !bc || !cos_t || !sin_t) return LG_ERR_NULL;
+  if (B <= 0 || N <= 0) return LG_ERR_SHAPE;
+  const size_t total = static_cast<size_t>(B) * N * 32;
+  lg::posenc_kernel<<<static_cast<unsigned>((total + 255) / 256), 256, 0, stream>>>(kpts, scales, oris, size, wr, wc, bc,
+                                                                                   cond, cos_t, sin_t, B, N);
   return static_cast<int>(cudaGetLastError());
 }
 

@@ -138,12 +138,10 @@ class LightGlue(nn.Module):
         d, h, L = conf.descriptor_dim, conf.num_heads, conf.n_layers
         if d != 256 or h != 4:
             raise ValueError("the sm_100a kernels are built for descriptor_dim=256, num_heads=4 (no fallback)")
-        if conf.add_scale_ori:
-            raise NotImplementedError("add_scale_ori (4-d positional input) is not built; SuperPoint/DISK use 2-d")
         if conf.b200.precision not in ("bf16", "fp32"):
             raise ValueError(f"b200.precision={conf.b200.precision!r}: 'bf16' (tensor-core throughput path) or 'fp32'")
         self.input_proj = nn.Linear(conf.input_dim, d, bias=True) if conf.input_dim != d else nn.Identity()
-        self.posenc = _PosEnc(2, (d // h) // 2)
+        self.posenc = _PosEnc(2 + 2 * int(bool(conf.add_scale_ori)), (d // h) // 2)
         self.transformers = nn.ModuleList([_Layer(d) for _ in range(L)])
         self.log_assignment = nn.ModuleList([_Assignment(d) for _ in range(L)])
         self.token_confidence = nn.ModuleList([_TokenConfidence(d) for _ in range(L - 1)])
@@ -284,10 +282,15 @@ class LightGlue(nn.Module):
             len1 = torch.full((b,), n, device=dev, dtype=torch.int32) if len1 is None else len1
         pe = self.posenc
         wc = pe.condition_modulation.weight.reshape(-1)
+        so0 = so1 = (None, None)
+        if conf.add_scale_ori:  # 4-d positional input [x, y, scale, ori] (lightglue.py:458-476)
+            flat = lambda t, k: t.reshape(b, k).float().contiguous()
+            so0 = (flat(data["scales0"], m), flat(data["oris0"], m))
+            so1 = (flat(data["scales1"], n), flat(data["oris1"], n))
         cs0 = C.posenc(kpts0.float().contiguous(), self._image_size(data, "view0", kpts0), pe.Wr.weight, wc,
-                       pe.condition_modulation.bias, float(m))
+                       pe.condition_modulation.bias, float(m), *so0)
         cs1 = C.posenc(kpts1.float().contiguous(), self._image_size(data, "view1", kpts1), pe.Wr.weight, wc,
-                       pe.condition_modulation.bias, float(n))
+                       pe.condition_modulation.bias, float(n), *so1)
         do_early_stop = conf.depth_confidence > 0
         do_point_pruning = conf.width_confidence > 0
         if conf.b200.precision == "fp32":

@@ -39,6 +39,12 @@ int lg_version(void);
 int lg_posenc(const float* kpts, const float* size, const float* wr, const float* wc, const float* bc,
               float cond, float* cos_t, float* sin_t, int B, int N, cudaStream_t stream);
 
+/* The same with add_scale_ori = True (lightglue.py:458-476): positional input [x, y, scale, ori], scales / oris (B,N)
+ * f32, wr (32,4). */
+int lg_posenc_scale_ori(const float* kpts, const float* scales, const float* oris, const float* size, const float* wr,
+                        const float* wc, const float* bc, float cond, float* cos_t, float* sin_t, int B, int N,
+                        cudaStream_t stream);
+
 /* size_out (B,2) f32 = 1 + max - min over each image's keypoints (lightglue.py:25-26). */
 int lg_keypoint_extent(const float* kpts, float* size_out, int B, int N, cudaStream_t stream);
 

@@ -146,6 +146,26 @@ def test_forward_fp32_path_2048_vs_oracle():
     assert err < FP32_TOL and agree > 0.999
 
 
+@pytest.mark.parametrize("precision,tol", [("bf16", BF16_TOL), ("fp32", 1e-4)])
+def test_forward_add_scale_ori_vs_oracle(precision, tol):
+    """add_scale_ori = True (lightglue.py:458-476): 4-d positional input [x, y, scale, ori], scales given as (B,N),
+    orientations as (B,N,1) -- both layouts the reference accepts."""
+    conf = {"filter_threshold": 0.1, "add_scale_ori": True}
+    sd = W.make_state_dict(conf, seed=0)
+    assert sd["posenc.Wr.weight"].shape == (32, 4)
+    data = W.make_inputs(2, 230, 180, seed=6, image_size=(640, 480), correlated=0.7)
+    g = torch.Generator().manual_seed(7)
+    data["scales0"], data["scales1"] = torch.rand(2, 230, generator=g) * 3 + 0.5, torch.rand(2, 180, generator=g) * 3 + 0.5
+    data["oris0"] = (torch.rand(2, 230, 1, generator=g) * 2 - 1) * 3.14159
+    data["oris1"] = (torch.rand(2, 180, 1, generator=g) * 2 - 1) * 3.14159
+    ref = O.forward(sd, conf, data)
+    pred = _model({**conf, "b200": {"precision": precision}}, sd)(_cuda(data))
+    err = (pred["log_assignment"].cpu() - ref["log_assignment"]).abs().max().item()
+    print(f"add_scale_ori {precision}: max|dlog_assignment|={err:.3e}")
+    assert err < tol
+    assert (pred["matches0"].cpu() == ref["matches0"]).float().mean() > 0.97
+
+
 def test_forward_edge_shapes_vs_oracle():
     """SURVEY 8(c) edge fixtures: a single keypoint in one image, keypoint counts that are not multiples of the tile."""
     conf = {"filter_threshold": 0.0}
