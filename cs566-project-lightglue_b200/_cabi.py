@@ -44,6 +44,8 @@ SIGNATURES = {
     "lg_linear_qkv_self": (_I, [_P, _P, _P, _P, _P, _P, _P, _P, _P, _P, _I, _I, _I, _I, _P]),
     "lg_linear_qkv_cross": (_I, [_P, _P, _P, _P, _P, _P, _P, _I, _I, _I, _I, _P]),
     "lg_attention_tiles": (_I, [_P, _P, _P, _P, _I, _P, _P, _I, _I, _I, _I, _I, _I, _F, _P]),
+    "lg_attention_tiles2": (_I, [_P, _P, _P, _I, _P, _P, _I, _I, _I, _I, _P, _P, _P, _I, _P, _P, _I, _I, _I, _I, _P, _I, _I,
+                                 _F, _P]),
     "lg_filter_matches": (_I, [_P, _L, _P, _P, _F, _P, _P, _P, _P, _P, _I, _I, _I, _P]),
     "lg_assign_keys": (_I, [_P, _P, _P, _P, _P, _P, _F, _P, _P, _P, _I, _I, _I, _P]),
     "lg_filter_from_keys": (_I, [_P, _P, _P, _F, _P, _P, _P, _P, _I, _I, _I, _P]),
@@ -459,6 +461,24 @@ def attention_tiles(q_tiles, k_tiles, v_tiles, out_tiles, rt_base: int, nq, nk, 
     if ATTN_EVENTS is not None:
         e1.record()
         ATTN_EVENTS.append((e0, e1, (3.0 if cross else 4.0) * 64 * nq * nk * B * H))
+    _count(1)
+
+
+def attention_tiles2(side0, side1, out_tiles, scale=0.125, cross=False):
+    """Both attention problems of a block in one launch; side = (q_tiles, k_tiles, v_tiles, rt_base, nq, nk, q_len,
+    k_len).  cross: the two directions of a CrossBlock (algorithmic flops count the shared similarity once)."""
+    B, H = side0[0].shape[:2]
+    if ATTN_EVENTS is not None:
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+    args = []
+    for q, k, v, rt, nq, nk, ql, kl in (side0, side1):
+        args += [_ptr(q), _ptr(k), _ptr(v), int(rt), _ptr(_i32(ql)), _ptr(_i32(kl)), int(nq), int(nk), q.shape[2], k.shape[2]]
+    _check(lib().lg_attention_tiles2(*args, _ptr(out_tiles), B, H, float(scale), _stream()), "lg_attention_tiles2")
+    if ATTN_EVENTS is not None:
+        e1.record()
+        flops = sum((3.0 if cross else 4.0) * 64 * sd[4] * sd[5] * B * H for sd in (side0, side1))
+        ATTN_EVENTS.append((e0, e1, flops))
     _count(1)
 
 

@@ -105,18 +105,25 @@ __device__ __forceinline__ unsigned long long gtime() {
 #define TRACE(slot, idx) do {} while (0)
 #endif
 
-struct AttnParams {
+// One launch serves up to two "sides" (the two images of a SelfBlock, or the two directions of a CrossBlock): half the
+// launches per layer, and twice the work items per launch when the batch is small.
+struct AttnSide {
   const uint8_t* q_tiles;
   const uint8_t* k_tiles;
   const uint8_t* v_tiles;
   float* out;          // (B, nq, H*64) fp32, or null when out_tiles is set
-  uint8_t* out_tiles;  // split tiles [rt][H atoms][hi 16 KB | lo 16 KB]: context as the A operand of lg_linear
   int out_rt_base;     // row tile of (b=0, query tile 0) inside out_tiles; image b starts at + b*tq_pad
   const int* q_len;    // per-image valid query rows, or null
   const int* k_len;    // per-image valid keys, or null
-  int B, H, nq, nk, tq_pad, tk_pad;
-  float scale_log2;    // dh^-0.5 * log2(e)
+  int nq, nk, tq_pad, tk_pad;
   int items;           // B * H * tq_pad / 2
+};
+struct AttnParams {
+  AttnSide side[2];
+  uint8_t* out_tiles;  // split tiles [rt][H atoms][hi 16 KB | lo 16 KB]: context as the A operand of lg_linear
+  int B, H;
+  float scale_log2;    // dh^-0.5 * log2(e)
+  int items;           // side[0].items + side[1].items
 };
 
 struct __align__(8) AttnBarriers {
@@ -137,18 +144,21 @@ constexpr int kAttnSmem = 1024 /*align slack*/ + 2 * 2 * kTileBytes + kStages * 
 
 // One work item, decoded identically by every role.
 struct AttnItem {
-  int b, h, qt0, q_len, k_len, nkt;
+  int s, b, h, qt0, q_len, k_len, nkt;  // s: side
   bool skip;  // no valid query row in the block, or no key: rows are written as zeros, no MMA work
 };
 __device__ __forceinline__ AttnItem attn_item(const AttnParams& p, int w) {
   AttnItem it;
-  const int nqb = p.tq_pad >> 1;
+  it.s = w >= p.side[0].items;
+  const AttnSide& sd = p.side[it.s];
+  w -= it.s ? p.side[0].items : 0;
+  const int nqb = sd.tq_pad >> 1;
   const int bh = w / nqb;
   it.qt0 = (w - bh * nqb) * 2;
   it.b = bh / p.H;
   it.h = bh - it.b * p.H;
-  it.q_len = p.q_len ? min(p.q_len[it.b], p.nq) : p.nq;
-  it.k_len = p.k_len ? min(p.k_len[it.b], p.nk) : p.nk;
+  it.q_len = sd.q_len ? min(sd.q_len[it.b], sd.nq) : sd.nq;
+  it.k_len = sd.k_len ? min(sd.k_len[it.b], sd.nk) : sd.nk;
   it.nkt = (it.k_len + kTile - 1) / kTile;
   it.skip = it.qt0 * kTile >= it.q_len || it.nkt == 0;
   return it;
@@ -190,10 +200,11 @@ __global__ void __launch_bounds__(kAttnThreads, 1) attention_kernel(const AttnPa
         for (int w = blockIdx.x; w < p.items; w += gridDim.x) {
           const AttnItem it = attn_item(p, w);
           if (it.skip) continue;
+          const AttnSide& sd = p.side[it.s];
           const size_t bh = static_cast<size_t>(it.b) * p.H + it.h;
-          const uint8_t* gq = p.q_tiles + (bh * p.tq_pad + it.qt0) * kTileBytes;
-          const uint8_t* gk = p.k_tiles + bh * p.tk_pad * kTileBytes;
-          const uint8_t* gv = p.v_tiles + bh * p.tk_pad * kTileBytes;
+          const uint8_t* gq = sd.q_tiles + (bh * sd.tq_pad + it.qt0) * kTileBytes;
+          const uint8_t* gk = sd.k_tiles + bh * sd.tk_pad * kTileBytes;
+          const uint8_t* gv = sd.v_tiles + bh * sd.tk_pad * kTileBytes;
           const int qs = cnt & 1;
           if (cnt >= 2) mbar_wait(&bar->q_empty[qs], ((cnt >> 1) - 1) & 1);
           mbar_arrive_expect_tx(&bar->q_full[qs], 2 * kTileBytes);
@@ -325,12 +336,14 @@ __global__ void __launch_bounds__(kAttnThreads, 1) attention_kernel(const AttnPa
     for (int w = blockIdx.x; w < p.items; w += gridDim.x) {
       const AttnItem it = attn_item(p, w);
       const int row = (it.qt0 + t) * kTile + r;
+      const AttnSide& sd = p.side[it.s];
+      const int side_nq = sd.nq;
       uint8_t* dt = p.out_tiles
-                        ? p.out_tiles + ((static_cast<size_t>(p.out_rt_base + it.b * p.tq_pad + it.qt0 + t) * p.H + it.h) * 32768)
+                        ? p.out_tiles + ((static_cast<size_t>(sd.out_rt_base + it.b * sd.tq_pad + it.qt0 + t) * p.H + it.h) * 32768)
                         : nullptr;
-      float4* drow = p.out ? reinterpret_cast<float4*>(p.out + (static_cast<size_t>(it.b) * p.nq + row) * row_stride +
-                                                       it.h * kHeadDim)
-                           : nullptr;
+      float4* drow = sd.out ? reinterpret_cast<float4*>(sd.out + (static_cast<size_t>(it.b) * sd.nq + row) * row_stride +
+                                                        it.h * kHeadDim)
+                            : nullptr;
       if (it.skip) {
         // nothing to attend from / to: rows are zero (reference: nan_to_num of an all-masked softmax)
         if (dt) {
@@ -339,7 +352,7 @@ __global__ void __launch_bounds__(kAttnThreads, 1) attention_kernel(const AttnPa
             *reinterpret_cast<uint4*>(dt + sw128_offset(r, ch)) = make_uint4(0u, 0u, 0u, 0u);
             *reinterpret_cast<uint4*>(dt + 16384 + sw128_offset(r, ch)) = make_uint4(0u, 0u, 0u, 0u);
           }
-        } else if (row < p.nq) {
+        } else if (row < side_nq) {
 #pragma unroll
           for (int i = 0; i < 16; ++i) drow[i] = make_float4(0.f, 0.f, 0.f, 0.f);
         }
@@ -679,7 +692,7 @@ __global__ void __launch_bounds__(kAttnThreads, 1) attention_kernel(const AttnPa
         __syncwarp();
         if (lane == 0) { bulk_s2g(gdst + 16384, stg, 4096); bulk_commit(); }
         if ((threadIdx.x & 127) == 0) TRACE(11 + t * 4, kv_base - it.nkt);
-      } else if (row < p.nq) {
+      } else if (row < side_nq) {
 #pragma unroll
         for (int i = 0; i < 8; ++i) {
           drow[i] = make_float4(__uint_as_float(va[4 * i]) * inv, __uint_as_float(va[4 * i + 1]) * inv,
@@ -698,12 +711,24 @@ __global__ void __launch_bounds__(kAttnThreads, 1) attention_kernel(const AttnPa
 
 }  // namespace lg
 
-static int launch_attention(const void* q_tiles, const void* k_tiles, const void* v_tiles, float* out, void* out_tiles,
-                            int out_rt_base, const int* q_len, const int* k_len, int B, int H, int nq, int nk,
-                            int tq_pad, int tk_pad, float softmax_scale, cudaStream_t stream) {
-  if (!q_tiles || !k_tiles || !v_tiles || (!out && !out_tiles)) return LG_ERR_NULL;
-  if (B <= 0 || H <= 0 || nq <= 0 || nk <= 0 || out_rt_base < 0) return LG_ERR_SHAPE;
-  if (tq_pad * lg::kTile < nq || tk_pad * lg::kTile < nk || (tq_pad & 1) || (tk_pad & 1)) return LG_ERR_SHAPE;
+struct AttnSideArgs {
+  const void *q_tiles, *k_tiles, *v_tiles;
+  float* out;
+  int out_rt_base;
+  const int *q_len, *k_len;
+  int nq, nk, tq_pad, tk_pad;
+};
+
+static int check_side(const AttnSideArgs& a, bool tiles) {
+  if (!a.q_tiles || !a.k_tiles || !a.v_tiles || (!tiles && !a.out)) return LG_ERR_NULL;
+  if (a.nq <= 0 || a.nk <= 0 || a.out_rt_base < 0) return LG_ERR_SHAPE;
+  if (a.tq_pad * lg::kTile < a.nq || a.tk_pad * lg::kTile < a.nk || (a.tq_pad & 1) || (a.tk_pad & 1)) return LG_ERR_SHAPE;
+  return 0;
+}
+
+static int launch_attention(const AttnSideArgs* sides, int n_sides, void* out_tiles, int B, int H, float softmax_scale,
+                            cudaStream_t stream) {
+  if (B <= 0 || H <= 0 || n_sides < 1 || n_sides > 2) return LG_ERR_SHAPE;
   static bool attr_done = false;  // idempotent attribute; a benign race at worst sets it twice
   static int sms = 148;
   if (!attr_done) {
@@ -715,11 +740,21 @@ static int launch_attention(const void* q_tiles, const void* k_tiles, const void
     if (cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev) != cudaSuccess || sms <= 0) sms = 148;
     attr_done = true;
   }
-  const int items = B * H * (tq_pad / 2);
-  lg::AttnParams p{static_cast<const uint8_t*>(q_tiles), static_cast<const uint8_t*>(k_tiles),
-                   static_cast<const uint8_t*>(v_tiles), out, static_cast<uint8_t*>(out_tiles), out_rt_base, q_len,
-                   k_len, B, H, nq, nk, tq_pad, tk_pad, softmax_scale * 1.4426950408889634f, items};
-  lg::attention_kernel<<<items < sms ? items : sms, lg::kAttnThreads, lg::kAttnSmem, stream>>>(p);
+  lg::AttnParams p{};
+  p.out_tiles = static_cast<uint8_t*>(out_tiles);
+  p.B = B; p.H = H; p.scale_log2 = softmax_scale * 1.4426950408889634f;
+  long long items = 0;
+  for (int i = 0; i < n_sides; ++i) {
+    if (int e = check_side(sides[i], out_tiles != nullptr)) return e;
+    const AttnSideArgs& a = sides[i];
+    p.side[i] = lg::AttnSide{static_cast<const uint8_t*>(a.q_tiles), static_cast<const uint8_t*>(a.k_tiles),
+                             static_cast<const uint8_t*>(a.v_tiles), a.out, a.out_rt_base, a.q_len, a.k_len, a.nq, a.nk,
+                             a.tq_pad, a.tk_pad, B * H * (a.tq_pad / 2)};
+    items += p.side[i].items;
+  }
+  if (items > 0x7fffffffLL) return LG_ERR_SHAPE;
+  p.items = static_cast<int>(items);
+  lg::attention_kernel<<<p.items < sms ? p.items : sms, lg::kAttnThreads, lg::kAttnSmem, stream>>>(p);
   return static_cast<int>(cudaGetLastError());
 }
 
@@ -727,16 +762,29 @@ extern "C" int lg_attention(const void* q_tiles, const void* k_tiles, const void
                             const int* q_len, const int* k_len, int B, int H, int nq, int nk, int tq_pad, int tk_pad,
                             float softmax_scale, cudaStream_t stream) {
   if (!out) return LG_ERR_NULL;
-  return launch_attention(q_tiles, k_tiles, v_tiles, out, nullptr, 0, q_len, k_len, B, H, nq, nk, tq_pad, tk_pad,
-                          softmax_scale, stream);
+  const AttnSideArgs a{q_tiles, k_tiles, v_tiles, out, 0, q_len, k_len, nq, nk, tq_pad, tk_pad};
+  return launch_attention(&a, 1, nullptr, B, H, softmax_scale, stream);
 }
 
 extern "C" int lg_attention_tiles(const void* q_tiles, const void* k_tiles, const void* v_tiles, void* out_tiles,
                                   int out_rt_base, const int* q_len, const int* k_len, int B, int H, int nq, int nk,
                                   int tq_pad, int tk_pad, float softmax_scale, cudaStream_t stream) {
   if (!out_tiles) return LG_ERR_NULL;
-  return launch_attention(q_tiles, k_tiles, v_tiles, nullptr, out_tiles, out_rt_base, q_len, k_len, B, H, nq, nk,
-                          tq_pad, tk_pad, softmax_scale, stream);
+  const AttnSideArgs a{q_tiles, k_tiles, v_tiles, nullptr, out_rt_base, q_len, k_len, nq, nk, tq_pad, tk_pad};
+  return launch_attention(&a, 1, out_tiles, B, H, softmax_scale, stream);
+}
+
+// Both images of a SelfBlock (side 0: image 0 attends to itself, side 1: image 1) or both directions of a CrossBlock
+// (side 0: queries of image 0 over the keys / values of image 1, side 1: the reverse) in ONE launch.
+extern "C" int lg_attention_tiles2(const void* q0, const void* k0, const void* v0, int rt_base0, const int* q_len0,
+                                   const int* k_len0, int nq0, int nk0, int tq_pad0, int tk_pad0, const void* q1,
+                                   const void* k1, const void* v1, int rt_base1, const int* q_len1, const int* k_len1,
+                                   int nq1, int nk1, int tq_pad1, int tk_pad1, void* out_tiles, int B, int H,
+                                   float softmax_scale, cudaStream_t stream) {
+  if (!out_tiles) return LG_ERR_NULL;
+  const AttnSideArgs a[2] = {{q0, k0, v0, nullptr, rt_base0, q_len0, k_len0, nq0, nk0, tq_pad0, tk_pad0},
+                             {q1, k1, v1, nullptr, rt_base1, q_len1, k_len1, nq1, nk1, tq_pad1, tk_pad1}};
+  return launch_attention(a, 2, out_tiles, B, H, softmax_scale, stream);
 }
 
 #ifdef LG_ATTN_TRACE

@@ -9,7 +9,7 @@ processed as ONE activation matrix: rows = [image-0 batch (B*tp0 tiles) | image-
 
 Per block (self or cross):
     1. lg_linear_qkv_{self,cross}   x -> bf16 attention operand tiles (head split, rotary fused)
-    2. lg_attention_tiles x2        context of image 0 / image 1 -> split tiles (K atom = head)
+    2. lg_attention_tiles2          context of image 0 and image 1 (one launch) -> split tiles (K atom = head)
     3. lg_ffn_ln_gelu               GELU(LayerNorm([x | ctx] . W0'^T + b0')) -> split tiles (one fused launch)
     4. lg_linear_split              x + h . W3^T + b3 -> next x (split tiles)
 Step 3 uses the out_proj / to_out projection folded into ffn.0 (exact algebra, done once in fp64):
@@ -129,13 +129,12 @@ class TileEngine:
         scale = 64 ** -0.5
         # SelfBlock on both images (lightglue.py:268-269)
         C.linear_qkv_self(self.x, blk_s["wqkv"], blk_s["bqkv"], self.rot, B, self.tp0, self.tp1, self.qkv, self.H)
-        C.attention_tiles(q0, k0, v0, self.ctx, 0, M, M, len0, len0, scale)
-        C.attention_tiles(q1, k1, v1, self.ctx, self.rt0, N, N, len1, len1, scale)
+        C.attention_tiles2((q0, k0, v0, 0, M, M, len0, len0), (q1, k1, v1, self.rt0, N, N, len1, len1), self.ctx, scale)
         self._ffn(blk_s)
         # CrossBlock (lightglue.py:270-272): shared to_qk projection, both directions
         C.linear_qkv_cross(self.x, blk_c["wqkv"], blk_c["bqkv"], B, self.tp0, self.tp1, ((q0, v0), (q1, v1)), self.H)
-        C.attention_tiles(q0, q1, v1, self.ctx, 0, M, N, len0, len1, scale, cross=True)
-        C.attention_tiles(q1, q0, v0, self.ctx, self.rt0, N, M, len1, len0, scale, cross=True)
+        C.attention_tiles2((q0, q1, v1, 0, M, N, len0, len1), (q1, q0, v0, self.rt0, N, M, len1, len0), self.ctx, scale,
+                           cross=True)
         self._ffn(blk_c)
 
     def run_layers(self, n_layers: int, len0=None, len1=None, use_graph: bool = True):

@@ -126,6 +126,15 @@ int lg_attention_tiles(const void* q_tiles, const void* k_tiles, const void* v_t
                        int out_rt_base, const int* q_len, const int* k_len, int B, int H, int nq, int nk, int tq_pad,
                        int tk_pad, float softmax_scale, cudaStream_t stream);
 
+/* Two attention problems of one block in ONE launch: both images of a SelfBlock (lightglue.py:268-269; side 0 =
+ * image 0 on itself, side 1 = image 1), or both directions of a CrossBlock (:229-244; side 0 = queries of image 0
+ * over keys / values of image 1, side 1 = the reverse).  Arguments per side as in lg_attention_tiles. */
+int lg_attention_tiles2(const void* q0, const void* k0, const void* v0, int rt_base0, const int* q_len0,
+                        const int* k_len0, int nq0, int nk0, int tq_pad0, int tk_pad0, const void* q1, const void* k1,
+                        const void* v1, int rt_base1, const int* q_len1, const int* k_len1, int nq1, int nk1,
+                        int tq_pad1, int tk_pad1, void* out_tiles, int B, int H, float softmax_scale,
+                        cudaStream_t stream);
+
 /* (3) MatchAssignment.forward from the similarity on (lightglue.py:310-315) + sigmoid_log_double_softmax
  * (lightglue.py:284-296).  md0 (B,M,256), md1 (B,N,256) f32 = final_proj outputs; prescale multiplies
  * both (d^-1/4 = 0.25, lightglue.py:310); z0 (B,M), z1 (B,N) f32 matchability logits.  Writes scores

@@ -12,16 +12,25 @@ qk = torch.randn(B, N, 256, generator=g).cuda()
 v = torch.randn(B, N, 256, generator=g).cuda()
 qt, vt = C.pack_cross_qkv(qk, v, None, 4)
 tp = C.tiles_pad(N)
-out = C.alloc_split(B * tp, 256, "cuda")
+out = C.alloc_split(2 * B * tp, 256, "cuda")
+qt1, vt1 = C.pack_cross_qkv(v, qk, None, 4)   # the second image of the pair: its own operand tiles
+s0 = (qt, qt, vt, 0, N, N, None, None)
+s1 = (qt1, qt1, vt1, B * tp, N, N, None, None)
+
+
+def launch():  # the layer's launch: both images of a SelfBlock in one kernel
+    C.attention_tiles2(s0, s1, out, 0.125)
+
+
 for _ in range(2):
-    C.attention_tiles(qt, qt, vt, out, 0, N, N, None, None, 0.125)
+    launch()
 torch.cuda.synchronize()
 e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
 e0.record()
 for _ in range(reps):
-    C.attention_tiles(qt, qt, vt, out, 0, N, N, None, None, 0.125)
+    launch()
 e1.record()
 torch.cuda.synchronize()
 ms = e0.elapsed_time(e1) / reps
-fl = 4.0 * 64 * N * N * B * 4
-print(f"attention B={B} N={N}: {ms:.4f} ms/launch, {fl / ms / 1e9:.1f} TFLOP/s")
+fl = 2 * 4.0 * 64 * N * N * B * 4
+print(f"attention (both images, one launch) B={B} N={N}: {ms:.4f} ms/launch, {fl / ms / 1e9:.1f} TFLOP/s")
