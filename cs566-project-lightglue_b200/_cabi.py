@@ -51,6 +51,7 @@ SIGNATURES = {
     "lg_filter_from_keys": (_I, [_P, _P, _P, _F, _P, _P, _P, _P, _I, _I, _I, _P]),
     "lg_assign_tiles_ws_bytes": (_c.c_size_t, [_I, _I, _I]),
     "lg_assign_tiles": (_I, [_P, _P, _I, _I, _P, _P, _P, _P, _F, _P, _P, _P, _I, _I, _I, _P]),
+    "lg_assign_tiles_tmem": (_I, [_P, _P, _I, _I, _P, _P, _P, _P, _F, _P, _P, _P, _I, _I, _I, _P]),
     "lg_logit_rows": (_I, [_P, _P, _P, _P, _L, _P]),
     "lg_nn_assign": (_I, [_P, _P, _P, _P, _P, _P, _P, _I, _I, _I, _P]),
     "lg_nn_ws_bytes": (_c.c_size_t, [_I, _I, _I]),
@@ -268,9 +269,12 @@ def logit_rows(x, w, bias):
     return out
 
 
-def assign_tiles(a_tiles, b_tiles, tpa, tpb, z0, z1, th=None, m_len=None, n_len=None, scale=1.0 / 16):
+def assign_tiles(a_tiles, b_tiles, tpa, tpb, z0, z1, th=None, m_len=None, n_len=None, scale=1.0 / 16, impl=None):
     """lg_assign_tiles: split tiles of final_proj(desc0 / desc1) (image b at row tile b*tpa / b*tpb), z0 (B,M), z1 (B,N)
-    -> log assignment (B,M+1,N+1); with `th` also the filter_matches outputs (keys gathered in pass 2)."""
+    -> log assignment (B,M+1,N+1); with `th` also the filter_matches outputs (keys gathered in pass 2).
+    impl="tmem" calls the variant that keeps the image-0 row tile in tensor memory (lg_assign_tiles_tmem)."""
+    assert impl in (None, "tmem")
+    entry = "lg_assign_tiles_tmem" if impl == "tmem" else "lg_assign_tiles"
     B, M = z0.shape
     N = z1.shape[1]
     dev = z0.device
@@ -278,9 +282,9 @@ def assign_tiles(a_tiles, b_tiles, tpa, tpb, z0, z1, th=None, m_len=None, n_len=
     ws = torch.empty(lib().lg_assign_tiles_ws_bytes(B, M, N), device=dev, dtype=torch.uint8)
     keys = None if th is None else torch.empty(lib().lg_filter_ws_bytes(B, M, N), device=dev, dtype=torch.uint8)
     ml, nl = _i32(m_len), _i32(n_len)
-    _check(lib().lg_assign_tiles(_ptr(a_tiles), _ptr(b_tiles), int(tpa), int(tpb), _ptr(_f32c(z0, "z0")),
+    _check(getattr(lib(), entry)(_ptr(a_tiles), _ptr(b_tiles), int(tpa), int(tpb), _ptr(_f32c(z0, "z0")),
                                  _ptr(_f32c(z1, "z1")), _ptr(ml), _ptr(nl), float(scale), _ptr(scores), _ptr(ws),
-                                 _ptr(keys), B, M, N, _stream()), "lg_assign_tiles")
+                                 _ptr(keys), B, M, N, _stream()), entry)
     _count(3)
     if th is None:
         return scores

@@ -123,7 +123,7 @@ __device__ __forceinline__ float exp_fast(float x) {  // x <= 0; 2 ulp of the ex
 template <int kPass>
 __global__ void __launch_bounds__(kAssignThreads, 1) assign_tile_kernel(const AssignParams p) {
   extern __shared__ uint8_t smem_raw[];
-  uint8_t* base = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+  uint8_t* base = smem_raw + ((1024u - (smem_u32(smem_raw) & 1023u)) & 1023u);  // 1 KB aligned, still provably shared
   uint8_t* ring = base;
   float* stage = reinterpret_cast<float*>(base + kAssignStages * 2 * kOperandStage);
   float* s_rowterm = reinterpret_cast<float*>(base + kAssignStages * 2 * kOperandStage + kTransposeBytes);  // [2][128]

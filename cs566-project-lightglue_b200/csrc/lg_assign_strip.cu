@@ -20,6 +20,7 @@
 //   * pass 1 = row / column (max, sum exp) partials, reduce (lg_assign.cu), pass 2 = recompute + write, and --
 //     with keys -- the row / column argmax of filter_matches (lightglue.py:321-337) as packed 64-bit keys.
 #include "lg_assign.cuh"
+#include <cstdlib>
 #include "lg_common.cuh"
 #include "lg_keys.cuh"
 #include "lg_tiles.cuh"
@@ -98,7 +99,7 @@ constexpr float kLog2e = 1.4426950408889634f;
 template <int kPass>
 __global__ void __launch_bounds__(kStripThreads, 1) assign_strip_kernel(const StripParams p) {
   extern __shared__ uint8_t smem_raw[];
-  uint8_t* base = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+  uint8_t* base = smem_raw + ((1024u - (smem_u32(smem_raw) & 1023u)) & 1023u);  // 1 KB aligned, still provably shared
   uint8_t* a_res = base;
   uint8_t* ring = base + kStripATile;
   float* wstage = reinterpret_cast<float*>(ring + kStripStages * kHalfAtom);
@@ -418,9 +419,9 @@ static inline size_t strip_align256(size_t x) { return (x + 255) & ~static_cast<
 
 extern "C" size_t lg_assign_tiles_ws_bytes(int B, int M, int N) {
   if (B <= 0 || M <= 0 || N <= 0) return 0;
-  const size_t rt = (M + 127) / 128, ct = (N + 127) / 128;
+  const size_t rt = (M + 127) / 128, ct64 = (N + 63) / 64;
   size_t bytes = 0;
-  bytes += strip_align256(B * ct * static_cast<size_t>(M) * sizeof(float2));  // row partials
+  bytes += strip_align256(B * ct64 * static_cast<size_t>(M) * sizeof(float2));  // row partials (64-col tiles of the TMEM variant)
   bytes += strip_align256(B * rt * 4 * static_cast<size_t>(N) * sizeof(float2));  // col partials, one per warp
   bytes += 2 * strip_align256(static_cast<size_t>(B) * M * 4) + 2 * strip_align256(static_cast<size_t>(B) * N * 4);
   return bytes;
@@ -434,6 +435,13 @@ extern "C" int lg_assign_tiles(const void* a_tiles, const void* b_tiles, int tpa
   const int rt = (M + 127) / 128, ct = (N + 127) / 128;
   if (tpa < rt || tpb < ct) return LG_ERR_SHAPE;
   if ((reinterpret_cast<uintptr_t>(a_tiles) | reinterpret_cast<uintptr_t>(b_tiles)) & 15) return LG_ERR_ALIGN;
+  static const int use_tmem = [] {
+    const char* e = getenv("LG_ASSIGN_IMPL");
+    return e && e[0] == 't' ? 1 : 0;
+  }();
+  if (use_tmem)
+    return lg_assign_tiles_tmem(a_tiles, b_tiles, tpa, tpb, z0, z1, m_len, n_len, scale, scores, ws, keys_ws, B, M, N,
+                                stream);
   uint8_t* w = static_cast<uint8_t*>(ws);
   float2* row_part = reinterpret_cast<float2*>(w); w += strip_align256(static_cast<size_t>(B) * ct * M * sizeof(float2));
   float2* col_part = reinterpret_cast<float2*>(w); w += strip_align256(static_cast<size_t>(B) * rt * 4 * N * sizeof(float2));

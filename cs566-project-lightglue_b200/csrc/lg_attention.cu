@@ -166,7 +166,7 @@ __device__ __forceinline__ AttnItem attn_item(const AttnParams& p, int w) {
 
 __global__ void __launch_bounds__(kAttnThreads, 1) attention_kernel(const AttnParams p) {
   extern __shared__ uint8_t smem_raw[];
-  uint8_t* base = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+  uint8_t* base = smem_raw + ((1024u - (smem_u32(smem_raw) & 1023u)) & 1023u);  // 1 KB aligned, still provably shared
   uint8_t* sQ = base;                               // 2 buffers x (2 x 16 KB)
   uint8_t* sKV = sQ + 4 * kTileBytes;               // kStages x (K 16 KB | V^T 16 KB)
   uint8_t* sOut = sKV + kStages * 2 * kTileBytes;   // 8 x 4 KB epilogue staging

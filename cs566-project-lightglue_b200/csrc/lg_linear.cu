@@ -127,7 +127,7 @@ __global__ void __launch_bounds__(kLinThreads, 1) linear_kernel(const LinearPara
   constexpr int kLinStages = linear_stages<kNt, kEpi, kCtas>();
   static_assert(kLinStages >= 2, "ring needs two stages");
   extern __shared__ uint8_t smem_raw[];
-  uint8_t* base = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+  uint8_t* base = smem_raw + ((1024u - (smem_u32(smem_raw) & 1023u)) & 1023u);  // 1 KB aligned, still provably shared
   uint8_t* ring = base;
   uint8_t* stg = ring + kLinStages * kStage;              // 32 KB epilogue staging (kEpiSplit, pair mode: 3 x 32 KB)
   uint8_t* rot = stg + kStageOut;                         // 32 KB rotary table (kEpiQkvSelf only)

@@ -176,6 +176,12 @@ size_t lg_assign_tiles_ws_bytes(int B, int M, int N);
 int lg_assign_tiles(const void* a_tiles, const void* b_tiles, int tpa, int tpb, const float* z0, const float* z1,
                     const int* m_len, const int* n_len, float scale, float* scores, void* ws, void* keys_ws, int B,
                     int M, int N, cudaStream_t stream);
+/* Same contract, the variant that keeps the image-0 row tile in TENSOR MEMORY (tcgen05.mma A operand from TMEM, 64-
+ * column tiles of image 1 streamed through shared memory).  lg_assign_tiles dispatches here when the environment has
+ * LG_ASSIGN_IMPL=tmem; exported so that the parity tests can call both. */
+int lg_assign_tiles_tmem(const void* a_tiles, const void* b_tiles, int tpa, int tpb, const float* z0, const float* z1,
+                         const int* m_len, const int* n_len, float scale, float* scores, void* ws, void* keys_ws,
+                         int B, int M, int N, cudaStream_t stream);
 
 /* Linear(256 -> 1) logits of every row: out[i] = <x[i,:], w> + bias[0]  (MatchAssignment.matchability,
  * lightglue.py:304,313-314, before the log-sigmoid).  x (rows, 256) f32 contiguous. */

@@ -25,8 +25,9 @@ def timeit(fn, reps=10):
     return e0.elapsed_time(e1) / reps
 
 
-print(f"assign_tiles + keys        {timeit(lambda: C.assign_tiles(a, b, tp, tp, z0, z1, 0.1)):.3f} ms")
-print(f"assign_tiles               {timeit(lambda: C.assign_tiles(a, b, tp, tp, z0, z1)):.3f} ms")
+IMPL = "tmem" if os.environ.get("LG_PROFILE_IMPL") == "tmem" else None  # ncu: -k regex:assign_tmem for this variant
+print(f"assign_tiles + keys        {timeit(lambda: C.assign_tiles(a, b, tp, tp, z0, z1, 0.1, impl=IMPL)):.3f} ms")
+print(f"assign_tiles               {timeit(lambda: C.assign_tiles(a, b, tp, tp, z0, z1, impl=IMPL)):.3f} ms")
 if os.environ.get("LG_PROFILE_TF32"):
     s = C.assign(md0, md1, z0, z1)
     print(f"assign (tf32x3)            {timeit(lambda: C.assign(md0, md1, z0, z1)):.3f} ms")

@@ -221,8 +221,12 @@ def _split_tiles(C, md):
     return C.rows_to_tiles(md.cuda().contiguous(), tp), tp
 
 
+IMPLS = [None, "tmem"]  # lg_assign_tiles (row tile resident in shared memory) / lg_assign_tiles_tmem (in tensor memory)
+
+
+@pytest.mark.parametrize("impl", IMPLS)
 @pytest.mark.parametrize("B,M,N", [(1, 128, 128), (2, 200, 333), (1, 1024, 1024), (2, 2048, 2048), (1, 1, 700), (3, 129, 1)])
-def test_assign_tiles_vs_oracle(C, B, M, N):
+def test_assign_tiles_vs_oracle(C, B, M, N, impl):
     """lg_assign_tiles (split-bf16 strips, the matcher's path) against the fp64 evaluation of
     sigmoid_log_double_softmax (lightglue.py:284-296): 3-term split-bf16 products, measured 1.3e-4 abs on these
     |sim| ~ 10 operands (the TF32x3 kernel: 1.3e-5), bound 3e-4 (the bf16-path budget on log_assignment is 2e-2)."""
@@ -234,7 +238,7 @@ def test_assign_tiles_vs_oracle(C, B, M, N):
     ref64 = O.sigmoid_log_double_softmax(sim, z0.double(), z1.double())
     a, tpa = _split_tiles(C, md0)
     b, tpb = _split_tiles(C, md1)
-    got = C.assign_tiles(a, b, tpa, tpb, z0[..., 0].contiguous().cuda(), z1[..., 0].contiguous().cuda()).cpu()
+    got = C.assign_tiles(a, b, tpa, tpb, z0[..., 0].contiguous().cuda(), z1[..., 0].contiguous().cuda(), impl=impl).cpu()
     assert torch.isfinite(got).all()
     assert (got.double() - ref64).abs().max().item() < 3e-4
     assert got[:, -1, -1].abs().max() == 0
@@ -242,7 +246,8 @@ def test_assign_tiles_vs_oracle(C, B, M, N):
 
 @pytest.mark.parametrize("B,M,N,varlen", [(1, 300, 200, False), (2, 257, 640, True), (1, 128, 128, False),
                                           (2, 97, 130, True), (3, 1500, 1100, True)])
-def test_assign_tiles_keys_equal_filter_scan(C, B, M, N, varlen):
+@pytest.mark.parametrize("impl", IMPLS)
+def test_assign_tiles_keys_equal_filter_scan(C, B, M, N, varlen, impl):
     """keys gathered in pass 2 of lg_assign_tiles + lg_filter_from_keys == lg_filter_matches (one scan of the matrix)
     on the same scores, bit for bit, including ties and variable-length batches; padding is -inf."""
     g = torch.Generator().manual_seed(B * 1000 + M + N)
@@ -260,8 +265,8 @@ def test_assign_tiles_keys_equal_filter_scan(C, B, M, N, varlen):
     nl = torch.tensor(nls, dtype=torch.int32).cuda() if varlen else None
     a, tpa = _split_tiles(C, md0)
     b, tpb = _split_tiles(C, md1)
-    s_plain = C.assign_tiles(a, b, tpa, tpb, z0.cuda(), z1.cuda(), None, ml, nl)
-    s_keys, f_keys = C.assign_tiles(a, b, tpa, tpb, z0.cuda(), z1.cuda(), 0.05, ml, nl)
+    s_plain = C.assign_tiles(a, b, tpa, tpb, z0.cuda(), z1.cuda(), None, ml, nl, impl=impl)
+    s_keys, f_keys = C.assign_tiles(a, b, tpa, tpb, z0.cuda(), z1.cuda(), 0.05, ml, nl, impl=impl)
     assert torch.equal(s_plain, s_keys)
     f_scan = C.filter_matches(s_keys, 0.05, ml, nl)
     for x, y in zip(f_scan, f_keys):
@@ -393,9 +398,10 @@ def _guards_intact(raw, g, fill=0x5A):
     return bool((raw[:g] == fill).all()) and bool((raw[-g:] == fill).all())
 
 
+@pytest.mark.parametrize("impl", IMPLS)
 @pytest.mark.parametrize("B,M,N,varlen", [(2, 200, 333, False), (3, 129, 257, True), (1, 1, 700, False), (2, 1024, 640, True)])
-def test_assign_tiles_writes_stay_in_bounds(C, B, M, N, varlen):
-    """lg_assign_tiles through the raw C ABI with guard zones around the scores, the workspace and the key buffer."""
+def test_assign_tiles_writes_stay_in_bounds(C, B, M, N, varlen, impl):
+    """lg_assign_tiles[_tmem] through the raw C ABI with guard zones around the scores, the workspace and the key buffer."""
     lib = C.lib()
     g = _gen(B + M + N)
     a, tpa = _split_tiles(C, torch.randn(B, M, 256, generator=g))
@@ -406,14 +412,15 @@ def test_assign_tiles_writes_stay_in_bounds(C, B, M, N, varlen):
     raw_s, s, gs = _guarded(B * (M + 1) * (N + 1) * 4)
     raw_w, w, gw = _guarded(lib.lg_assign_tiles_ws_bytes(B, M, N))
     raw_k, k, gk = _guarded(lib.lg_filter_ws_bytes(B, M, N))
-    rc = lib.lg_assign_tiles(a.data_ptr(), b.data_ptr(), tpa, tpb, z0.data_ptr(), z1.data_ptr(),
-                             None if ml is None else ml.data_ptr(), None if nl is None else nl.data_ptr(), 1.0 / 16,
-                             s.data_ptr(), w.data_ptr(), k.data_ptr(), B, M, N, torch.cuda.current_stream().cuda_stream)
+    entry = lib.lg_assign_tiles_tmem if impl == "tmem" else lib.lg_assign_tiles
+    rc = entry(a.data_ptr(), b.data_ptr(), tpa, tpb, z0.data_ptr(), z1.data_ptr(),
+               None if ml is None else ml.data_ptr(), None if nl is None else nl.data_ptr(), 1.0 / 16,
+               s.data_ptr(), w.data_ptr(), k.data_ptr(), B, M, N, torch.cuda.current_stream().cuda_stream)
     torch.cuda.synchronize()
     assert rc == 0
     assert _guards_intact(raw_s, gs) and _guards_intact(raw_w, gw) and _guards_intact(raw_k, gk)
     got = s.view(torch.float32).view(B, M + 1, N + 1)
-    want = C.assign_tiles(a, b, tpa, tpb, z0, z1, None, ml, nl)
+    want = C.assign_tiles(a, b, tpa, tpb, z0, z1, None, ml, nl, impl=impl)
     assert torch.equal(got, want)
 
 
