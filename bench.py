@@ -45,7 +45,7 @@ def parse():
     ap.add_argument("--gpus", type=int, default=1)
     ap.add_argument("--steps", type=int, default=10)
     ap.add_argument("--warmup", type=int, default=3)
-    ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
+    ap.add_argument("--impl", default="b200", choices=["b200", "reference", "eager"])
     ap.add_argument("--batch", type=int, default=32, help="pairs per GPU per step")
     ap.add_argument("--kpts", type=int, default=2048)
     ap.add_argument("--cpu-pairs", type=int, default=4, help="pairs timed for the cpu_baseline sample")
@@ -94,6 +94,41 @@ def run_reference(a):
         "config": {"workload": workload_name(a), "note": "CPU arm: oracle port of the reference (Python reference cannot travel)"},
         "cpu_baseline": {"value": rate, "unit": UNIT, "cores": cores, "kind": "port", "sample": sample},
         "e2e": {"value": rate, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        "gpu_launches": 0,
+    })
+
+
+def run_eager(a):
+    """Informative arm (SURVEY 8(d) "extra informative baseline"): the reference's algorithm in PyTorch eager fp32 on
+    the SAME B200 -- the oracle port (torch ops in the reference's op order) on cuda tensors, fp32 SDPA as in
+    lightglue.py:146-149, TF32 off.  Not the product and not the reference arm the driver compares against."""
+    from oracle import lightglue_oracle as O
+
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return
+    W = importlib.import_module(PKG + ".weights")
+    dev = torch.device("cuda", 0)
+    torch.backends.cuda.matmul.allow_tf32 = False
+    torch.backends.cudnn.allow_tf32 = False
+    sd = {k: v.to(dev) for k, v in W.make_state_dict(CONF, seed=0).items()}
+    data = to_device(W.make_inputs(a.batch, a.kpts, a.kpts, seed=1), dev, non_blocking=False)
+    for _ in range(max(a.warmup, 3)):
+        O.forward(sd, CONF, data)
+    torch.cuda.synchronize()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for _ in range(a.steps):
+        O.forward(sd, CONF, data)
+    e1.record()
+    torch.cuda.synchronize()
+    ms = e0.elapsed_time(e1)
+    emit({
+        "impl": "eager", "metric": METRIC, "value": a.batch * a.steps / (ms / 1e3), "unit": UNIT, "n_gpus": 1,
+        "steps": a.steps, "warmup": max(a.warmup, 3), "ms_per_step": ms / a.steps, "higher_is_better": True,
+        "scaling": "weak", "vs_baseline": None, "dtype": "f32 (PyTorch eager, cuBLAS / SDPA, TF32 off)",
+        "data": "synthetic",
+        "config": {"workload": workload_name(a), "note": "oracle port of the reference on cuda tensors: informative only"},
         "gpu_launches": 0,
     })
 
@@ -351,5 +386,7 @@ if __name__ == "__main__":
     args = parse()
     if args.impl == "reference":
         run_reference(args)
+    elif args.impl == "eager":
+        run_eager(args)
     else:
         run_b200(args)
