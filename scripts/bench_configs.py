@@ -75,13 +75,17 @@ def fp32_path(N=2048, steps=3):
     model.load_state_dict(sd)
     model = model.cuda()
     out = {"config": "fp32 path (b200.precision=fp32), %d kpts" % N}
-    for B in (1, 4):
+    for B in (1, 4, 32):
         ms, _ = timed(model, cuda(W.make_inputs(B, N, N, seed=1, correlated=0.7)), steps, warmup=1)
         out["pairs_per_s_B%d" % B] = B / ms * 1e3
     print(json.dumps(out))
 
 
 if __name__ == "__main__":
-    config3()
-    config4()
-    fp32_path()
+    import sys
+    if "fp32" in sys.argv[1:]:
+        fp32_path()
+    else:
+        config3()
+        config4()
+        fp32_path()

@@ -1,21 +1,17 @@
-"""Summarise an `ncu --metrics gpu__time_duration.sum --csv` launch list by kernel name."""
+"""Sum an ncu --csv launch list (gpu__time_duration.sum) by kernel name: python scripts/summarize_launches.py file.csv [last_n]"""
 import csv, sys, collections
-rows = [r for r in csv.reader(open(sys.argv[1], errors="ignore")) if len(r) > 5]
-hdr = next(i for i, r in enumerate(rows) if "Kernel Name" in r)
-H = rows[hdr]
-kn, mv, mu = H.index("Kernel Name"), H.index("Metric Value"), H.index("Metric Unit")
-tot = collections.defaultdict(lambda: [0.0, 0])
-for r in rows[hdr + 1:]:
-    try:
-        v = float(r[mv].replace(",", ""))
-    except ValueError:
-        continue
-    u = r[mu]
-    ms = v / 1e6 if u in ("ns", "nsecond") else v / 1e3 if u in ("us", "usecond") else v
-    name = r[kn].split("(")[0][:70]
-    tot[name][0] += ms
-    tot[name][1] += 1
-total = sum(v[0] for v in tot.values())
-print(f"total {total:.2f} ms, {sum(v[1] for v in tot.values())} launches")
-for name, (ms, n) in sorted(tot.items(), key=lambda kv: -kv[1][0]):
-    print(f"  {ms:8.2f} ms {100 * ms / total:5.1f}%  x{n:4d}  {name}")
+rows = [r for r in csv.reader(open(sys.argv[1])) if len(r) > 10]
+hdr = rows[0]
+ki, vi = hdr.index("Kernel Name"), hdr.index("Metric Value")
+ui = hdr.index("Metric Unit")
+body = rows[1:]
+if len(sys.argv) > 2:
+    body = body[-int(sys.argv[2]):]
+tot = collections.Counter(); cnt = collections.Counter()
+for r in body:
+    v = float(r[vi].replace(",", "")) * (1e-3 if r[ui] in ("ns", "nsecond") else 1.0)
+    tot[r[ki][:70]] += v; cnt[r[ki][:70]] += 1
+s = sum(tot.values())
+print(f"total {s:.1f} us, {len(body)} launches")
+for k, v in tot.most_common(14):
+    print(f"{v:10.1f} us {100 * v / s:5.1f}% x{cnt[k]:4d} {k}")
