@@ -4,3 +4,5 @@ import importlib
 _p = importlib.import_module("cs566-project-lightglue_b200.pipeline")
 HostPipeline = _p.HostPipeline
 RESULT_KEYS = _p.RESULT_KEYS
+pack_pairs = _p.pack_pairs
+unpack_pred = _p.unpack_pred

@@ -24,6 +24,8 @@ SIGNATURES = {
     "lg_posenc": (_I, [_P, _P, _P, _P, _P, _F, _P, _P, _I, _I, _P]),
     "lg_posenc_scale_ori": (_I, [_P, _P, _P, _P, _P, _P, _P, _F, _P, _P, _I, _I, _P]),
     "lg_keypoint_extent": (_I, [_P, _P, _I, _I, _P]),
+    "lg_keypoint_extent_valid": (_I, [_P, _P, _P, _I, _I, _P]),
+    "lg_posenc_per_image": (_I, [_P, _P, _P, _P, _P, _P, _P, _P, _P, _P, _I, _I, _P]),
     "lg_pack_self_qkv": (_I, [_P, _P, _P, _P, _P, _P, _P, _I, _I, _I, _I, _P]),
     "lg_pack_cross_qkv": (_I, [_P, _P, _P, _P, _P, _I, _I, _I, _I, _P]),
     "lg_attention": (_I, [_P, _P, _P, _P, _P, _P, _I, _I, _I, _I, _I, _I, _F, _P]),
@@ -136,27 +138,39 @@ def version() -> int:
     return lib().lg_version()
 
 
-def posenc(kpts, size, wr, wc, bc, cond: float, scales=None, oris=None):
-    """-> (cos, sin) compact tables (B,N,32). size (B,2) f32 or None (extent of the points); scales / oris (B,N):
-    the 4-d positional input of add_scale_ori (wr is then (32,4))."""
+def posenc(kpts, size, wr, wc, bc, cond, scales=None, oris=None, lens=None):
+    """-> (cos, sin) compact tables (B,N,32). size (B,2) f32 or None (extent of the points, of the first lens[b] points
+    when `lens` is given); scales / oris (B,N): the 4-d positional input of add_scale_ori (wr is then (32,4)).
+    cond: the keypoint count as a float (the reference's scalar condition), or a (B,) tensor = one count per image."""
     B, N, _ = kpts.shape
     _f32c(kpts, "kpts")
     if size is None:
         size = torch.empty(B, 2, device=kpts.device, dtype=torch.float32)
-        _check(lib().lg_keypoint_extent(_ptr(kpts), _ptr(size), B, N, _stream()), "lg_keypoint_extent")
+        if lens is None:
+            _check(lib().lg_keypoint_extent(_ptr(kpts), _ptr(size), B, N, _stream()), "lg_keypoint_extent")
+        else:
+            _check(lib().lg_keypoint_extent_valid(_ptr(kpts), _ptr(_i32(lens)), _ptr(size), B, N, _stream()),
+                   "lg_keypoint_extent_valid")
+        _count(1)
     cos = torch.empty(B, N, 32, device=kpts.device, dtype=torch.float32)
     sin = torch.empty_like(cos)
+    assert wr.shape == ((32, 4) if scales is not None else (32, 2))
     if scales is not None:
-        assert wr.shape == (32, 4) and scales.shape == (B, N) and oris.shape == (B, N)
-        _check(lib().lg_posenc_scale_ori(_ptr(kpts), _ptr(_f32c(scales, "scales")), _ptr(_f32c(oris, "oris")),
-                                         _ptr(_f32c(size, "size")), _ptr(_f32c(wr, "wr")), _ptr(_f32c(wc, "wc")),
-                                         _ptr(_f32c(bc, "bc")), float(cond), _ptr(cos), _ptr(sin), B, N, _stream()),
-               "lg_posenc_scale_ori")
-        _count(1)
-        return cos, sin
-    assert wr.shape == (32, 2)
-    _check(lib().lg_posenc(_ptr(kpts), _ptr(_f32c(size, "size")), _ptr(_f32c(wr, "wr")), _ptr(_f32c(wc, "wc")),
-                           _ptr(_f32c(bc, "bc")), float(cond), _ptr(cos), _ptr(sin), B, N, _stream()), "lg_posenc")
+        assert scales.shape == (B, N) and oris.shape == (B, N)
+        _f32c(scales, "scales"), _f32c(oris, "oris")
+    if isinstance(cond, torch.Tensor):
+        assert cond.shape == (B,)
+        cond = cond.to(device=kpts.device, dtype=torch.float32).contiguous()
+        _check(lib().lg_posenc_per_image(_ptr(kpts), _ptr(scales), _ptr(oris), _ptr(_f32c(size, "size")),
+                                         _ptr(_f32c(wr, "wr")), _ptr(_f32c(wc, "wc")), _ptr(_f32c(bc, "bc")), _ptr(cond),
+                                         _ptr(cos), _ptr(sin), B, N, _stream()), "lg_posenc_per_image")
+    elif scales is not None:
+        _check(lib().lg_posenc_scale_ori(_ptr(kpts), _ptr(scales), _ptr(oris), _ptr(_f32c(size, "size")),
+                                         _ptr(_f32c(wr, "wr")), _ptr(_f32c(wc, "wc")), _ptr(_f32c(bc, "bc")), float(cond),
+                                         _ptr(cos), _ptr(sin), B, N, _stream()), "lg_posenc_scale_ori")
+    else:
+        _check(lib().lg_posenc(_ptr(kpts), _ptr(_f32c(size, "size")), _ptr(_f32c(wr, "wr")), _ptr(_f32c(wc, "wc")),
+                               _ptr(_f32c(bc, "bc")), float(cond), _ptr(cos), _ptr(sin), B, N, _stream()), "lg_posenc")
     _count(1)
     return cos, sin
 

@@ -13,10 +13,13 @@
 namespace lg {
 
 // per-image (shift, scale) when no image size is given: size = 1 + max - min over the points
-__global__ void posenc_extent_kernel(const float* __restrict__ kpts, float* __restrict__ size_out, int N) {
+// lens (B) non-null: only the first lens[b] points of image b count (padded batches of unequal images)
+__global__ void posenc_extent_kernel(const float* __restrict__ kpts, const int* __restrict__ lens,
+                                     float* __restrict__ size_out, int N) {
   const int b = blockIdx.x;
+  const int nv = lens ? min(max(lens[b], 0), N) : N;
   float mnx = INFINITY, mny = INFINITY, mxx = -INFINITY, mxy = -INFINITY;
-  for (int i = threadIdx.x; i < N; i += blockDim.x) {
+  for (int i = threadIdx.x; i < nv; i += blockDim.x) {
     const float2 k = reinterpret_cast<const float2*>(kpts)[static_cast<size_t>(b) * N + i];
     mnx = fminf(mnx, k.x); mxx = fmaxf(mxx, k.x); mny = fminf(mny, k.y); mxy = fmaxf(mxy, k.y);
   }
@@ -30,9 +33,9 @@ __global__ void posenc_extent_kernel(const float* __restrict__ kpts, float* __re
     mnx = l < nw ? red[0][l] : INFINITY; mny = l < nw ? red[1][l] : INFINITY;
     mxx = l < nw ? red[2][l] : -INFINITY; mxy = l < nw ? red[3][l] : -INFINITY;
     mnx = -warp_max(-mnx); mny = -warp_max(-mny); mxx = warp_max(mxx); mxy = warp_max(mxy);
-    if (l == 0) {
-      size_out[2 * b] = __fsub_rn(__fadd_rn(1.f, mxx), mnx);
-      size_out[2 * b + 1] = __fsub_rn(__fadd_rn(1.f, mxy), mny);
+    if (l == 0) {  // an image without points gets a unit extent (nothing reads its encodings)
+      size_out[2 * b] = nv > 0 ? __fsub_rn(__fadd_rn(1.f, mxx), mnx) : 1.f;
+      size_out[2 * b + 1] = nv > 0 ? __fsub_rn(__fadd_rn(1.f, mxy), mny) : 1.f;
     }
   }
 }
@@ -42,8 +45,8 @@ __global__ void posenc_extent_kernel(const float* __restrict__ kpts, float* __re
 __global__ void posenc_kernel(const float* __restrict__ kpts, const float* __restrict__ scales,
                               const float* __restrict__ oris, const float* __restrict__ size,
                               const float* __restrict__ wr, const float* __restrict__ wc,
-                              const float* __restrict__ bc, float cond, float* __restrict__ cos_t,
-                              float* __restrict__ sin_t, int B, int N) {
+                              const float* __restrict__ bc, float cond, const float* __restrict__ cond_b,
+                              float* __restrict__ cos_t, float* __restrict__ sin_t, int B, int N) {
   const size_t idx = static_cast<size_t>(blockIdx.x) * blockDim.x + threadIdx.x;
   if (idx >= static_cast<size_t>(B) * N * 32) return;
   const int j = idx & 31;
@@ -65,7 +68,8 @@ __global__ void posenc_kernel(const float* __restrict__ kpts, const float* __res
     proj = __fmaf_rn(oris[pt], wr[4 * j + 3], proj);
   }
   // Linear(1->32)(relu(count)): count*w + b
-  const float modulated = __fmaf_rn(fmaxf(cond, 0.f), wc[j], bc[j]);
+  // cond_b (B) non-null: one count per image (a padded batch of unequal images, each conditioned on its own count)
+  const float modulated = __fmaf_rn(fmaxf(cond_b ? cond_b[b] : cond, 0.f), wc[j], bc[j]);
   const float phase = __fadd_rn(proj, modulated);
   float s, c;
   sincosf(phase, &s, &c);
@@ -82,7 +86,7 @@ extern "C" int lg_posenc(const float* kpts, const float* size, const float* wr, 
   if (!size) return LG_ERR_NULL;  // size=None branch: call lg_keypoint_extent first
   const size_t total = static_cast<size_t>(B) * N * 32;
   lg::posenc_kernel<<<static_cast<unsigned>((total + 255) / 256), 256, 0, stream>>>(kpts, nullptr, nullptr, size, wr, wc,
-                                                                                   bc, cond, cos_t, sin_t, B, N);
+                                                                                   bc, cond, nullptr, cos_t, sin_t, B, N);
   return static_cast<int>(cudaGetLastError());
 }
 
@@ -94,7 +98,7 @@ extern "C" int lg_posenc_scale_ori(const float* kpts, const float* scales, const
   if (B <= 0 || N <= 0) return LG_ERR_SHAPE;
   const size_t total = static_cast<size_t>(B) * N * 32;
   lg::posenc_kernel<<<static_cast<unsigned>((total + 255) / 256), 256, 0, stream>>>(kpts, scales, oris, size, wr, wc, bc,
-                                                                                   cond, cos_t, sin_t, B, N);
+                                                                                   cond, nullptr, cos_t, sin_t, B, N);
   return static_cast<int>(cudaGetLastError());
 }
 
@@ -102,7 +106,31 @@ extern "C" int lg_posenc_scale_ori(const float* kpts, const float* scales, const
 extern "C" int lg_keypoint_extent(const float* kpts, float* size_out, int B, int N, cudaStream_t stream) {
   if (!kpts || !size_out) return LG_ERR_NULL;
   if (B <= 0 || N <= 0) return LG_ERR_SHAPE;
-  lg::posenc_extent_kernel<<<B, 256, 0, stream>>>(kpts, size_out, N);
+  lg::posenc_extent_kernel<<<B, 256, 0, stream>>>(kpts, nullptr, size_out, N);
+  return static_cast<int>(cudaGetLastError());
+}
+
+// The same over the first lens[b] points of every image (lens (B) int32, may be null = all N)
+extern "C" int lg_keypoint_extent_valid(const float* kpts, const int* lens, float* size_out, int B, int N,
+                                        cudaStream_t stream) {
+  if (!kpts || !size_out) return LG_ERR_NULL;
+  if (B <= 0 || N <= 0) return LG_ERR_SHAPE;
+  lg::posenc_extent_kernel<<<B, 256, 0, stream>>>(kpts, lens, size_out, N);
+  return static_cast<int>(cudaGetLastError());
+}
+
+// lg_posenc / lg_posenc_scale_ori with ONE CONDITION PER IMAGE: cond_b (B) f32 replaces the scalar count, so that a
+// padded batch of images with unequal keypoint counts gets, image by image, the encodings of the reference's own
+// one-pair-per-call forward (condition = that image's count, lightglue.py:490-491).  scales / oris may be null.
+extern "C" int lg_posenc_per_image(const float* kpts, const float* scales, const float* oris, const float* size,
+                                   const float* wr, const float* wc, const float* bc, const float* cond_b,
+                                   float* cos_t, float* sin_t, int B, int N, cudaStream_t stream) {
+  if (!kpts || !size || !wr || !wc || !bc || !cond_b || !cos_t || !sin_t) return LG_ERR_NULL;
+  if ((scales == nullptr) != (oris == nullptr)) return LG_ERR_NULL;
+  if (B <= 0 || N <= 0) return LG_ERR_SHAPE;
+  const size_t total = static_cast<size_t>(B) * N * 32;
+  lg::posenc_kernel<<<static_cast<unsigned>((total + 255) / 256), 256, 0, stream>>>(kpts, scales, oris, size, wr, wc, bc,
+                                                                                   0.f, cond_b, cos_t, sin_t, B, N);
   return static_cast<int>(cudaGetLastError());
 }
 

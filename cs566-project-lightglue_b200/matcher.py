@@ -128,7 +128,10 @@ class LightGlue(nn.Module):
         "weights_from_version": "v0.1_arxiv",
         "loss": {"gamma": 1.0, "fn": "nll", "nll_balancing": 0.5},
         # namespaced additions (existing YAMLs stay valid)
-        "b200": {"precision": "bf16", "cuda_graph": True, "engine_cache": 2},
+        # condition: "padded" = the reference's own behaviour on a padded batch (every image conditioned on the padded
+        # length, lightglue.py:490-491); "valid" = every image of a batch with num_keypoints0/1 conditioned on ITS OWN
+        # count, so that the batch reproduces the reference's one-pair-per-call results (pipeline.pack_pairs)
+        "b200": {"precision": "bf16", "cuda_graph": True, "engine_cache": 2, "condition": "padded"},
     }
     required_data_keys = ["keypoints0", "keypoints1", "descriptors0", "descriptors1"]
 
@@ -140,6 +143,8 @@ class LightGlue(nn.Module):
             raise ValueError("the sm_100a kernels are built for descriptor_dim=256, num_heads=4 (no fallback)")
         if conf.b200.precision not in ("bf16", "fp32"):
             raise ValueError(f"b200.precision={conf.b200.precision!r}: 'bf16' (tensor-core throughput path) or 'fp32'")
+        if conf.b200.condition not in ("padded", "valid"):
+            raise ValueError(f"b200.condition={conf.b200.condition!r}: 'padded' (reference semantics) or 'valid'")
         self.input_proj = nn.Linear(conf.input_dim, d, bias=True) if conf.input_dim != d else nn.Identity()
         self.posenc = _PosEnc(2 + 2 * int(bool(conf.add_scale_ori)), (d // h) // 2)
         self.transformers = nn.ModuleList([_Layer(d) for _ in range(L)])
@@ -287,10 +292,13 @@ class LightGlue(nn.Module):
             flat = lambda t, k: t.reshape(b, k).float().contiguous()
             so0 = (flat(data["scales0"], m), flat(data["oris0"], m))
             so1 = (flat(data["scales1"], n), flat(data["oris1"], n))
+        per_image = conf.b200.condition == "valid" and len0 is not None
+        cond0 = len0.float() if per_image else float(m)
+        cond1 = len1.float() if per_image else float(n)
         cs0 = C.posenc(kpts0.float().contiguous(), self._image_size(data, "view0", kpts0), pe.Wr.weight, wc,
-                       pe.condition_modulation.bias, float(m), *so0)
+                       pe.condition_modulation.bias, cond0, *so0, lens=len0 if per_image else None)
         cs1 = C.posenc(kpts1.float().contiguous(), self._image_size(data, "view1", kpts1), pe.Wr.weight, wc,
-                       pe.condition_modulation.bias, float(n), *so1)
+                       pe.condition_modulation.bias, cond1, *so1, lens=len1 if per_image else None)
         do_early_stop = conf.depth_confidence > 0
         do_point_pruning = conf.width_confidence > 0
         if conf.b200.precision == "fp32":

@@ -29,6 +29,68 @@ def _copy_into(dst, src):
             dst[k].copy_(v, non_blocking=True)
 
 
+PAIR_KEYS = ("keypoints", "descriptors", "scales", "oris")
+
+
+def pack_pairs(pairs, length0=None, length1=None, multiple=128):
+    """One padded batch out of single-pair data dicts with unequal keypoint counts -- the batching the reference's
+    exporter cannot do (utils/export_predictions.py:32-79 feeds one pair per call; its pad helper is
+    models/utils/misc.py:19-57 `pad_to_length(mode="zeros")`, mirrored here: zeros behind the valid points).
+
+    pairs: list of reference-style dicts with (1, n_i, .) tensors `keypoints0/1`, `descriptors0/1` (+ `scales*`,
+    `oris*` when used) and optional `view0/1.image_size`.  Returns a dict with (B, N_pad, .) tensors, `num_keypoints0/1`
+    (B,) int32 and `view*.image_size` (B, 2) f32; N_pad = the longest count rounded up to `multiple` (the kernels' row
+    tile), or `length0/1`.  For a pair without `image_size` the reference's size=None rule (1 + max - min over the
+    pair's own points, lightglue.py:25-26) is applied here, so the padding never enters it.
+    With conf `b200.condition: valid` the matcher then reproduces, pair by pair, the one-pair-per-call results."""
+    assert len(pairs) > 0
+    out = {}
+    for side, length in (("0", length0), ("1", length1)):
+        counts = [int(p["keypoints" + side].shape[-2]) for p in pairs]
+        n_pad = length if length is not None else max(multiple, -(-max(counts) // multiple) * multiple)
+        assert n_pad >= max(counts)
+        for key in PAIR_KEYS:
+            name = key + side
+            if name not in pairs[0]:
+                continue
+            rows = []
+            for p, c in zip(pairs, counts):
+                t = p[name].reshape(c, -1)
+                rows.append(torch.cat([t, t.new_zeros((n_pad - c, t.shape[1]))], 0))
+            stacked = torch.stack(rows, 0)
+            out[name] = stacked[..., 0] if key in ("scales", "oris") else stacked
+        out["num_keypoints" + side] = torch.tensor(counts, dtype=torch.int32, device=pairs[0]["keypoints" + side].device)
+        sizes = []
+        for p in pairs:
+            v = p.get("view" + side)
+            sz = None if v is None else v.get("image_size")
+            k = p["keypoints" + side].reshape(-1, 2).float()
+            if sz is None:
+                sz = 1 + k.max(0).values - k.min(0).values if k.shape[0] > 0 else k.new_ones(2)
+            sizes.append(torch.as_tensor(sz).reshape(-1)[-2:].to(device=k.device, dtype=torch.float32))
+        out["view" + side] = {"image_size": torch.stack(sizes, 0)}
+    return out
+
+
+def unpack_pred(pred, batch):
+    """Per-pair views of a batched prediction, cut to each pair's valid counts (the shapes the one-pair-per-call
+    forward returns): list of dicts with `matches0/1`, `matching_scores0/1` (1, n_i) and, when present,
+    `log_assignment` (1, m_i + 1, n_i + 1) = the valid block plus the dustbin row / column."""
+    l0, l1 = batch["num_keypoints0"].tolist(), batch["num_keypoints1"].tolist()
+    outs = []
+    for b, (m, n) in enumerate(zip(l0, l1)):
+        d = {"matches0": pred["matches0"][b:b + 1, :m], "matches1": pred["matches1"][b:b + 1, :n],
+             "matching_scores0": pred["matching_scores0"][b:b + 1, :m],
+             "matching_scores1": pred["matching_scores1"][b:b + 1, :n]}
+        if "log_assignment" in pred:
+            s = pred["log_assignment"][b]
+            rows = torch.cat([torch.arange(m, device=s.device), torch.tensor([s.shape[0] - 1], device=s.device)])
+            cols = torch.cat([torch.arange(n, device=s.device), torch.tensor([s.shape[1] - 1], device=s.device)])
+            d["log_assignment"] = s.index_select(0, rows).index_select(1, cols)[None]
+        outs.append(d)
+    return outs
+
+
 class HostPipeline:
     """`for pred in HostPipeline(model).run(batches)`: `batches` yields reference-style data dicts of (pinned) host
     tensors, all of one shape; `pred` holds pinned host tensors for `keys`, valid until `depth` more batches have

@@ -47,6 +47,14 @@ int lg_posenc_scale_ori(const float* kpts, const float* scales, const float* ori
 
 /* size_out (B,2) f32 = 1 + max - min over each image's keypoints (lightglue.py:25-26). */
 int lg_keypoint_extent(const float* kpts, float* size_out, int B, int N, cudaStream_t stream);
+/* the same over the first lens[b] points of image b (lens (B) int32 or NULL): padded batches of unequal images */
+int lg_keypoint_extent_valid(const float* kpts, const int* lens, float* size_out, int B, int N, cudaStream_t stream);
+/* lg_posenc / lg_posenc_scale_ori (scales, oris may be NULL) with ONE CONDITION PER IMAGE: cond_b (B) f32 replaces the
+ * scalar keypoint count of lightglue.py:490-491, so that every image of a padded batch gets the encodings of the
+ * reference's one-pair-per-call forward on that image alone (conf b200.condition = "valid"). */
+int lg_posenc_per_image(const float* kpts, const float* scales, const float* oris, const float* size, const float* wr,
+                        const float* wc, const float* bc, const float* cond_b, float* cos_t, float* sin_t, int B, int N,
+                        cudaStream_t stream);
 
 /* (1)+(2) SelfBlock operand producer (lightglue.py:185-188): de-interleave Wqkv output
  * qkv (B,N,H*192) [f = h*192 + d*3 + {q,k,v}], rotary on q,k (lightglue.py:36-43) from the compact

@@ -345,3 +345,36 @@ def test_host_pipeline_matches_direct_calls():
     for i, (a, b) in enumerate(zip(want, got)):
         for k in P.RESULT_KEYS:
             assert torch.equal(a[k], b[k]), (i, k)
+
+
+@pytest.mark.parametrize("precision,la_tol", [("bf16", 1e-4), ("fp32", 1e-5)])
+def test_packed_pairs_reproduce_one_pair_per_call(precision, la_tol):
+    """pipeline.pack_pairs + conf b200.condition = "valid": pairs with unequal keypoint counts in ONE padded batch give,
+    pair by pair, what one call per pair gives (the only mode of the reference's exporter,
+    utils/export_predictions.py:32-79; the reference conditions the positional encoding on the count,
+    lightglue.py:490-491: a common phase of q and k, which cancels in exact arithmetic but moves every sin / cos by
+    rounding, so a plainly padded batch agrees only to the path's noise level) -- and with it the oracle's one-pair forward."""
+    P = pkg("pipeline")
+    conf = {"filter_threshold": 0.1, "b200": {"condition": "valid", "precision": precision}}
+    sd = W.make_state_dict(conf, seed=0)
+    model = _model(conf, sd)
+    shapes = [(300, 222), (517, 640), (700, 511), (129, 128)]
+    pairs = [W.make_inputs(1, m, n, seed=40 + i, correlated=0.7) for i, (m, n) in enumerate(shapes)]
+    pairs[1].pop("view0"), pairs[1].pop("view1")  # the size=None branch must not see the padding either
+    batch = P.pack_pairs([_cuda(p) for p in pairs])
+    assert batch["keypoints0"].shape == (4, 768, 2) and batch["keypoints1"].shape == (4, 640, 2)
+    pred = model(batch)
+    per_pair = P.unpack_pred(pred, batch)
+    for i, (p, got) in enumerate(zip(pairs, per_pair)):
+        single = model(_cuda(p))
+        for k in ("matches0", "matches1"):
+            assert torch.equal(single[k], got[k]), (i, k)
+        for k in ("matching_scores0", "matching_scores1"):
+            assert (single[k] - got[k]).abs().max() < 1e-5, (i, k)
+        la_s, la_b = single["log_assignment"], got["log_assignment"]
+        assert la_s.shape == la_b.shape
+        assert (la_s - la_b).abs().max() < la_tol, i
+        want = O.forward(sd, conf, p)  # the reference's own one-pair forward (oracle pinned to it by the goldens)
+        err = (want["log_assignment"] - la_b.cpu()).abs().max().item()
+        assert err < (BF16_TOL if precision == "bf16" else 1e-4), (i, err)
+        assert (want["matches0"] == got["matches0"].cpu()).float().mean() > 0.97

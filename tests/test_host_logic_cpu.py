@@ -77,3 +77,34 @@ def test_cpu_inputs_are_rejected_not_computed():
     with pytest.raises(NotImplementedError):
         NN.NearestNeighborMatcher({"loss": "N_pair"})
     assert NN.NearestNeighborMatcher({"ratio_thresh": 0.8}).conf.mutual_check is True
+
+
+def test_pack_pairs_and_unpack_pred_shapes():
+    """pipeline.pack_pairs: zero padding behind the valid points (pad_to_length(mode="zeros"), models/utils/misc.py:19-57),
+    counts, per-pair extents when image_size is missing; unpack_pred cuts back to the valid block + dustbins."""
+    P = pkg("pipeline")
+    W = pkg("weights")
+    pairs = [W.make_inputs(1, m, n, seed=3 + i) for i, (m, n) in enumerate([(5, 130), (200, 7)])]
+    pairs[0].pop("view0")
+    b = P.pack_pairs(pairs)
+    assert b["keypoints0"].shape == (2, 256, 2) and b["descriptors1"].shape == (2, 256, 256)
+    assert b["num_keypoints0"].tolist() == [5, 200] and b["num_keypoints1"].tolist() == [130, 7]
+    assert torch.equal(b["keypoints0"][0, :5], pairs[0]["keypoints0"][0]) and b["keypoints0"][0, 5:].abs().max() == 0
+    k = pairs[0]["keypoints0"][0]
+    assert torch.equal(b["view0"]["image_size"][0], 1 + k.max(0).values - k.min(0).values)
+    assert torch.equal(b["view0"]["image_size"][1], pairs[1]["view0"]["image_size"][0].float())
+    assert P.pack_pairs(pairs, length0=384)["keypoints0"].shape[1] == 384
+    M, N = 256, 256
+    pred = {"matches0": torch.zeros(2, M, dtype=torch.int64), "matches1": torch.zeros(2, N, dtype=torch.int64),
+            "matching_scores0": torch.zeros(2, M), "matching_scores1": torch.zeros(2, N),
+            "log_assignment": torch.arange(2 * (M + 1) * (N + 1), dtype=torch.float32).reshape(2, M + 1, N + 1)}
+    out = P.unpack_pred(pred, b)
+    assert out[0]["matches0"].shape == (1, 5) and out[0]["log_assignment"].shape == (1, 6, 131)
+    assert out[1]["log_assignment"][0, -1, -1] == pred["log_assignment"][1, M, N]
+    assert out[1]["log_assignment"][0, 3, -1] == pred["log_assignment"][1, 3, N]
+
+
+def test_condition_option_validated():
+    with pytest.raises(ValueError):
+        M.LightGlue({"b200": {"condition": "per-image"}})
+    assert M.LightGlue({}).conf.b200.condition == "padded"
