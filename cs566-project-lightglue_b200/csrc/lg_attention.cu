@@ -93,6 +93,14 @@ __device__ __forceinline__ void reg_inc() { asm volatile("setmaxnreg.inc.sync.al
 template <int N>
 __device__ __forceinline__ void reg_dec() { asm volatile("setmaxnreg.dec.sync.aligned.u32 %0;" ::"n"(N)); }
 
+#ifdef LG_ATTN_DBG
+// progress markers into MAPPED PINNED HOST memory (survive a launch failure): 16 ints per CTA
+__device__ volatile int* g_dbg = nullptr;
+#define DBG(slot, val) do { if (g_dbg) { g_dbg[blockIdx.x * 16 + (slot)] = (val); __threadfence_system(); } } while (0)
+#else
+#define DBG(slot, val) do {} while (0)
+#endif
+
 #ifdef LG_ATTN_TRACE
 __device__ unsigned long long g_trace[8192];
 __device__ __forceinline__ unsigned long long gtime() {
@@ -132,8 +140,8 @@ struct __align__(8) AttnBarriers {
   uint64_t kv_full[kStages];
   uint64_t kv_empty[kStages];
   uint64_t s_full[3];
-  uint64_t p_full[2];
-  uint64_t pv_done[2];
+  uint64_t p_full[4];  // [tile t][key block parity]: see the note at the arrival
+  uint64_t pv_done[4];  // [tile t][key block parity], like p_full
   uint64_t o_free[2];
   uint32_t tmem_base;
 };
@@ -178,7 +186,8 @@ __global__ void __launch_bounds__(kAttnThreads, 1) attention_kernel(const AttnPa
   if (threadIdx.x == 0) {
     for (int i = 0; i < 2; ++i) {
       mbar_init(&bar->q_full[i], 1); mbar_init(&bar->q_empty[i], 1);
-      mbar_init(&bar->p_full[i], 1); mbar_init(&bar->pv_done[i], 1); mbar_init(&bar->o_free[i], 128);
+      mbar_init(&bar->p_full[2 * i], 1); mbar_init(&bar->p_full[2 * i + 1], 1);
+      mbar_init(&bar->pv_done[2 * i], 1); mbar_init(&bar->pv_done[2 * i + 1], 1); mbar_init(&bar->o_free[i], 128);
     }
     for (int s = 0; s < kStages; ++s) { mbar_init(&bar->kv_full[s], 1); mbar_init(&bar->kv_empty[s], 1); }
     for (int i = 0; i < 3; ++i) mbar_init(&bar->s_full[i], 1);
@@ -200,6 +209,7 @@ __global__ void __launch_bounds__(kAttnThreads, 1) attention_kernel(const AttnPa
         for (int w = blockIdx.x; w < p.items; w += gridDim.x) {
           const AttnItem it = attn_item(p, w);
           if (it.skip) continue;
+          DBG(0, w);
           const AttnSide& sd = p.side[it.s];
           const size_t bh = static_cast<size_t>(it.b) * p.H + it.h;
           const uint8_t* gq = sd.q_tiles + (bh * sd.tq_pad + it.qt0) * kTileBytes;
@@ -211,6 +221,7 @@ __global__ void __launch_bounds__(kAttnThreads, 1) attention_kernel(const AttnPa
           bulk_g2s(sQ + qs * 2 * kTileBytes, gq, 2 * kTileBytes, &bar->q_full[qs]);  // tiles qt0, qt0+1 are adjacent
           for (int j = 0; j < it.nkt; ++j, ++kvi) {
             const int s = kvi % kStages;
+            DBG(1, static_cast<int>(kvi));
             if (kvi >= kStages) mbar_wait(&bar->kv_empty[s], ((kvi / kStages) - 1) & 1);
             mbar_arrive_expect_tx(&bar->kv_full[s], 2 * kTileBytes);
             bulk_g2s(sKV + s * 2 * kTileBytes, gk + static_cast<size_t>(j) * kTileBytes, kTileBytes, &bar->kv_full[s]);
@@ -296,10 +307,14 @@ __global__ void __launch_bounds__(kAttnThreads, 1) attention_kernel(const AttnPa
           // P sits in the first 64 columns of S buffer G % 3 as packed bf16 (A operand from TMEM)
           const uint32_t tP = tmem + kColS + (G_p % 3) * 128;
           const uint64_t dv = dV0 + static_cast<uint64_t>(s * (2 * kTileBytes >> 4));
+          if (leader) { DBG(2, w); DBG(3, static_cast<int>(G_p)); DBG(4, qw); DBG(5, static_cast<int>(G_q)); DBG(12, 1); }
           prepare_qk();                         // step G+3: recycles S buffer G % 3 behind this PV
-          mbar_wait(&bar->p_full[t], kvi & 1);  // P_t(j) stored in its S buffer
+          if (leader) DBG(12, 2);
+          mbar_wait(&bar->p_full[2 * t + (kvi & 1)], (kvi >> 1) & 1);  // P_t(j) stored in its S buffer
           if (leader) TRACE(6, G_p);
+          if (leader) DBG(12, 3);
           if (j == 0 && p_cnt > 0) mbar_wait(&bar->o_free[t], (p_cnt - 1) & 1);  // previous item's O_t was read out
+          if (leader) DBG(12, 4);
           tc_fence_after();
 #pragma unroll
           for (int kk = 0; kk < 8; ++kk) {  // K = 128 keys = 8 x 16: 8 TMEM columns / 32 B of a V^T row per step
@@ -309,10 +324,11 @@ __global__ void __launch_bounds__(kAttnThreads, 1) attention_kernel(const AttnPa
                            (j > 0 || kk > 0));
           }
           issue_qk();  // same-thread MMAs execute in order: the similarity overwrites the buffer after PV read P
-          if (leader) umma_commit(&bar->pv_done[t]);  // (fires after the similarity too: only the rare rescale
+          if (leader) umma_commit(&bar->pv_done[2 * t + (kvi & 1)]);  // (fires after the similarity too: only the rare rescale
                                                       // path and the item epilogue wait on it)
           if (leader && t == 1) umma_commit(&bar->kv_empty[s]);  // K_j and V_j are dead once PV1_j retires
           commit_qk();
+          if (leader) DBG(12, 5);
           if (leader) TRACE(7, G_p);
         }
         p_kv += it.nkt;
@@ -344,8 +360,12 @@ __global__ void __launch_bounds__(kAttnThreads, 1) attention_kernel(const AttnPa
       float4* drow = sd.out ? reinterpret_cast<float4*>(sd.out + (static_cast<size_t>(it.b) * sd.nq + row) * row_stride +
                                                         it.h * kHeadDim)
                             : nullptr;
+      if ((threadIdx.x & 127) == 0) { DBG(6 + t, w); DBG(10 + t, it.skip ? 9 : 0); }
       if (it.skip) {
         // nothing to attend from / to: rows are zero (reference: nan_to_num of an all-masked softmax)
+#ifdef LG_DBG_NOSKIPZERO
+        continue;
+#endif
         if (dt) {
 #pragma unroll
           for (int ch = 0; ch < 8; ++ch) {
@@ -366,7 +386,9 @@ __global__ void __launch_bounds__(kAttnThreads, 1) attention_kernel(const AttnPa
         const uint32_t G = 2 * (kv_base + j) + t;    // global step: S buffer G % 3
         const uint32_t tS = tS0 + (G % 3) * 128;
         if ((threadIdx.x & 127) == 0) TRACE(t * 3, kv_base + j);
+        if ((threadIdx.x & 127) == 0) { DBG(8 + t, j); DBG(10 + t, 1); }
         mbar_wait(&bar->s_full[G % 3], (G / 3) & 1);
+        if ((threadIdx.x & 127) == 0) DBG(10 + t, 2);
         tc_fence_after();
         if ((threadIdx.x & 127) == 0) TRACE(t * 3 + 1, kv_base + j);
 
@@ -396,9 +418,8 @@ __global__ void __launch_bounds__(kAttnThreads, 1) attention_kernel(const AttnPa
             if (need) { alpha = first ? 0.f : ex2_approx((m_used - mx) * c); m_used = mx; }
             l *= alpha;
             if (!first) {
-              // O_t must be quiescent: PV_t(j-1) retired.  The barrier is at most one phase ahead of that PV,
-              // so a parity wait is valid although earlier phases were never waited for.
-              mbar_wait(&bar->pv_done[t], (kv_base + j - 1) & 1);
+              // O_t must be quiescent: PV_t(j-1) retired (barrier pair: see the epilogue wait)
+              mbar_wait(&bar->pv_done[2 * t + ((kv_base + j - 1) & 1)], ((kv_base + j - 1) >> 1) & 1);
               tc_fence_after();
 #pragma unroll
               for (int cb = 0; cb < 2; ++cb) {
@@ -637,12 +658,32 @@ __global__ void __launch_bounds__(kAttnThreads, 1) attention_kernel(const AttnPa
         // one block ahead: ONE arrival per block, after all 128 rows are stored (a 128-count barrier could be
         // completed by a mix of arrivals of block j and block j+1).
         asm volatile("bar.sync %0, 128;" ::"r"(1 + t) : "memory");
-        if ((threadIdx.x & 127) == 0) { mbar_arrive(&bar->p_full[t]); TRACE(t * 3 + 2, kv_base + j); }
+        // Two barriers per tile, alternating with the key block: the three-deep similarity lookahead lets a warpgroup
+        // finish blocks j and j+1 while the MMA warp is held up (at an item boundary it decodes the next items, which
+        // with per-image lengths costs dependent global loads, and waits for their Q tile).  On ONE barrier those two
+        // arrivals would flip the phase twice and the MMA warp's parity wait for block j would never return; block
+        // j+2 (the same barrier again) cannot be reached before PV(j) has consumed P(j).
+        if ((threadIdx.x & 127) == 0) {
+          mbar_arrive(&bar->p_full[2 * t + ((kv_base + j) & 1)]);
+          TRACE(t * 3 + 2, kv_base + j);
+        }
       }
 
       // epilogue: O / l.  O_t is copied to registers and released first so the next item's PV can start.
       if ((threadIdx.x & 127) == 0) TRACE(8 + t * 4, kv_base);
-      mbar_wait(&bar->pv_done[t], (kv_base + it.nkt - 1) & 1);
+      if ((threadIdx.x & 127) == 0) DBG(10 + t, 3);
+      // Earlier phases of this barrier were never waited for, so a parity wait is only sound if the barrier cannot be
+      // TWO completions behind: when this warpgroup finishes its last block, PV_t(nkt-3) has retired (its commit
+      // precedes the similarity of block nkt-1 in the MMA warp's order) but PV_t(nkt-2) may not have -- with the MMA
+      // warp held up at the item boundary (it decodes the next items and waits for their Q tile first).  On ONE
+      // barrier per tile that state has the parity this wait looks for: it returned early and O_t was read two
+      // blocks short (intermittent errors of ~5e-2 with many items per CTA).  With one barrier per block parity the
+      // barrier of block nkt-1 is at most one completion behind.
+      {
+        const uint32_t last = kv_base + it.nkt - 1;
+        mbar_wait(&bar->pv_done[2 * t + (last & 1)], (last >> 1) & 1);
+      }
+      if ((threadIdx.x & 127) == 0) DBG(10 + t, 4);
       tc_fence_after();
       if ((threadIdx.x & 127) == 0) TRACE(9 + t * 4, kv_base);
       tmem_ld32(tO, va);
@@ -703,6 +744,7 @@ __global__ void __launch_bounds__(kAttnThreads, 1) attention_kernel(const AttnPa
       }
     }
     if (lane == 0) bulk_wait_all();  // outstanding context stores
+    if ((threadIdx.x & 127) == 0) DBG(10 + t, 7);
   }
   tc_fence_before();
   __syncthreads();
@@ -786,6 +828,12 @@ extern "C" int lg_attention_tiles2(const void* q0, const void* k0, const void* v
                              {q1, k1, v1, nullptr, rt_base1, q_len1, k_len1, nq1, nk1, tq_pad1, tk_pad1}};
   return launch_attention(a, 2, out_tiles, B, H, softmax_scale, stream);
 }
+
+#ifdef LG_ATTN_DBG
+extern "C" int lg_debug_attn_set(int* host_mapped) {
+  return static_cast<int>(cudaMemcpyToSymbol(lg::g_dbg, &host_mapped, sizeof(host_mapped)));
+}
+#endif
 
 #ifdef LG_ATTN_TRACE
 extern "C" int lg_debug_attn_trace(unsigned long long* host_out, int n) {

@@ -81,10 +81,53 @@ def fp32_path(N=2048, steps=3):
     print(json.dumps(out))
 
 
+def exporter_loop(pairs_total=64, group=16, lo=1024, hi=2048):
+    """The exporter's workload (utils/export_predictions.py:32-79): single pairs with unequal keypoint counts.
+    (a) one call per pair, as the reference drives the matcher; (b) pipeline.pack_pairs in groups + b200.condition=valid
+    (same results pair by pair, tests/test_forward_gpu.py::test_packed_pairs_reproduce_one_pair_per_call)."""
+    P = importlib.import_module(PKG + ".pipeline")
+    conf = {"filter_threshold": 0.1, "b200": {"condition": "valid"}}
+    model = M.LightGlue(conf)
+    model.load_state_dict(W.make_state_dict(conf, seed=0))
+    model = model.cuda()
+    rng = np.random.default_rng(7)
+    counts = rng.integers(lo, hi + 1, (pairs_total, 2))
+    pairs = [cuda(W.make_inputs(1, int(m), int(n), seed=100 + i, correlated=0.7)) for i, (m, n) in enumerate(counts)]
+
+    def one_by_one():
+        return [model(p)["matches0"] for p in pairs]
+
+    def packed():
+        out = []
+        for g in range(0, pairs_total, group):
+            batch = P.pack_pairs(pairs[g:g + group], length0=hi, length1=hi)
+            out += [d["matches0"] for d in P.unpack_pred(model(batch), batch)]
+        return out
+
+    res = {}
+    for name, fn in (("one_pair_per_call", one_by_one), ("packed_groups_of_%d" % group, packed)):
+        for _ in range(2):
+            got = fn()
+        torch.cuda.synchronize()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        got = fn()
+        e1.record()
+        torch.cuda.synchronize()
+        res[name] = pairs_total / e0.elapsed_time(e1) * 1e3
+        res.setdefault("_m", []).append(got)
+    a, b = res.pop("_m")
+    same = sum(int(torch.equal(x, y)) for x, y in zip(a, b))
+    print(json.dumps({"config": "exporter loop: %d single pairs, counts U{%d..%d} per image" % (pairs_total, lo, hi),
+                      "pairs_per_s": res, "pairs_with_identical_matches0": "%d/%d" % (same, pairs_total)}))
+
+
 if __name__ == "__main__":
     import sys
     if "fp32" in sys.argv[1:]:
         fp32_path()
+    elif "exporter" in sys.argv[1:]:
+        exporter_loop()
     else:
         config3()
         config4()

@@ -378,3 +378,37 @@ def test_packed_pairs_reproduce_one_pair_per_call(precision, la_tol):
         err = (want["log_assignment"] - la_b.cpu()).abs().max().item()
         assert err < (BF16_TOL if precision == "bf16" else 1e-4), (i, err)
         assert (want["matches0"] == got["matches0"].cpu()).float().mean() > 0.97
+
+
+def test_packed_pairs_at_export_scale():
+    """16 pairs of 1024..2048 keypoints packed to 2048 (the exporter workload): many work items per persistent CTA with
+    skipped blocks in between -- the shape that dead-locked the attention kernel before the P-ready barriers alternated."""
+    P = pkg("pipeline")
+    conf = {"filter_threshold": 0.1, "b200": {"condition": "valid"}}
+    model = _model(conf, W.make_state_dict(conf, seed=0))
+    rng = np.random.default_rng(7)
+    counts = rng.integers(1024, 2049, (16, 2))
+    pairs = [_cuda(W.make_inputs(1, int(m), int(n), seed=100 + i, correlated=0.7)) for i, (m, n) in enumerate(counts)]
+    batch = P.pack_pairs(pairs, length0=2048, length1=2048)
+    for _ in range(2):  # eager call, then the captured graph
+        per_pair = P.unpack_pred(model(batch), batch)
+    for i in (0, 9, 15):
+        single = model(pairs[i])
+        assert torch.equal(single["matches0"], per_pair[i]["matches0"])
+        assert (single["log_assignment"] - per_pair[i]["log_assignment"]).abs().max() < 1e-4
+
+
+def test_forward_large_batch_equals_one_pair_calls():
+    """16 x 2048 x 2048 (1024 attention work items on 148 persistent CTAs, 7 per CTA) against the same pairs one per
+    call (64 items: one per CTA).  Caught a premature read of the attention accumulator at item boundaries (parity wait
+    on a barrier two completions behind) that only showed with several items per CTA."""
+    conf = {"filter_threshold": 0.1}
+    model = _model(conf, W.make_state_dict(conf, seed=0))
+    data = _cuda(W.make_inputs(16, 2048, 2048, seed=3, correlated=0.7))
+    for _ in range(3):  # eager, capture, replay
+        pred = model(data)
+        la = pred["log_assignment"].clone()
+        for b in (0, 5, 10, 15):
+            single = model(_slice_pair(data, b))
+            assert (single["log_assignment"][0] - la[b]).abs().max() < 1e-4, b
+            assert torch.equal(single["matches0"][0], pred["matches0"][b])
