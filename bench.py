@@ -296,6 +296,20 @@ def run_b200(a):
     sampler.stop_flag = True
     value = world * a.batch * a.steps / (ms / 1e3)
 
+    # ---- self-check outside the timed regions: three pairs of the timed batch (several work items per persistent CTA)
+    # against the same pairs one per call (one item per CTA); a synchronisation fault at scale shows here as ~5e-2
+    pred = step()
+    la_batch = pred["log_assignment"]
+    check_err, check_same = 0.0, True
+    for b in sorted({0, a.batch // 2, a.batch - 1}):
+        one = model({k: ({kk: vv[b:b + 1] for kk, vv in v.items()} if isinstance(v, dict) else v[b:b + 1])
+                     for k, v in data.items()})
+        check_err = max(check_err, float((one["log_assignment"][0] - la_batch[b]).abs().max()))
+        check_same = check_same and bool(torch.equal(one["matches0"][0], pred["matches0"][b]))
+    check = {"max_abs_diff_log_assignment_vs_one_pair_calls": check_err, "matches0_identical": check_same}
+    if check_err > 1e-3:
+        raise RuntimeError(f"bench self-check failed: batched forward differs from one-pair calls by {check_err}")
+
     # ---- roofline of the dominant kernel (attention): CUDA events around every launch
     C.ATTN_EVENTS = []
     barrier()
@@ -374,6 +388,7 @@ def run_b200(a):
             "roofline": roofline,
             "roofline_assignment": roofline_assign,
             "cpu_baseline": cpu,
+            "check": check,
             "clocks": sampler.summary(),
         }
         emit(line)

@@ -16,7 +16,7 @@ def cuda(data):
     return {k: ({kk: vv.cuda() for kk, vv in v.items()} if isinstance(v, dict) else v.cuda()) for k, v in data.items()}
 
 
-def timed(model, data, steps, warmup=3):
+def timed(model, data, steps, warmup=10):  # a fresh box needs ~10 forwards to ramp its clocks / page in
     for _ in range(warmup):
         pred = model(data)
     torch.cuda.synchronize()
