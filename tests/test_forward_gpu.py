@@ -412,3 +412,20 @@ def test_forward_large_batch_equals_one_pair_calls():
             single = model(_slice_pair(data, b))
             assert (single["log_assignment"][0] - la[b]).abs().max() < 1e-4, b
             assert torch.equal(single["matches0"][0], pred["matches0"][b])
+
+
+def test_adaptive_batched_at_scale_vs_single():
+    """Adaptive depth + width on 16 pairs x 2048 keypoints (several work items per persistent CTA in every kernel, pruned
+    lengths differ per image): pairs 0, 7, 15 must match the same pair run alone through the B = 1 adaptive path."""
+    conf = {"filter_threshold": 0.1, "depth_confidence": 0.95, "width_confidence": 0.95}
+    sd = W.make_state_dict(conf, seed=0, adaptive_fixture=True)
+    data = _cuda(W.make_inputs(16, 2048, 2048, seed=5, correlated=0.7))
+    model = _model(conf, sd)
+    pred = model(data)
+    for b in (0, 7, 15):
+        one = model(_slice_pair(data, b))
+        assert int(one["exit_layer"]) == int(pred["exit_layer"][b])
+        assert torch.equal(one["prune0"], pred["prune0"][b:b + 1]) and torch.equal(one["prune1"], pred["prune1"][b:b + 1])
+        assert one["log_assignment"].shape == pred["log_assignment"][b].shape
+        assert (one["log_assignment"] - pred["log_assignment"][b]).abs().max() < 1e-3
+        assert (one["matches0"] == pred["matches0"][b:b + 1]).float().mean() > 0.995

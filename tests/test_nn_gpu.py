@@ -62,3 +62,20 @@ def test_nn_registry_alias():
     assert mod.__main_model__ is pkg("nn_matcher").NearestNeighborMatcher
     with pytest.raises(RuntimeError):
         mod.__main_model__({})({"descriptors0": torch.zeros(1, 4, 256), "descriptors1": torch.zeros(1, 4, 256)})
+
+
+def test_nn_matcher_large_batch_equals_one_pair_calls():
+    """16 x 2048 x 2048 through the NN matcher (similarity tiles, double log-softmax, top-2 passes) against one pair
+    per call: the persistent kernels run several work items per CTA only at this size."""
+    conf = {"ratio_thresh": 0.95, "distance_thresh": 1.2, "mutual_check": True}
+    model = pkg("nn_matcher").NearestNeighborMatcher(conf)
+    g = torch.Generator().manual_seed(3)
+    d0 = torch.nn.functional.normalize(torch.randn(16, 2048, 256, generator=g), dim=-1).cuda()
+    d1 = torch.nn.functional.normalize(0.8 * d0.cpu()[:, torch.randperm(2048, generator=g)] +
+                                       0.02 * torch.randn(16, 2048, 256, generator=g), dim=-1).cuda()
+    pred = model({"descriptors0": d0, "descriptors1": d1})
+    assert (pred["matches0"] >= 0).float().mean() > 0.5
+    for b in (0, 9, 15):
+        one = model({"descriptors0": d0[b:b + 1], "descriptors1": d1[b:b + 1]})
+        assert torch.equal(one["matches0"][0], pred["matches0"][b]) and torch.equal(one["matches1"][0], pred["matches1"][b])
+        assert (one["log_assignment"][0] - pred["log_assignment"][b]).abs().max() < 1e-5
