@@ -95,6 +95,33 @@ def test_posenc_vs_oracle(C, B, N, size):
     assert (sin.cpu() - sin_r).abs().max() < 2e-6
 
 
+@pytest.mark.parametrize("with_size", [True, False])
+def test_posenc_per_image_condition_vs_oracle(C, with_size):
+    """lg_posenc_per_image + lg_keypoint_extent_valid: every image of a padded batch gets the table the oracle computes
+    for that image ALONE (its own count as the condition, lightglue.py:490-491; its own extent when size is None,
+    :25-26) -- bit for bit what the scalar-condition kernel gives on the un-padded image."""
+    sd = W.make_state_dict({}, seed=0)
+    wr = sd["posenc.Wr.weight"].cuda()
+    wc = sd["posenc.condition_modulation.weight"].cuda().reshape(-1).contiguous()
+    bc = sd["posenc.condition_modulation.bias"].cuda()
+    lens = [700, 33, 1, 512]
+    N = 768
+    k = W.make_inputs(4, N, N, seed=8, image_size=(640, 480))["keypoints0"]
+    for b, n in enumerate(lens):
+        k[b, n:] = 0  # zero padding, as pack_pairs writes it
+    size = torch.tensor([[640., 480.]] * 4).cuda() if with_size else None
+    ln = torch.tensor(lens, dtype=torch.int32).cuda()
+    cos, sin = C.posenc(k.cuda(), size, wr, wc, bc, ln.float(), lens=ln)
+    for b, n in enumerate(lens):
+        kb = k[b:b + 1, :n]
+        kn = O.normalize_keypoints(kb, torch.tensor([[640., 480.]]) if with_size else None)
+        cos_r, sin_r = O.posenc_table(sd, kn, float(n))
+        # one fp32 ulp of a phase of ~n rad (6e-5 at 700): the CPU's (n,2)x(2,32) GEMV may round mul+add or fma
+        assert (cos[b, :n].cpu() - cos_r[0]).abs().max() < 1.3e-4 and (sin[b, :n].cpu() - sin_r[0]).abs().max() < 1.3e-4
+        c1, s1 = C.posenc(kb.cuda().contiguous(), None if size is None else size[:1], wr, wc, bc, float(n))
+        assert torch.equal(c1[0], cos[b, :n]) and torch.equal(s1[0], sin[b, :n])
+
+
 # ----------------------------------------------------------------------------- (2) attention
 def _unswizzle_tiles(t, n):
     """Inverse of the SWIZZLE_128B tile image: (B,H,T,16384) u8 -> (B,H,T*128,64) bf16 rows."""
