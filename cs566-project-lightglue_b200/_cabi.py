@@ -105,7 +105,10 @@ def lib():
 
 def _check(code: int, what: str):
     if code != 0:
-        kind = {-1: "null pointer", -2: "bad shape", -3: "misaligned pointer"}.get(code, f"cudaError {code}")
+        kind = {-1: "null pointer", -2: "bad shape", -3: "misaligned pointer",
+                719: "cudaError 719 (launch failure: a device trap -- the kernels abort through mbar_wait's spin limit "
+                     "instead of hanging when a pipeline stalls -- or a fault of an EARLIER asynchronous launch)",
+                }.get(code, f"cudaError {code}")
         raise RuntimeError(f"{what} failed: {kind}")
 
 
