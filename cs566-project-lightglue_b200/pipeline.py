@@ -53,11 +53,11 @@ def pack_pairs(pairs, length0=None, length1=None, multiple=128):
             name = key + side
             if name not in pairs[0]:
                 continue
-            rows = []
-            for p, c in zip(pairs, counts):
-                t = p[name].reshape(c, -1)
-                rows.append(torch.cat([t, t.new_zeros((n_pad - c, t.shape[1]))], 0))
-            stacked = torch.stack(rows, 0)
+            first = pairs[0][name]
+            width = first.shape[-1] if key in ("keypoints", "descriptors") else 1
+            stacked = first.new_zeros((len(pairs), n_pad, width))  # one allocation, one slice copy per pair
+            for b, (p, c) in enumerate(zip(pairs, counts)):
+                stacked[b, :c] = p[name].reshape(c, width)
             out[name] = stacked[..., 0] if key in ("scales", "oris") else stacked
         out["num_keypoints" + side] = torch.tensor(counts, dtype=torch.int32, device=pairs[0]["keypoints" + side].device)
         sizes = []

@@ -429,3 +429,28 @@ def test_adaptive_batched_at_scale_vs_single():
         assert one["log_assignment"].shape == pred["log_assignment"][b].shape
         assert (one["log_assignment"] - pred["log_assignment"][b]).abs().max() < 1e-3
         assert (one["matches0"] == pred["matches0"][b:b + 1]).float().mean() > 0.995
+
+
+def test_forward_soak_random_lengths():
+    """Timing-dependent faults need more than one shape: ten padded batches with random sizes and valid counts (some
+    images with very few or no points); two pairs of each batch against the same pair run alone with the same padding
+    and counts (same condition, same arithmetic, one work item per CTA)."""
+    conf = {"filter_threshold": 0.1}
+    model = _model(conf, W.make_state_dict(conf, seed=0))
+    rng = np.random.default_rng(123)
+    for it in range(10):
+        B = int(rng.choice([6, 12, 20]))
+        m, n = int(rng.choice([640, 1024, 1536, 2048])), int(rng.choice([640, 1024, 1536, 2048]))
+        data = _cuda(W.make_inputs(B, m, n, seed=200 + it, correlated=0.7))
+        l0, l1 = rng.integers(m // 3, m + 1, B), rng.integers(n // 3, n + 1, B)
+        l0[rng.integers(B)] = int(rng.choice([0, 1, 5]))
+        l1[rng.integers(B)] = int(rng.choice([0, 1, 127]))
+        data["num_keypoints0"], data["num_keypoints1"] = torch.tensor(l0).cuda(), torch.tensor(l1).cuda()
+        pred = model(data)
+        la = pred["log_assignment"]
+        for b in (int(rng.integers(B)), B - 1):
+            one = model(_slice_pair(data, b))
+            fin = torch.isfinite(one["log_assignment"][0])
+            assert torch.equal(fin, torch.isfinite(la[b])), (it, b)
+            assert (one["log_assignment"][0][fin] - la[b][fin]).abs().max() < 1e-4, (it, b, B, m, n)
+            assert torch.equal(one["matches0"][0], pred["matches0"][b]), (it, b)
