@@ -6,3 +6,4 @@ HostPipeline = _p.HostPipeline
 RESULT_KEYS = _p.RESULT_KEYS
 pack_pairs = _p.pack_pairs
 unpack_pred = _p.unpack_pred
+group_by_length = _p.group_by_length

@@ -72,6 +72,15 @@ def pack_pairs(pairs, length0=None, length1=None, multiple=128):
     return out
 
 
+def group_by_length(pairs, group: int):
+    """Index groups of at most `group` pairs, pairs of similar size together (sorted by the larger keypoint count), so
+    that `pack_pairs` pads each group only to ITS longest pair: attention cost grows with the square of the padded
+    length.  Returns a list of index lists; results can be put back in order with the indices."""
+    order = sorted(range(len(pairs)), key=lambda i: max(int(pairs[i]["keypoints0"].shape[-2]),
+                                                        int(pairs[i]["keypoints1"].shape[-2])))
+    return [order[g:g + group] for g in range(0, len(order), group)]
+
+
 def unpack_pred(pred, batch):
     """Per-pair views of a batched prediction, cut to each pair's valid counts (the shapes the one-pair-per-call
     forward returns): list of dicts with `matches0/1`, `matching_scores0/1` (1, n_i) and, when present,

@@ -104,8 +104,21 @@ def exporter_loop(pairs_total=64, group=16, lo=1024, hi=2048):
             out += [d["matches0"] for d in P.unpack_pred(model(batch), batch)]
         return out
 
+    sorted_model = M.LightGlue({"filter_threshold": 0.1, "b200": {"condition": "valid", "engine_cache": 8}})
+    sorted_model.load_state_dict(W.make_state_dict(conf, seed=0))
+    sorted_model = sorted_model.cuda()
+
+    def packed_sorted():  # similar sizes together, each group padded to its own longest pair (multiple of 256)
+        out = [None] * pairs_total
+        for idx in P.group_by_length(pairs, group):
+            batch = P.pack_pairs([pairs[i] for i in idx], multiple=256)
+            for i, d in zip(idx, P.unpack_pred(sorted_model(batch), batch)):
+                out[i] = d["matches0"]
+        return out
+
     res = {}
-    for name, fn in (("one_pair_per_call", one_by_one), ("packed_groups_of_%d" % group, packed)):
+    for name, fn in (("one_pair_per_call", one_by_one), ("packed_groups_of_%d" % group, packed),
+                     ("packed_sorted_groups_of_%d" % group, packed_sorted)):
         for _ in range(2):
             got = fn()
         torch.cuda.synchronize()
@@ -116,8 +129,8 @@ def exporter_loop(pairs_total=64, group=16, lo=1024, hi=2048):
         torch.cuda.synchronize()
         res[name] = pairs_total / e0.elapsed_time(e1) * 1e3
         res.setdefault("_m", []).append(got)
-    a, b = res.pop("_m")
-    same = sum(int(torch.equal(x, y)) for x, y in zip(a, b))
+    a, b, c = res.pop("_m")
+    same = sum(int(torch.equal(x, y) and torch.equal(x, z)) for x, y, z in zip(a, b, c))
     print(json.dumps({"config": "exporter loop: %d single pairs, counts U{%d..%d} per image" % (pairs_total, lo, hi),
                       "pairs_per_s": res, "pairs_with_identical_matches0": "%d/%d" % (same, pairs_total)}))
 
