@@ -362,7 +362,7 @@ def run_b200(a):
     assign_bytes = a.batch * ((a.kpts + 1) ** 2 * 4 + 2 * a.kpts * 256 * 4)
     hbm_peak = float(peaks.get("hbm_gbs", 6500.0))
     assign_gbs = assign_bytes / (assign_ms / 1e3) / 1e9
-    roofline_assign = {"kernel": "assign_strip_kernel<1|2> + reduce + filter_finalize (final_proj and logits included)",
+    roofline_assign = {"kernel": "assign_strip_kernel<1> + reduce + assign_tmem_kernel<2> + filter_finalize (final_proj and logits included)",
                        "bound": "hbm", "achieved": assign_gbs, "peak": hbm_peak, "unit": "GB/s",
                        "frac": assign_gbs / hbm_peak, "ms": assign_ms, "algorithmic_bytes": assign_bytes,
                        "share_of_step": assign_ms / (ms / a.steps)}

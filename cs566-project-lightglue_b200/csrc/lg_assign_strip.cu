@@ -435,11 +435,13 @@ extern "C" int lg_assign_tiles(const void* a_tiles, const void* b_tiles, int tpa
   const int rt = (M + 127) / 128, ct = (N + 127) / 128;
   if (tpa < rt || tpb < ct) return LG_ERR_SHAPE;
   if ((reinterpret_cast<uintptr_t>(a_tiles) | reinterpret_cast<uintptr_t>(b_tiles)) & 15) return LG_ERR_ALIGN;
+  // LG_ASSIGN_IMPL: "tmem" = both passes of the TMEM-resident variant, "strip" = both passes of the strip kernels;
+  // default = strip pass 1 (128x128 SS tiles: the faster statistics pass) + TMEM pass 2 (the faster write pass)
   static const int use_tmem = [] {
     const char* e = getenv("LG_ASSIGN_IMPL");
-    return e && e[0] == 't' ? 1 : 0;
+    return !e ? 0 : e[0] == 't' ? 1 : e[0] == 's' ? 2 : 0;
   }();
-  if (use_tmem)
+  if (use_tmem == 1)
     return lg_assign_tiles_tmem(a_tiles, b_tiles, tpa, tpb, z0, z1, m_len, n_len, scale, scores, ws, keys_ws, B, M, N,
                                 stream);
   uint8_t* w = static_cast<uint8_t*>(ws);
@@ -484,6 +486,9 @@ extern "C" int lg_assign_tiles(const void* a_tiles, const void* b_tiles, int tpa
   lg::assign_strip_kernel<1><<<grid, lg::kStripThreads, lg::kStripSmem, stream>>>(p);
   lg::launch_assign_reduce(row_part, col_part, z0, z1, m_len, n_len, row_lse, col_lse, row_ls, col_ls, scores, B, M, N,
                            4 * rt, ct, stream);  // 4 column partials per row tile (one per epilogue warp)
+  if (use_tmem == 0)
+    return lg::launch_assign_tmem_pass2(a_tiles, b_tiles, tpa, tpb, m_len, n_len, row_lse, col_lse, row_ls, col_ls, scores,
+                                        rowkey, colkey, scale, B, M, N, stream);
   lg::assign_strip_kernel<2><<<grid, lg::kStripThreads, lg::kStripSmem, stream>>>(p);
   return static_cast<int>(cudaGetLastError());
 }

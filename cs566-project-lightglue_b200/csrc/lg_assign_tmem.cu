@@ -499,3 +499,33 @@ extern "C" int lg_assign_tiles_tmem(const void* a_tiles, const void* b_tiles, in
   lg::tm::assign_tmem_kernel<2><<<grid, lg::tm::kThreads, lg::tm::kSmem, stream>>>(p);
   return static_cast<int>(cudaGetLastError());
 }
+
+namespace lg {
+int launch_assign_tmem_pass2(const void* a_tiles, const void* b_tiles, int tpa, int tpb, const int* m_len,
+                             const int* n_len, const float* row_lse, const float* col_lse, const float* row_ls,
+                             const float* col_ls, float* scores, unsigned long long* rowkey,
+                             unsigned long long* colkey, float scale, int B, int M, int N, cudaStream_t stream) {
+  const int rt = (M + 127) / 128, ct64 = (N + 63) / 64;
+  static bool attr_done = false;
+  if (!attr_done) {
+    cudaError_t e = cudaFuncSetAttribute(tm::assign_tmem_kernel<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, tm::kSmem);
+    if (e != cudaSuccess) return static_cast<int>(e);
+    attr_done = true;
+  }
+  int sms = 0, dev = 0;
+  cudaGetDevice(&dev);
+  cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+  if (sms <= 0) sms = 148;
+  int cw = 16;
+  while (cw > 1 && static_cast<long long>(B) * rt * ((ct64 + cw - 1) / cw) < 4LL * sms) cw >>= 1;
+  const int chunks = (ct64 + cw - 1) / cw;
+  const long long items = static_cast<long long>(B) * rt * chunks;
+  if (items > 0x7fffffffLL) return LG_ERR_SHAPE;
+  const int grid = items < sms ? static_cast<int>(items) : sms;
+  tm::Params p{static_cast<const uint8_t*>(a_tiles), static_cast<const uint8_t*>(b_tiles), tpa, tpb, m_len, n_len,
+               nullptr, nullptr, const_cast<float*>(row_lse), const_cast<float*>(col_lse), const_cast<float*>(row_ls),
+               const_cast<float*>(col_ls), scores, rowkey, colkey, scale, B, M, N, rt, ct64, cw, chunks};
+  tm::assign_tmem_kernel<2><<<grid, tm::kThreads, tm::kSmem, stream>>>(p);
+  return static_cast<int>(cudaGetLastError());
+}
+}  // namespace lg

@@ -493,3 +493,17 @@ def test_gemm_f32_strided_batches_and_bounds(C):
         want = A[b, :, :kk].double() @ Bk[b, :kk].double()
         assert (out[b, :, :N].double() - want).abs().max() < 1e-4
     assert _guards_intact(raw, gz)
+
+
+def test_assign_tiles_pure_strip_variant_in_subprocess():
+    """The default lg_assign_tiles mixes strip pass 1 with TMEM pass 2; LG_ASSIGN_IMPL=strip (read once per process) keeps
+    both strip passes reachable: same accuracy script, keys == scan."""
+    import os, subprocess, sys
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    env = dict(os.environ, LG_ASSIGN_IMPL="strip")
+    r = subprocess.run([sys.executable, os.path.join(root, "scripts", "exp_assign_tiles.py")], env=env, capture_output=True,
+                       text=True, timeout=300)
+    assert r.returncode == 0, r.stderr[-400:]
+    assert "keys == scan: True" in r.stdout
+    errs = [float(l.split("|strip - f64| =")[1].split()[0]) for l in r.stdout.splitlines() if "|strip - f64|" in l]
+    assert len(errs) == 5 and max(errs) < 3e-4
