@@ -108,3 +108,14 @@ def test_condition_option_validated():
     with pytest.raises(ValueError):
         M.LightGlue({"b200": {"condition": "per-image"}})
     assert M.LightGlue({}).conf.b200.condition == "padded"
+
+
+def test_b200glue_pipeline_reexports():
+    import importlib
+    mod = importlib.import_module("b200glue.pipeline")
+    P = pkg("pipeline")
+    for name in ("HostPipeline", "pack_pairs", "unpack_pred", "group_by_length", "RESULT_KEYS"):
+        assert getattr(mod, name) is getattr(P, name)
+    pairs = [{"keypoints0": torch.zeros(1, a, 2), "keypoints1": torch.zeros(1, b, 2)} for a, b in [(5, 9), (100, 3), (7, 7)]]
+    groups = P.group_by_length(pairs, 2)
+    assert sorted(i for g in groups for i in g) == [0, 1, 2] and groups[0] == [2, 0]
