@@ -454,3 +454,23 @@ def test_forward_soak_random_lengths():
             assert torch.equal(fin, torch.isfinite(la[b])), (it, b)
             assert (one["log_assignment"][0][fin] - la[b][fin]).abs().max() < 1e-4, (it, b, B, m, n)
             assert torch.equal(one["matches0"][0], pred["matches0"][b]), (it, b)
+
+
+def test_adaptive_batched_varlen_at_scale():
+    """Adaptive depth + width AND per-image valid counts on 12 pairs padded to 2048: pairs 0, 5, 11 against the same
+    pair run alone with the same padding and counts."""
+    conf = {"filter_threshold": 0.1, "depth_confidence": 0.95, "width_confidence": 0.95}
+    sd = W.make_state_dict(conf, seed=0, adaptive_fixture=True)
+    data = _cuda(W.make_inputs(12, 2048, 2048, seed=6, correlated=0.7))
+    rng = np.random.default_rng(5)
+    l0, l1 = rng.integers(700, 2049, 12), rng.integers(700, 2049, 12)
+    data["num_keypoints0"], data["num_keypoints1"] = torch.tensor(l0).cuda(), torch.tensor(l1).cuda()
+    model = _model(conf, sd)
+    pred = model(data)
+    for b in (0, 5, 11):
+        one = model(_slice_pair(data, b))
+        assert one["exit_layer"].tolist() == pred["exit_layer"][b:b + 1].tolist()
+        assert torch.equal(one["prune0"], pred["prune0"][b:b + 1]) and torch.equal(one["prune1"], pred["prune1"][b:b + 1])
+        assert one["log_assignment"][0].shape == pred["log_assignment"][b].shape
+        assert (one["matches0"] == pred["matches0"][b:b + 1]).float().mean() > 0.995
+        assert (pred["matches0"][b, int(l0[b]):] == -1).all()
