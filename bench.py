@@ -306,7 +306,15 @@ def run_b200(a):
                      for k, v in data.items()})
         check_err = max(check_err, float((one["log_assignment"][0] - la_batch[b]).abs().max()))
         check_same = check_same and bool(torch.equal(one["matches0"][0], pred["matches0"][b]))
-    check = {"max_abs_diff_log_assignment_vs_one_pair_calls": check_err, "matches0_identical": check_same}
+    # and the e2e path: what HostPipeline hands back for the same host batch (copies on side streams, graph replays)
+    pipe_same = True
+    for got in pipe.run(host for _ in range(3)):
+        pipe_same = pipe_same and bool(torch.equal(got["matches0"], pred["matches0"].cpu())) and \
+            bool(torch.equal(got["matching_scores0"], pred["matching_scores0"].cpu()))
+    check = {"max_abs_diff_log_assignment_vs_one_pair_calls": check_err, "matches0_identical": check_same,
+             "host_pipeline_identical": pipe_same}
+    if not pipe_same:
+        raise RuntimeError("bench self-check failed: HostPipeline results differ from the direct call")
     if check_err > 1e-3:
         raise RuntimeError(f"bench self-check failed: batched forward differs from one-pair calls by {check_err}")
 
