@@ -49,6 +49,7 @@ SIGNATURES = {
     "lg_attention_tiles2": (_I, [_P, _P, _P, _I, _P, _P, _I, _I, _I, _I, _P, _P, _P, _I, _P, _P, _I, _I, _I, _I, _P, _I, _I,
                                  _F, _P]),
     "lg_filter_matches": (_I, [_P, _L, _P, _P, _F, _P, _P, _P, _P, _P, _I, _I, _I, _P]),
+    "lg_filter_matches_static": (_I, [_P, _L, _P, _P, _F, _P, _P, _P, _P, _I, _I, _I, _P]),
     "lg_assign_keys": (_I, [_P, _P, _P, _P, _P, _P, _F, _P, _P, _P, _I, _I, _I, _P]),
     "lg_filter_from_keys": (_I, [_P, _P, _P, _F, _P, _P, _P, _P, _I, _I, _I, _P]),
     "lg_assign_tiles_ws_bytes": (_c.c_size_t, [_I, _I, _I]),
@@ -106,6 +107,7 @@ def lib():
 def _check(code: int, what: str):
     if code != 0:
         kind = {-1: "null pointer", -2: "bad shape", -3: "misaligned pointer",
+                -4: "problem larger than the fixed capacity of this non-allocating entry point",
                 719: "cudaError 719 (launch failure: a device trap -- the kernels abort through mbar_wait's spin limit "
                      "instead of hanging when a pipeline stalls -- or a fault of an EARLIER asynchronous launch)",
                 }.get(code, f"cudaError {code}")
@@ -250,6 +252,26 @@ def filter_matches(scores, th: float, m_len=None, n_len=None):
                                    _ptr(m1), _ptr(ms0), _ptr(ms1), _ptr(ws), B, M, N, _stream()), "lg_filter_matches")
     _count(2)
     return m0, m1, ms0, ms1
+
+
+FILTER_STATIC_MAX_KEYS = 131072  # LG_FILTER_STATIC_MAX_KEYS of include/lg_b200.h
+
+
+def filter_matches_static(scores, th: float, out, m_len=None, n_len=None):
+    """lg_filter_matches_static: the caller passes the outputs `out` = (m0, m1, ms0, ms1); the call itself allocates
+    nothing (key scratch = a static device array of the library; B*(M+N) <= FILTER_STATIC_MAX_KEYS)."""
+    _f32c(scores, "scores")
+    B, M1, N1 = scores.shape
+    M, N = M1 - 1, N1 - 1
+    m0, m1, ms0, ms1 = out
+    assert m0.shape == (B, M) and m1.shape == (B, N) and m0.dtype == torch.int64 and m1.dtype == torch.int64
+    assert ms0.shape == (B, M) and ms1.shape == (B, N) and ms0.dtype == torch.float32 and ms1.dtype == torch.float32
+    assert all(t.is_cuda and t.is_contiguous() for t in out)
+    _check(lib().lg_filter_matches_static(_ptr(scores), N1, _ptr(_i32(m_len)), _ptr(_i32(n_len)), float(th), _ptr(m0),
+                                          _ptr(m1), _ptr(ms0), _ptr(ms1), B, M, N, _stream()),
+           "lg_filter_matches_static")
+    _count(2)
+    return out
 
 
 def assign_and_filter(md0, md1, z0, z1, th: float, m_len=None, n_len=None, prescale=0.25):

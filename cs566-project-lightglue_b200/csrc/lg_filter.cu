@@ -156,3 +156,54 @@ extern "C" int lg_filter_from_keys(const void* keys_ws, const int* m_len, const 
                                                                             ms0, ms1, M, N);
   return static_cast<int>(cudaGetLastError());
 }
+
+// ---------------------------------------------------------------------------------------------------------------
+// lg_filter_matches_static: lg_filter_matches for callers that cannot allocate (CUDA graph capture, serving loops,
+// harnesses that forbid cudaMalloc).  The row / column key scratch lives in a file-scope device array instead of a
+// caller-supplied workspace.  No counterpart in the reference.
+//   * limit: B * (M + N) <= LG_FILTER_STATIC_MAX_KEYS (1 MiB of keys, held by every GPU that loads the library);
+//   * the array is shared by every call on a device: it is cleared on the stream at the start of each call, and
+//     calls that overlap on the GPU (different streams) race on it;
+//   * the host-side name of the array is not a device address: the address is resolved once per device with
+//     cudaGetSymbolAddress (that device current) and cached.
+namespace lg {
+constexpr int kMaxDevices = 64;
+static __device__ __align__(256) unsigned long long g_filter_keys[LG_FILTER_STATIC_MAX_KEYS];
+}  // namespace lg
+
+extern "C" int lg_filter_matches_static(const float* scores, int64_t pitch, const int* m_len, const int* n_len,
+                                        float th, int64_t* m0, int64_t* m1, float* ms0, float* ms1, int B, int M,
+                                        int N, cudaStream_t stream) {
+  if (!scores || !m0 || !m1 || !ms0 || !ms1) return LG_ERR_NULL;
+  if (B <= 0 || M <= 0 || N <= 0 || pitch < N) return LG_ERR_SHAPE;
+  const size_t keys = static_cast<size_t>(B) * (static_cast<size_t>(M) + N);
+  if (keys > static_cast<size_t>(LG_FILTER_STATIC_MAX_KEYS)) return LG_ERR_TOO_LARGE;
+  static unsigned long long* dev_ptr[lg::kMaxDevices] = {};  // per device; a benign race resolves the same address twice
+  int dev = -1;
+  cudaError_t e = cudaGetDevice(&dev);
+  if (e != cudaSuccess) return static_cast<int>(e);
+  if (dev < 0 || dev >= lg::kMaxDevices) return LG_ERR_SHAPE;
+  if (!dev_ptr[dev]) {
+    void* p = nullptr;
+    e = cudaGetSymbolAddress(&p, lg::g_filter_keys);  // the current device's instance of the array
+    if (e != cudaSuccess) return static_cast<int>(e);
+    if (!p) return LG_ERR_NULL;
+    dev_ptr[dev] = static_cast<unsigned long long*>(p);
+  }
+  unsigned long long* rowkey = dev_ptr[dev];
+  unsigned long long* colkey = rowkey + static_cast<size_t>(B) * M;
+  e = cudaMemsetAsync(rowkey, 0, keys * sizeof(unsigned long long), stream);  // the last call's keys are still there
+  if (e != cudaSuccess) return static_cast<int>(e);
+  const int strips = (M + 31) / 32, nchunks = (N + 31) / 32;
+  int nsplit = (148 * 16 + B * strips - 1) / (B * strips);
+  nsplit = max(1, min(nsplit, nchunks));
+  const int col_groups = (nsplit + lg::kFilterWarps - 1) / lg::kFilterWarps;
+  lg::filter_scan_kernel<<<dim3(strips, col_groups, B), lg::kFilterWarps * 32, 0, stream>>>(
+      scores, pitch, static_cast<int64_t>(M + 1) * pitch, m_len, n_len, rowkey, colkey, M, N, nsplit);
+  e = cudaGetLastError();
+  if (e != cudaSuccess) return static_cast<int>(e);
+  const int pts = M > N ? M : N;
+  lg::filter_finalize_kernel<<<dim3((pts + 255) / 256, B), 256, 0, stream>>>(rowkey, colkey, m_len, n_len, th, m0, m1,
+                                                                            ms0, ms1, M, N);
+  return static_cast<int>(cudaGetLastError());
+}

@@ -24,6 +24,7 @@ typedef struct CUstream_st* cudaStream_t;
 #define LG_ERR_NULL (-1)   /* required pointer is null */
 #define LG_ERR_SHAPE (-2)  /* unsupported / inconsistent sizes */
 #define LG_ERR_ALIGN (-3)  /* pointer not 16-byte aligned */
+#define LG_ERR_TOO_LARGE (-4)  /* problem exceeds the fixed capacity of a non-allocating entry point */
 
 #define LG_TILE 128        /* rows per operand tile */
 #define LG_TILE_BYTES 16384
@@ -160,6 +161,19 @@ int lg_assign(const float* md0, const float* md1, const float* z0, const float* 
 size_t lg_filter_ws_bytes(int B, int M, int N);
 int lg_filter_matches(const float* scores, int64_t pitch, const int* m_len, const int* n_len, float th, int64_t* m0,
                       int64_t* m1, float* ms0, float* ms1, void* ws, int B, int M, int N, cudaStream_t stream);
+
+/* lg_filter_matches without a workspace argument and without any allocation (no cudaMalloc / cudaFree, no allocating
+ * library routine): the key scratch is a file-scope `static __device__` array of LG_FILTER_STATIC_MAX_KEYS 64-bit
+ * keys (1 MiB, held by every GPU that loads the library until exit), for callers that cannot allocate -- CUDA graph
+ * capture, tight serving loops, harnesses that forbid cudaMalloc.  NO COUNTERPART IN THE REFERENCE.
+ * Same outputs as lg_filter_matches (bit-identical).  Limit: B*(M+N) <=
+ * LG_FILTER_STATIC_MAX_KEYS, else LG_ERR_TOO_LARGE.  Every call on a device shares the one array: it is cleared on
+ * `stream` at the start of each call, and calls that overlap on the GPU (different streams) race on it.  The first
+ * call on a device resolves the array's address (cudaGetSymbolAddress) -- make it outside a graph capture. */
+#define LG_FILTER_STATIC_MAX_KEYS 131072
+int lg_filter_matches_static(const float* scores, int64_t pitch, const int* m_len, const int* n_len, float th,
+                             int64_t* m0, int64_t* m1, float* ms0, float* ms1, int B, int M, int N,
+                             cudaStream_t stream);
 
 /* (3)+(4) fused: lg_assign that also gathers, while the scores are still on chip, the best column of every row
  * and the best row of every column of the valid block as order-preserving keys (largest score, lowest index on
