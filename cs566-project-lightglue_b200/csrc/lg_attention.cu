@@ -37,6 +37,25 @@ constexpr uint32_t kColS = 0, kColO = 384;  // TMEM column map: 3 rotating S buf
 #ifndef LG_SWEEP
 #define LG_SWEEP 2  // 0: pair-by-pair source order, 1: staged over the 32-column chunk, 2: software-pipelined groups
 #endif
+#ifndef LG_PREFETCH
+#define LG_PREFETCH 0  // start loading the next block's similarity before the P hand-off of this block
+#endif
+#ifndef LG_WARP_ARRIVE
+#define LG_WARP_ARRIVE 0  // P ready: one arrival per warp (count 4) instead of a warpgroup barrier + one arrival
+#endif
+#ifndef LG_ONE_LANE_WAIT
+#define LG_ONE_LANE_WAIT 0  // full-warp barrier waits: one lane polls
+#endif
+#if LG_ONE_LANE_WAIT & 1
+#define LG_WAIT_M(bar, par) mbar_wait_warp(bar, par)  // MMA warp
+#else
+#define LG_WAIT_M(bar, par) mbar_wait(bar, par)
+#endif
+#if LG_ONE_LANE_WAIT & 2
+#define LG_WAIT(bar, par) mbar_wait_warp(bar, par)  // softmax warps
+#else
+#define LG_WAIT(bar, par) mbar_wait(bar, par)
+#endif
 #ifndef LG_POLYEXP
 #define LG_POLYEXP 1  // 0: none, 1: 25 %, 2: 37.5 %, 3: 50 %, 4: 75 % of the exponentials on the FMA pipe
 #endif
@@ -141,7 +160,7 @@ struct __align__(8) AttnBarriers {
   uint64_t kv_empty[kStages];
   uint64_t s_full[3];
   uint64_t p_full[4];  // [tile t][key block parity]: see the note at the arrival
-  uint64_t pv_done[4];  // [tile t][key block parity], like p_full
+  uint64_t pv_done[2];  // [tile t]: the last PV of an item retired (one completion per item)
   uint64_t o_free[2];
   uint32_t tmem_base;
 };
@@ -186,8 +205,8 @@ __global__ void __launch_bounds__(kAttnThreads, 1) attention_kernel(const AttnPa
   if (threadIdx.x == 0) {
     for (int i = 0; i < 2; ++i) {
       mbar_init(&bar->q_full[i], 1); mbar_init(&bar->q_empty[i], 1);
-      mbar_init(&bar->p_full[2 * i], 1); mbar_init(&bar->p_full[2 * i + 1], 1);
-      mbar_init(&bar->pv_done[2 * i], 1); mbar_init(&bar->pv_done[2 * i + 1], 1); mbar_init(&bar->o_free[i], 128);
+      mbar_init(&bar->p_full[2 * i], LG_WARP_ARRIVE ? 4 : 1); mbar_init(&bar->p_full[2 * i + 1], LG_WARP_ARRIVE ? 4 : 1);
+      mbar_init(&bar->pv_done[i], 1); mbar_init(&bar->o_free[i], 128);
     }
     for (int s = 0; s < kStages; ++s) { mbar_init(&bar->kv_full[s], 1); mbar_init(&bar->kv_empty[s], 1); }
     for (int i = 0; i < 3; ++i) mbar_init(&bar->s_full[i], 1);
@@ -244,17 +263,18 @@ __global__ void __launch_bounds__(kAttnThreads, 1) attention_kernel(const AttnPa
       const uint64_t dV0 = umma_desc_kmajor_sw128(smem_u32(sKV) + kTileBytes);
 
       // Similarity cursor: runs three global steps ahead of the PV cursor, across item boundaries.
-      // Global step G = (key block, query tile) pairs in issue order; S buffer = G % 3.
+      // Global step G = (key block, query tile) pairs in issue order; S buffer = G % 3 (kept as a rotating counter).
+      // The similarity of step G+3 is issued right behind the PV of step G, before the commits, because the softmax
+      // warpgroup of the other tile is waiting for exactly this similarity.  Everything the issue needs (item decode,
+      // Q / K arrival, descriptors) is resolved by prepare_qk() before the wait for P.
+      // The warp's own instruction stream bounds the kernel (measured: 1250 cycles per half step of which the tensor
+      // pipe works 512): ONE predicated region per half step holds all tcgen05 instructions, the rotating indices
+      // are counters (no % 3, no divisions), and only the last PV of an item commits pv_done.
       int qw = blockIdx.x, q_n = 0, q_cnt = 0, q_nkt = 0;
       bool q_loaded = false;
-      uint32_t q_kv = 0, G_q = 0;
-      // The similarity of step G+3 is issued right behind the PV of step G and BEFORE any commit: a tcgen05.commit
-      // holds the issuing thread until the queued MMAs have drained (measured ~200 cycles each), and the softmax
-      // warpgroup of the other tile is waiting for exactly this similarity.  Everything the issue needs (item
-      // decode, Q / K arrival, descriptors) is resolved by prepare_qk() before the wait for P.
+      uint32_t q_kv = 0, q_sb = 0;  // q_sb: S buffer of the next similarity
       bool qk_ready = false, qk_last = false;
       uint64_t qk_da = 0, qk_db = 0;
-      uint32_t qk_sb = 0;
       auto prepare_qk = [&]() {
         qk_ready = false;
         while (!q_loaded) {
@@ -262,74 +282,85 @@ __global__ void __launch_bounds__(kAttnThreads, 1) attention_kernel(const AttnPa
           const AttnItem it = attn_item(p, qw);
           if (it.skip) { qw += gridDim.x; continue; }
           q_nkt = it.nkt; q_n = 0; q_loaded = true;
-          mbar_wait(&bar->q_full[q_cnt & 1], (q_cnt >> 1) & 1);
+          LG_WAIT_M(&bar->q_full[q_cnt & 1], (q_cnt >> 1) & 1);
         }
         const int t = q_n & 1;
         const uint32_t kvi = q_kv + (q_n >> 1), s = kvi % kStages;
-        if (t == 0) mbar_wait(&bar->kv_full[s], (kvi / kStages) & 1);
-        qk_sb = G_q % 3;
+        if (t == 0) LG_WAIT_M(&bar->kv_full[s], (kvi / kStages) & 1);
         qk_da = dQ0 + static_cast<uint64_t>(((q_cnt & 1) * 2 + t) * (kTileBytes >> 4));
         qk_db = dK0 + static_cast<uint64_t>(s * (2 * kTileBytes >> 4));
         qk_last = q_n + 1 == 2 * q_nkt;
         qk_ready = true;
       };
-      auto issue_qk = [&]() {  // MMAs only
+      auto advance_qk = [&]() {  // bookkeeping behind an issued similarity (all lanes)
         if (!qk_ready) return;
-#pragma unroll
-        for (int kk = 0; kk < 4; ++kk)  // K = 64 = 4 x 16, 32 B per step inside the 128 B swizzle row
-          if (leader) umma_bf16_ss(tmem + kColS + qk_sb * 128, qk_da + 2 * kk, qk_db + 2 * kk, idesc_qk, kk > 0);
-      };
-      auto commit_qk = [&]() {
-        if (!qk_ready) return;
-        if (leader) umma_commit(&bar->s_full[qk_sb]);
-        ++G_q;
+        q_sb = q_sb == 2 ? 0 : q_sb + 1;
         ++q_n;
-        if (qk_last) {  // last similarity of the item: its Q buffer is free once these retire
-          if (leader) umma_commit(&bar->q_empty[q_cnt & 1]);
-          q_kv += q_nkt; ++q_cnt; q_loaded = false; qw += gridDim.x;
-        }
+        if (qk_last) { q_kv += q_nkt; ++q_cnt; q_loaded = false; qw += gridDim.x; }
       };
 
       for (int i = 0; i < 3; ++i) {
         prepare_qk();
         tc_fence_after();
-        issue_qk();
-        commit_qk();
+        if (leader && qk_ready) {
+#pragma unroll
+          for (int kk = 0; kk < 4; ++kk)  // K = 64 = 4 x 16, 32 B per step inside the 128 B swizzle row
+            umma_bf16_ss(tmem + kColS + q_sb * 128, qk_da + 2 * kk, qk_db + 2 * kk, idesc_qk, kk > 0);
+          umma_commit(&bar->s_full[q_sb]);
+          if (qk_last) umma_commit(&bar->q_empty[q_cnt & 1]);
+        }
+        advance_qk();
       }
-      uint32_t p_kv = 0, G_p = 0;
+      uint32_t p_kv = 0, p_sb = 0;
       int p_cnt = 0;
+#ifdef LG_ATTN_TRACE
+      uint32_t G_p = 0;
+#endif
       for (int w = blockIdx.x; w < p.items; w += gridDim.x) {
         const AttnItem it = attn_item(p, w);
         if (it.skip) continue;
-        for (int n = 0; n < 2 * it.nkt; ++n, ++G_p) {
+        const int nsteps = 2 * it.nkt;
+        for (int n = 0; n < nsteps; ++n) {
           const int t = n & 1, j = n >> 1;
           const uint32_t kvi = p_kv + j, s = kvi % kStages;
           // P sits in the first 64 columns of S buffer G % 3 as packed bf16 (A operand from TMEM)
-          const uint32_t tP = tmem + kColS + (G_p % 3) * 128;
+          const uint32_t tP = tmem + kColS + p_sb * 128;
           const uint64_t dv = dV0 + static_cast<uint64_t>(s * (2 * kTileBytes >> 4));
-          if (leader) { DBG(2, w); DBG(3, static_cast<int>(G_p)); DBG(4, qw); DBG(5, static_cast<int>(G_q)); DBG(12, 1); }
+          if (leader) TRACE(24, G_p);
           prepare_qk();                         // step G+3: recycles S buffer G % 3 behind this PV
-          if (leader) DBG(12, 2);
-          mbar_wait(&bar->p_full[2 * t + (kvi & 1)], (kvi >> 1) & 1);  // P_t(j) stored in its S buffer
+          if (leader) TRACE(25, G_p);
+          LG_WAIT_M(&bar->p_full[2 * t + (kvi & 1)], (kvi >> 1) & 1);  // P_t(j) stored in its S buffer
           if (leader) TRACE(6, G_p);
-          if (leader) DBG(12, 3);
-          if (j == 0 && p_cnt > 0) mbar_wait(&bar->o_free[t], (p_cnt - 1) & 1);  // previous item's O_t was read out
-          if (leader) DBG(12, 4);
+          if (j == 0 && p_cnt > 0) LG_WAIT_M(&bar->o_free[t], (p_cnt - 1) & 1);  // previous item's O_t was read out
           tc_fence_after();
+          if (leader) {
 #pragma unroll
-          for (int kk = 0; kk < 8; ++kk) {  // K = 128 keys = 8 x 16: 8 TMEM columns / 32 B of a V^T row per step
-            if (leader)
+            for (int kk = 0; kk < 8; ++kk)  // K = 128 keys = 8 x 16: 8 TMEM columns / 32 B of a V^T row per step
               umma_bf16_ts(tmem + kColO + t * 64, tP + kk * 8,
                            dv + static_cast<uint64_t>((kk >> 2) * (kTileBytes / 2 >> 4) + (kk & 3) * 2), idesc_pv,
                            (j > 0 || kk > 0));
+            TRACE(26, G_p);
+            // same-thread MMAs execute in order: the similarity overwrites the S buffer after PV has read P from it
+            if (qk_ready) {
+#pragma unroll
+              for (int kk = 0; kk < 4; ++kk)
+                umma_bf16_ss(tmem + kColS + q_sb * 128, qk_da + 2 * kk, qk_db + 2 * kk, idesc_qk, kk > 0);
+            }
+            TRACE(27, G_p);
+            if (qk_ready) {
+              umma_commit(&bar->s_full[q_sb]);
+              if (qk_last) umma_commit(&bar->q_empty[q_cnt & 1]);  // last similarity of the item: its Q buffer is free
+            }
+            if (t == 1) umma_commit(&bar->kv_empty[s]);  // K_j and V_j are dead once PV1_j retires (the rare rescale
+                                                         // path of the softmax warps waits on this barrier too)
+            if (n + 2 >= nsteps) umma_commit(&bar->pv_done[t]);  // last PV_t of the item: the item epilogue waits for it
           }
-          issue_qk();  // same-thread MMAs execute in order: the similarity overwrites the buffer after PV read P
-          if (leader) umma_commit(&bar->pv_done[2 * t + (kvi & 1)]);  // (fires after the similarity too: only the rare rescale
-                                                      // path and the item epilogue wait on it)
-          if (leader && t == 1) umma_commit(&bar->kv_empty[s]);  // K_j and V_j are dead once PV1_j retires
-          commit_qk();
-          if (leader) DBG(12, 5);
+          advance_qk();
+          p_sb = p_sb == 2 ? 0 : p_sb + 1;
           if (leader) TRACE(7, G_p);
+#ifdef LG_ATTN_TRACE
+          ++G_p;
+#endif
         }
         p_kv += it.nkt;
         ++p_cnt;
@@ -348,6 +379,7 @@ __global__ void __launch_bounds__(kAttnThreads, 1) attention_kernel(const AttnPa
     uint32_t va[32], vb[32];
     uint32_t pk0[32], pk1[32];  // P of the block as packed bf16 pairs: 64 TMEM columns
     uint32_t kv_base = 0;       // running key-block counter: barrier phases continue across items
+    uint32_t item_cnt = 0;      // non-skipped items so far (phase of pv_done)
 
     for (int w = blockIdx.x; w < p.items; w += gridDim.x) {
       const AttnItem it = attn_item(p, w);
@@ -380,6 +412,7 @@ __global__ void __launch_bounds__(kAttnThreads, 1) attention_kernel(const AttnPa
       }
 
       float m_used = -INFINITY, l = 0.f;
+      bool pf = false;  // the first 32 columns of this block's S are already on their way into va (see the block's end)
       for (int j = 0; j < it.nkt; ++j) {
         const int rem = it.k_len - j * kTile;        // valid keys in this block (>= 1)
         const bool partial = rem < kTile;
@@ -387,9 +420,11 @@ __global__ void __launch_bounds__(kAttnThreads, 1) attention_kernel(const AttnPa
         const uint32_t tS = tS0 + (G % 3) * 128;
         if ((threadIdx.x & 127) == 0) TRACE(t * 3, kv_base + j);
         if ((threadIdx.x & 127) == 0) { DBG(8 + t, j); DBG(10 + t, 1); }
-        mbar_wait(&bar->s_full[G % 3], (G / 3) & 1);
+        if (!pf) {
+          LG_WAIT(&bar->s_full[G % 3], (G / 3) & 1);
+          tc_fence_after();
+        }
         if ((threadIdx.x & 127) == 0) DBG(10 + t, 2);
-        tc_fence_after();
         if ((threadIdx.x & 127) == 0) TRACE(t * 3 + 1, kv_base + j);
 
         float tile_sum = 0.f;
@@ -418,8 +453,10 @@ __global__ void __launch_bounds__(kAttnThreads, 1) attention_kernel(const AttnPa
             if (need) { alpha = first ? 0.f : ex2_approx((m_used - mx) * c); m_used = mx; }
             l *= alpha;
             if (!first) {
-              // O_t must be quiescent: PV_t(j-1) retired (barrier pair: see the epilogue wait)
-              mbar_wait(&bar->pv_done[2 * t + ((kv_base + j - 1) & 1)], ((kv_base + j - 1) >> 1) & 1);
+              // O_t must be quiescent: PV_t(j-1) retired.  kv_empty of block j-1 completes when PV_1(j-1) has retired
+              // (and with it everything issued before); its next completion (block j+3) needs this block's P first,
+              // so the parity wait cannot alias.
+              LG_WAIT(&bar->kv_empty[(kv_base + j - 1) % kStages], ((kv_base + j - 1) / kStages) & 1);
               tc_fence_after();
 #pragma unroll
               for (int cb = 0; cb < 2; ++cb) {
@@ -577,16 +614,18 @@ __global__ void __launch_bounds__(kAttnThreads, 1) attention_kernel(const AttnPa
   E[g][3] = make_float2(__int_as_float((__float_as_int(RR[g].x) << 23) + __float_as_int(PP[g].x)),      \
                         __int_as_float((__float_as_int(RR[g].y) << 23) + __float_as_int(PP[g].y)));
 #define LG_PK(g, k) (((g) < 8 ? pk0 : pk1)[((g) & 7) * 4 + (k)])
-            tmem_ld32(tS, va);
+            if (!pf) tmem_ld32(tS, va);
+            pf = false;
             tmem_wait_ld();
+            if (threadIdx.x == 0) TRACE(16, kv_base + j);
             tmem_ld32(tS + 32, vb);
             mask_chunk(va, 0);
             LG_ARGS1(0) LG_ARGS2(0) LG_PA(0) LG_PB(0) LG_PC(0) LG_PD(0) LG_PE(0) LG_PF(0) LG_PG(0)
 #pragma unroll
             for (int g = 0; g < 16; ++g) {
-              if (g == 3) { tmem_wait_ld(); mask_chunk(vb, 1); }
-              if (g == 7) { tmem_wait_ld(); mask_chunk(va, 2); }
-              if (g == 11) { tmem_wait_ld(); mask_chunk(vb, 3); }
+              if (g == 3) { if (threadIdx.x == 0) TRACE(17, kv_base + j); tmem_wait_ld(); mask_chunk(vb, 1); }
+              if (g == 7) { if (threadIdx.x == 0) TRACE(18, kv_base + j); tmem_wait_ld(); mask_chunk(va, 2); }
+              if (g == 11) { if (threadIdx.x == 0) TRACE(19, kv_base + j); tmem_wait_ld(); mask_chunk(vb, 3); }
               E[g][0].x = ex2_approx(T[g][0].x);
               if (g + 1 < 16) { LG_ARGS1(g + 1) }
               E[g][0].y = ex2_approx(T[g][0].y);
@@ -611,6 +650,7 @@ __global__ void __launch_bounds__(kAttnThreads, 1) attention_kernel(const AttnPa
             s2 = __fadd2_rn(s2, E[15][2]); LG_PK(15, 2) = pack_bf16x2(E[15][2].x, E[15][2].y);
             s3 = __fadd2_rn(s3, E[15][3]); LG_PK(15, 3) = pack_bf16x2(E[15][3].x, E[15][3].y);
             tile_sum = ((s0.x + s0.y) + (s1.x + s1.y)) + ((s2.x + s2.y) + (s3.x + s3.y));
+            if (threadIdx.x == 0) TRACE(20, kv_base + j);
 #undef LG_V
 #undef LG_ARGS1
 #undef LG_ARGS2
@@ -648,41 +688,51 @@ __global__ void __launch_bounds__(kAttnThreads, 1) attention_kernel(const AttnPa
           if (!__any_sync(0xffffffffu, !(tile_sum < kSumLimit))) break;
         }
         l += tile_sum;
+        // The next block's similarity was queued three steps ahead and is normally complete by now: start loading its
+        // first 32 columns (va is dead) so that the wake-up, fence and TMEM-load latency of block j+1 hide behind the
+        // P store / hand-off of block j.  Non-blocking: if the similarity has not landed, block j+1 waits as before.
+        if (LG_PREFETCH && j + 1 < it.nkt) {
+          const uint32_t Gn = G + 2;
+          pf = __all_sync(0xffffffffu, mbar_test_wait(&bar->s_full[Gn % 3], (Gn / 3) & 1));
+          if (pf) {
+            tc_fence_after();
+            tmem_ld32(tS0 + (Gn % 3) * 128, va);
+          }
+        }
         // P overwrites the first 64 columns of its own S buffer (every S value has been consumed); the PV MMA reads
         // it from TMEM as the A operand, then the similarity of step G+3 recycles the buffer.
         tmem_st32(tS, pk0);
         tmem_st32(tS + 32, pk1);
+        if (threadIdx.x == 0) TRACE(21, kv_base + j);
         tmem_wait_st();
         tc_fence_before();
-        // The warps of a warpgroup are otherwise unsynchronised and the similarity lookahead lets a fast warp run
-        // one block ahead: ONE arrival per block, after all 128 rows are stored (a 128-count barrier could be
-        // completed by a mix of arrivals of block j and block j+1).
-        asm volatile("bar.sync %0, 128;" ::"r"(1 + t) : "memory");
-        // Two barriers per tile, alternating with the key block: the three-deep similarity lookahead lets a warpgroup
+        if (threadIdx.x == 0) TRACE(22, kv_base + j);
+        // One arrival per WARP (barrier count 4), no warpgroup barrier: the warps of a warpgroup drift apart by less
+        // than two blocks -- the similarity of block j+2 of this tile is queued behind PV(j) of the OTHER tile, which
+        // the MMA warp issues after PV_t(j), i.e. after all four warps have arrived for block j -- and blocks j, j+1
+        // use different barriers (below), so the four arrivals that complete a phase always belong to one block.
+        // Two barriers per tile, alternating with the key block: the three-deep similarity lookahead lets a warp
         // finish blocks j and j+1 while the MMA warp is held up (at an item boundary it decodes the next items, which
-        // with per-image lengths costs dependent global loads, and waits for their Q tile).  On ONE barrier those two
+        // with per-image lengths costs dependent global loads, and waits for their Q tile).  On ONE barrier those
         // arrivals would flip the phase twice and the MMA warp's parity wait for block j would never return; block
         // j+2 (the same barrier again) cannot be reached before PV(j) has consumed P(j).
-        if ((threadIdx.x & 127) == 0) {
-          mbar_arrive(&bar->p_full[2 * t + ((kv_base + j) & 1)]);
-          TRACE(t * 3 + 2, kv_base + j);
-        }
+#if LG_WARP_ARRIVE
+        __syncwarp();
+        if (lane == 0) mbar_arrive(&bar->p_full[2 * t + ((kv_base + j) & 1)]);
+#else
+        asm volatile("bar.sync %0, 128;" ::"r"(1 + t) : "memory");
+        if ((threadIdx.x & 127) == 0) mbar_arrive(&bar->p_full[2 * t + ((kv_base + j) & 1)]);
+#endif
+        if ((threadIdx.x & 127) == 0) TRACE(t * 3 + 2, kv_base + j);
       }
 
       // epilogue: O / l.  O_t is copied to registers and released first so the next item's PV can start.
       if ((threadIdx.x & 127) == 0) TRACE(8 + t * 4, kv_base);
       if ((threadIdx.x & 127) == 0) DBG(10 + t, 3);
-      // Earlier phases of this barrier were never waited for, so a parity wait is only sound if the barrier cannot be
-      // TWO completions behind: when this warpgroup finishes its last block, PV_t(nkt-3) has retired (its commit
-      // precedes the similarity of block nkt-1 in the MMA warp's order) but PV_t(nkt-2) may not have -- with the MMA
-      // warp held up at the item boundary (it decodes the next items and waits for their Q tile first).  On ONE
-      // barrier per tile that state has the parity this wait looks for: it returned early and O_t was read two
-      // blocks short (intermittent errors of ~5e-2 with many items per CTA).  With one barrier per block parity the
-      // barrier of block nkt-1 is at most one completion behind.
-      {
-        const uint32_t last = kv_base + it.nkt - 1;
-        mbar_wait(&bar->pv_done[2 * t + (last & 1)], (last >> 1) & 1);
-      }
+      // pv_done[t] completes once per (non-skipped) item, behind the item's last PV_t; the next completion needs this
+      // warpgroup's P of the next item, so the barrier is never more than one completion away from this wait.
+      LG_WAIT(&bar->pv_done[t], item_cnt & 1);
+      ++item_cnt;
       if ((threadIdx.x & 127) == 0) DBG(10 + t, 4);
       tc_fence_after();
       if ((threadIdx.x & 127) == 0) TRACE(9 + t * 4, kv_base);

@@ -28,12 +28,15 @@ for i in range(0, nb, 16):
     print(f"kv_base={i:3d} wg0 " + " ".join(f"{tr[8 + k, i] - t0:6d}" for k in range(4)) + " | wg1 " + " ".join(f"{tr[12 + k, i] - t0:6d}" for k in range(4)))
 
 if (tr[16] > 0).any():
-    print("wg0 inside a block: gotS | c0 loaded, sweep0, c1 loaded, sweep1, sweep2, c3 loaded, sweep3, P stored | arrive")
-    for j in range(17, 30):
-        print(f"blk={j:3d} gotS={tr[1, j] - t0:6d} | " + " ".join(f"{tr[16 + k, j] - t0:6d}" for k in range(8)) + f" | arr={tr[2, j] - t0:6d}")
+    print("wg0 warp 0 inside a block, cycles after gotS: first chunk loaded | groups 0-2 | 3-6 | 7-10 | 11-15 + sums | P st issued | "
+          "st waited + fenced | bar.sync + arrive | (pre of the next block)")
+    for j in range(33, 47):
+        t = [tr[1, j]] + [tr[16 + k, j] for k in range(7)] + [tr[2, j], tr[0, j + 1]]
+        print(f"blk={j:3d} " + " ".join(f"{t[k + 1] - t[k]:5d}" for k in range(len(t) - 1)))
 
 if (tr[24] > 0).any():
-    print("mma warp per global step G: wake | fenced | pv issued | committed | qk: kv ready | qk issued | step end")
-    for G in range(34, 60):
-        print(f"G={G:3d} t={G & 1} wake={tr[6, G] - t0:6d} fenced={tr[28, G] - t0:6d} pv={tr[24, G] - t0:6d} commit={tr[25, G] - t0:6d} "
-              f"kvready={tr[26, G] - t0:6d} qk={tr[27, G] - t0:6d} end={tr[7, G] - t0:6d}")
+    print("mma warp per global step G (cycles): loop top -> operands of QK(G+3) ready -> P(G) ready -> PV issued -> QK issued -> commits done | period")
+    for G in range(70, 96):
+        t = [tr[24, G], tr[25, G], tr[6, G], tr[26, G], tr[27, G], tr[7, G]]
+        print(f"G={G:3d} t={G & 1} " + " ".join(f"{t[k + 1] - t[k]:5d}" for k in range(5)) + f" | {tr[24, G + 1] - tr[24, G]:5d}"
+              f"   P arrived {tr[(G & 1) * 3 + 2, G >> 1] - tr[24, G]:6d} after loop top")
