@@ -47,7 +47,7 @@ constexpr uint32_t kColS = 0, kColO = 384;  // TMEM column map: 3 rotating S buf
 #define LG_ONE_LANE_WAIT 0  // full-warp barrier waits: one lane polls
 #endif
 #if LG_ONE_LANE_WAIT & 1
-#define LG_WAIT_M(bar, par) mbar_wait_warp(bar, par)  // MMA warp
+#define LG_WAIT_M(bar, par) mbar_wait_warp(bar, par)  // MMA warps (unused: deadlocks, see DESIGN)
 #else
 #define LG_WAIT_M(bar, par) mbar_wait(bar, par)
 #endif
@@ -55,6 +55,15 @@ constexpr uint32_t kColS = 0, kColO = 384;  // TMEM column map: 3 rotating S buf
 #define LG_WAIT(bar, par) mbar_wait_warp(bar, par)  // softmax warps
 #else
 #define LG_WAIT(bar, par) mbar_wait(bar, par)
+#endif
+#ifndef LG_POLY_PAIRS
+#define LG_POLY_PAIRS 2  // pairs of every 4 (8 columns) whose exp2 runs as a polynomial on the FMA pipe: 1 = 25 %, 2 = 50 %
+#endif
+#ifndef LG_STAGGER
+#define LG_STAGGER 0
+#endif
+#ifndef LG_ALTERNATE
+#define LG_ALTERNATE 0  // the two softmax warpgroups take turns: a block starts when the other tile's block is half done
 #endif
 #ifndef LG_POLYEXP
 #define LG_POLYEXP 1  // 0: none, 1: 25 %, 2: 37.5 %, 3: 50 %, 4: 75 % of the exponentials on the FMA pipe
@@ -161,6 +170,7 @@ struct __align__(8) AttnBarriers {
   uint64_t s_full[3];
   uint64_t p_full[4];  // [tile t][key block parity]: see the note at the arrival
   uint64_t pv_done[2];  // [tile t]: the last PV of an item retired (one completion per item)
+  uint64_t t0_free[2];  // [key block parity]: PV_0(j) retired, its S buffer may be overwritten
   uint64_t o_free[2];
   uint32_t tmem_base;
 };
@@ -206,7 +216,7 @@ __global__ void __launch_bounds__(kAttnThreads, 1) attention_kernel(const AttnPa
     for (int i = 0; i < 2; ++i) {
       mbar_init(&bar->q_full[i], 1); mbar_init(&bar->q_empty[i], 1);
       mbar_init(&bar->p_full[2 * i], LG_WARP_ARRIVE ? 4 : 1); mbar_init(&bar->p_full[2 * i + 1], LG_WARP_ARRIVE ? 4 : 1);
-      mbar_init(&bar->pv_done[i], 1); mbar_init(&bar->o_free[i], 128);
+      mbar_init(&bar->pv_done[i], 1); mbar_init(&bar->t0_free[i], 1); mbar_init(&bar->o_free[i], 128);
     }
     for (int s = 0; s < kStages; ++s) { mbar_init(&bar->kv_full[s], 1); mbar_init(&bar->kv_empty[s], 1); }
     for (int i = 0; i < 3; ++i) mbar_init(&bar->s_full[i], 1);
@@ -250,67 +260,62 @@ __global__ void __launch_bounds__(kAttnThreads, 1) attention_kernel(const AttnPa
           ++cnt;
         }
       }
-    } else if (warp == 9) {
-      // ---------------------------------------------------------------- MMA issuer
+    } else if (warp == 10) {
+      // ---------------------------------------------------------------- similarity issuer: S(G) = Q_t K_j^T
+      // Two issuing warps (this one and the PV warp) instead of one: a single issuer measured 1250 cycles per half
+      // step against 512 cycles of tensor work -- every ready mbarrier wait costs ~90 cycles, every tcgen05.commit
+      // ~150, and the issue of an MMA blocks while the tensor pipe's short queue is full, so one warp's waits and
+      // bookkeeping run with an idle tensor pipe.  With two warps the queue holds the other warp's MMAs meanwhile.
+      // Global step G = (key block, query tile) pairs in order, across items; S buffer = G % 3.  S(G) may be written
+      // once PV(G-3) has READ P(G-3) from the same buffer: for an even G-3 (tile 0) the PV warp commits
+      // t0_free[block & 1]; for an odd G-3 (tile 1) its commit of kv_empty[stage] says the same.
       const bool leader = elect_one();  // all lanes run the loop (uniform operands); one lane issues
       constexpr uint32_t idesc_qk = umma_idesc(kFmtBF16, 128, 128);
-      constexpr uint32_t idesc_pv = umma_idesc(kFmtBF16, 128, 64);
-      // Descriptors differ only in their 14-bit (address >> 4) field, which cannot carry out for addresses below
-      // 256 KB: one descriptor per operand array, plain 64-bit adds per step (the MMA warp's instruction count per
-      // step bounds how early the next similarity can be queued -- keep this loop lean).
       const uint64_t dQ0 = umma_desc_kmajor_sw128(smem_u32(sQ));
       const uint64_t dK0 = umma_desc_kmajor_sw128(smem_u32(sKV));
-      const uint64_t dV0 = umma_desc_kmajor_sw128(smem_u32(sKV) + kTileBytes);
-
-      // Similarity cursor: runs three global steps ahead of the PV cursor, across item boundaries.
-      // Global step G = (key block, query tile) pairs in issue order; S buffer = G % 3 (kept as a rotating counter).
-      // The similarity of step G+3 is issued right behind the PV of step G, before the commits, because the softmax
-      // warpgroup of the other tile is waiting for exactly this similarity.  Everything the issue needs (item decode,
-      // Q / K arrival, descriptors) is resolved by prepare_qk() before the wait for P.
-      // The warp's own instruction stream bounds the kernel (measured: 1250 cycles per half step of which the tensor
-      // pipe works 512): ONE predicated region per half step holds all tcgen05 instructions, the rotating indices
-      // are counters (no % 3, no divisions), and only the last PV of an item commits pv_done.
-      int qw = blockIdx.x, q_n = 0, q_cnt = 0, q_nkt = 0;
-      bool q_loaded = false;
-      uint32_t q_kv = 0, q_sb = 0;  // q_sb: S buffer of the next similarity
-      bool qk_ready = false, qk_last = false;
-      uint64_t qk_da = 0, qk_db = 0;
-      auto prepare_qk = [&]() {
-        qk_ready = false;
-        while (!q_loaded) {
-          if (qw >= p.items) return;
-          const AttnItem it = attn_item(p, qw);
-          if (it.skip) { qw += gridDim.x; continue; }
-          q_nkt = it.nkt; q_n = 0; q_loaded = true;
-          LG_WAIT_M(&bar->q_full[q_cnt & 1], (q_cnt >> 1) & 1);
-        }
-        const int t = q_n & 1;
-        const uint32_t kvi = q_kv + (q_n >> 1), s = kvi % kStages;
-        if (t == 0) LG_WAIT_M(&bar->kv_full[s], (kvi / kStages) & 1);
-        qk_da = dQ0 + static_cast<uint64_t>(((q_cnt & 1) * 2 + t) * (kTileBytes >> 4));
-        qk_db = dK0 + static_cast<uint64_t>(s * (2 * kTileBytes >> 4));
-        qk_last = q_n + 1 == 2 * q_nkt;
-        qk_ready = true;
-      };
-      auto advance_qk = [&]() {  // bookkeeping behind an issued similarity (all lanes)
-        if (!qk_ready) return;
-        q_sb = q_sb == 2 ? 0 : q_sb + 1;
-        ++q_n;
-        if (qk_last) { q_kv += q_nkt; ++q_cnt; q_loaded = false; qw += gridDim.x; }
-      };
-
-      for (int i = 0; i < 3; ++i) {
-        prepare_qk();
-        tc_fence_after();
-        if (leader && qk_ready) {
+      uint32_t kv0 = 0, sb = 0, G = 0;  // kv0: key blocks of the earlier items; sb = G % 3
+      int cnt = 0;                      // non-skipped items so far (Q buffer = cnt & 1)
+      for (int w = blockIdx.x; w < p.items; w += gridDim.x) {
+        const AttnItem it = attn_item(p, w);
+        if (it.skip) continue;
+        mbar_wait(&bar->q_full[cnt & 1], (cnt >> 1) & 1);
+        const int nsteps = 2 * it.nkt;
+        for (int n = 0; n < nsteps; ++n, ++G) {
+          const int t = n & 1;
+          const uint32_t kvi = kv0 + (n >> 1), s = kvi % kStages;
+          if (t == 0) mbar_wait(&bar->kv_full[s], (kvi / kStages) & 1);
+          if (G >= 3) {
+            if (t == 0) {  // G-3 = tile 1 of block kvi-2
+              const uint32_t kp = kvi - 2;
+              mbar_wait(&bar->kv_empty[kp % kStages], (kp / kStages) & 1);
+            } else {       // G-3 = tile 0 of block kvi-1
+              const uint32_t kp = kvi - 1;
+              mbar_wait(&bar->t0_free[kp & 1], (kp >> 1) & 1);
+            }
+          }
+          tc_fence_after();
+          const uint64_t da = dQ0 + static_cast<uint64_t>(((cnt & 1) * 2 + t) * (kTileBytes >> 4));
+          const uint64_t db = dK0 + static_cast<uint64_t>(s * (2 * kTileBytes >> 4));
+          if (leader) {
 #pragma unroll
-          for (int kk = 0; kk < 4; ++kk)  // K = 64 = 4 x 16, 32 B per step inside the 128 B swizzle row
-            umma_bf16_ss(tmem + kColS + q_sb * 128, qk_da + 2 * kk, qk_db + 2 * kk, idesc_qk, kk > 0);
-          umma_commit(&bar->s_full[q_sb]);
-          if (qk_last) umma_commit(&bar->q_empty[q_cnt & 1]);
+            for (int kk = 0; kk < 4; ++kk)  // K = 64 = 4 x 16, 32 B per step inside the 128 B swizzle row
+              umma_bf16_ss(tmem + kColS + sb * 128, da + 2 * kk, db + 2 * kk, idesc_qk, kk > 0);
+            umma_commit(&bar->s_full[sb]);
+            if (n + 1 == nsteps) umma_commit(&bar->q_empty[cnt & 1]);  // last similarity of the item: Q buffer free
+            TRACE(27, G);
+          }
+          sb = sb == 2 ? 0 : sb + 1;
         }
-        advance_qk();
+        kv0 += it.nkt;
+        ++cnt;
       }
+    } else if (warp == 9) {
+      // ---------------------------------------------------------------- PV issuer: O_t += P_t(j) V_j
+      const bool leader = elect_one();
+      constexpr uint32_t idesc_pv = umma_idesc(kFmtBF16, 128, 64);
+      // Descriptors differ only in their 14-bit (address >> 4) field, which cannot carry out for addresses below
+      // 256 KB: one descriptor per operand array, plain 64-bit adds per step.
+      const uint64_t dV0 = umma_desc_kmajor_sw128(smem_u32(sKV) + kTileBytes);
       uint32_t p_kv = 0, p_sb = 0;
       int p_cnt = 0;
 #ifdef LG_ATTN_TRACE
@@ -327,11 +332,9 @@ __global__ void __launch_bounds__(kAttnThreads, 1) attention_kernel(const AttnPa
           const uint32_t tP = tmem + kColS + p_sb * 128;
           const uint64_t dv = dV0 + static_cast<uint64_t>(s * (2 * kTileBytes >> 4));
           if (leader) TRACE(24, G_p);
-          prepare_qk();                         // step G+3: recycles S buffer G % 3 behind this PV
-          if (leader) TRACE(25, G_p);
-          LG_WAIT_M(&bar->p_full[2 * t + (kvi & 1)], (kvi >> 1) & 1);  // P_t(j) stored in its S buffer
+          mbar_wait(&bar->p_full[2 * t + (kvi & 1)], (kvi >> 1) & 1);  // P_t(j) stored in its S buffer
           if (leader) TRACE(6, G_p);
-          if (j == 0 && p_cnt > 0) LG_WAIT_M(&bar->o_free[t], (p_cnt - 1) & 1);  // previous item's O_t was read out
+          if (j == 0 && p_cnt > 0) mbar_wait(&bar->o_free[t], (p_cnt - 1) & 1);  // previous item's O_t was read out
           tc_fence_after();
           if (leader) {
 #pragma unroll
@@ -340,22 +343,12 @@ __global__ void __launch_bounds__(kAttnThreads, 1) attention_kernel(const AttnPa
                            dv + static_cast<uint64_t>((kk >> 2) * (kTileBytes / 2 >> 4) + (kk & 3) * 2), idesc_pv,
                            (j > 0 || kk > 0));
             TRACE(26, G_p);
-            // same-thread MMAs execute in order: the similarity overwrites the S buffer after PV has read P from it
-            if (qk_ready) {
-#pragma unroll
-              for (int kk = 0; kk < 4; ++kk)
-                umma_bf16_ss(tmem + kColS + q_sb * 128, qk_da + 2 * kk, qk_db + 2 * kk, idesc_qk, kk > 0);
-            }
-            TRACE(27, G_p);
-            if (qk_ready) {
-              umma_commit(&bar->s_full[q_sb]);
-              if (qk_last) umma_commit(&bar->q_empty[q_cnt & 1]);  // last similarity of the item: its Q buffer is free
-            }
-            if (t == 1) umma_commit(&bar->kv_empty[s]);  // K_j and V_j are dead once PV1_j retires (the rare rescale
-                                                         // path of the softmax warps waits on this barrier too)
+            // ONE commit per step says "PV(G) has retired": the S buffer may be overwritten (similarity warp), and for
+            // tile 1 also "K_j, V_j are dead" (producer; the rare rescale path of the softmax warps waits on it too)
+            if (t == 1) umma_commit(&bar->kv_empty[s]);
+            else umma_commit(&bar->t0_free[kvi & 1]);
             if (n + 2 >= nsteps) umma_commit(&bar->pv_done[t]);  // last PV_t of the item: the item epilogue waits for it
           }
-          advance_qk();
           p_sb = p_sb == 2 ? 0 : p_sb + 1;
           if (leader) TRACE(7, G_p);
 #ifdef LG_ATTN_TRACE
@@ -380,6 +373,12 @@ __global__ void __launch_bounds__(kAttnThreads, 1) attention_kernel(const AttnPa
     uint32_t pk0[32], pk1[32];  // P of the block as packed bf16 pairs: 64 TMEM columns
     uint32_t kv_base = 0;       // running key-block counter: barrier phases continue across items
     uint32_t item_cnt = 0;      // non-skipped items so far (phase of pv_done)
+#if LG_STAGGER > 0
+    if (t == 1) {  // start tile 1 half a block late: the sweeps of the two warpgroups then alternate on the MUFU unit
+      long long c0 = clock64();
+      while (clock64() - c0 < LG_STAGGER) {}
+    }
+#endif
 
     for (int w = blockIdx.x; w < p.items; w += gridDim.x) {
       const AttnItem it = attn_item(p, w);
@@ -420,6 +419,14 @@ __global__ void __launch_bounds__(kAttnThreads, 1) attention_kernel(const AttnPa
         const uint32_t tS = tS0 + (G % 3) * 128;
         if ((threadIdx.x & 127) == 0) TRACE(t * 3, kv_base + j);
         if ((threadIdx.x & 127) == 0) { DBG(8 + t, j); DBG(10 + t, 1); }
+#if LG_ALTERNATE
+        // Tile 1 starts block n when tile 0 is half way through its block n; tile 0 starts block n+1 when tile 1 is
+        // half way through block n.  Left alone the two warpgroups fall into step (tile 1 trails by the latency of its
+        // similarity), sweep at the same time at half the MUFU rate each and then sit in their P hand-off together
+        // with the MUFU unit idle; alternating, one sweeps alone while the other stores P, waits and loads.
+        if (t == 1) asm volatile("bar.sync 3, 256;" ::: "memory");
+        else if (kv_base + j > 0) asm volatile("bar.sync 4, 256;" ::: "memory");
+#endif
         if (!pf) {
           LG_WAIT(&bar->s_full[G % 3], (G / 3) & 1);
           tc_fence_after();
@@ -433,6 +440,7 @@ __global__ void __launch_bounds__(kAttnThreads, 1) attention_kernel(const AttnPa
         for (int attempt = 0; attempt < 2; ++attempt) {
           if (first || attempt == 1) {
             // exact block max (first block of a row, or a row sum that reached the limit): new reference, rescale
+            // (taking the max of the first 32 columns only for a first block measured slower: 0.3435 vs 0.3410 ms)
             float mx = -INFINITY;
 #pragma unroll
             for (int cb = 0; cb < 4; ++cb) {
@@ -584,6 +592,9 @@ __global__ void __launch_bounds__(kAttnThreads, 1) attention_kernel(const AttnPa
             constexpr float kMagic126 = 12582912.f - 126.f;
             const float2 k252 = make_float2(252.f, 252.f), km = make_float2(kMagic126, kMagic126);
             float2 T[16][3], E[16][4], Y[16], RR[16], FR[16], PP[16];
+#if LG_POLY_PAIRS == 2
+            float2 Y2[16], RR2[16], FR2[16], PP2[16];
+#endif
             float2 s2 = make_float2(0.f, 0.f), s3 = make_float2(0.f, 0.f);
             auto mask_chunk = [&](uint32_t(&v)[32], const int cb) {
               if (partial) {
@@ -596,8 +607,39 @@ __global__ void __launch_bounds__(kAttnThreads, 1) attention_kernel(const AttnPa
 #define LG_ARGS1(g)                                                                   \
   T[g][0] = __ffma2_rn(make_float2(LG_V(g, 0), LG_V(g, 1)), c2, nms2);                \
   T[g][1] = __ffma2_rn(make_float2(LG_V(g, 2), LG_V(g, 3)), c2, nms2);
+#if LG_POLY_PAIRS == 2
+#define LG_ARGS2_T2(g)                                                                \
+  {                                                                                   \
+    float ya, yb;                                                                     \
+    asm("fma.rn.sat.f32 %0, %1, %2, %3;" : "=f"(ya) : "f"(LG_V(g, 4)), "f"(cs252), "f"(bs252)); \
+    asm("fma.rn.sat.f32 %0, %1, %2, %3;" : "=f"(yb) : "f"(LG_V(g, 5)), "f"(cs252), "f"(bs252)); \
+    Y2[g] = make_float2(ya, yb);                                                      \
+  }
+#define LG_QA(g) RR2[g] = __ffma2_rn(Y2[g], k252, km);
+#define LG_QB(g) FR2[g] = __fadd2_rn(km, make_float2(-RR2[g].x, -RR2[g].y));
+#define LG_QC(g) FR2[g] = __ffma2_rn(Y2[g], k252, FR2[g]);
+#define LG_QD(g) PP2[g] = __ffma2_rn(make_float2(0.0551716685f, 0.0551716685f), FR2[g], make_float2(0.2426111251f, 0.2426111251f));
+#define LG_QE(g) PP2[g] = __ffma2_rn(PP2[g], FR2[g], make_float2(0.6932609677f, 0.6932609677f));
+#define LG_QF(g) PP2[g] = __ffma2_rn(PP2[g], FR2[g], make_float2(0.9999280572f, 0.9999280572f));
+#define LG_QG(g)                                                                                        \
+  E[g][2] = make_float2(__int_as_float((__float_as_int(RR2[g].x) << 23) + __float_as_int(PP2[g].x)),    \
+                        __int_as_float((__float_as_int(RR2[g].y) << 23) + __float_as_int(PP2[g].y)));
+#define LG_MUFU2X(g)
+#define LG_MUFU2Y(g)
+#else
+#define LG_ARGS2_T2(g) T[g][2] = __ffma2_rn(make_float2(LG_V(g, 4), LG_V(g, 5)), c2, nms2);
+#define LG_QA(g)
+#define LG_QB(g)
+#define LG_QC(g)
+#define LG_QD(g)
+#define LG_QE(g)
+#define LG_QF(g)
+#define LG_QG(g)
+#define LG_MUFU2X(g) E[g][2].x = ex2_approx(T[g][2].x);
+#define LG_MUFU2Y(g) E[g][2].y = ex2_approx(T[g][2].y);
+#endif
 #define LG_ARGS2(g)                                                                   \
-  T[g][2] = __ffma2_rn(make_float2(LG_V(g, 4), LG_V(g, 5)), c2, nms2);                \
+  LG_ARGS2_T2(g)                                                                      \
   {                                                                                   \
     float ya, yb;                                                                     \
     asm("fma.rn.sat.f32 %0, %1, %2, %3;" : "=f"(ya) : "f"(LG_V(g, 6)), "f"(cs252), "f"(bs252)); \
@@ -620,11 +662,17 @@ __global__ void __launch_bounds__(kAttnThreads, 1) attention_kernel(const AttnPa
             if (threadIdx.x == 0) TRACE(16, kv_base + j);
             tmem_ld32(tS + 32, vb);
             mask_chunk(va, 0);
-            LG_ARGS1(0) LG_ARGS2(0) LG_PA(0) LG_PB(0) LG_PC(0) LG_PD(0) LG_PE(0) LG_PF(0) LG_PG(0)
+            LG_ARGS1(0) LG_ARGS2(0) LG_PA(0) LG_QA(0) LG_PB(0) LG_QB(0) LG_PC(0) LG_QC(0) LG_PD(0) LG_QD(0) LG_PE(0) LG_QE(0) LG_PF(0) LG_QF(0) LG_PG(0) LG_QG(0)
 #pragma unroll
             for (int g = 0; g < 16; ++g) {
               if (g == 3) { if (threadIdx.x == 0) TRACE(17, kv_base + j); tmem_wait_ld(); mask_chunk(vb, 1); }
               if (g == 7) { if (threadIdx.x == 0) TRACE(18, kv_base + j); tmem_wait_ld(); mask_chunk(va, 2); }
+#if LG_ALTERNATE
+              if (g == 8 && attempt == 0) {  // half way: once per block (the rare second attempt does not signal again)
+                if (t == 0) asm volatile("bar.arrive 3, 256;" ::: "memory");
+                else asm volatile("bar.arrive 4, 256;" ::: "memory");
+              }
+#endif
               if (g == 11) { if (threadIdx.x == 0) TRACE(19, kv_base + j); tmem_wait_ld(); mask_chunk(vb, 3); }
               E[g][0].x = ex2_approx(T[g][0].x);
               if (g + 1 < 16) { LG_ARGS1(g + 1) }
@@ -633,16 +681,16 @@ __global__ void __launch_bounds__(kAttnThreads, 1) attention_kernel(const AttnPa
               if (g == 3) tmem_ld32(tS + 64, va);   // va is dead: the arguments of group 3 were its last readers
               if (g == 7) tmem_ld32(tS + 96, vb);
               E[g][1].x = ex2_approx(T[g][1].x);
-              if (g + 1 < 16) { LG_PA(g + 1) }
+              if (g + 1 < 16) { LG_PA(g + 1) LG_QA(g + 1) }
               if (g > 0) { s0 = __fadd2_rn(s0, E[g - 1][0]); LG_PK(g - 1, 0) = pack_bf16x2(E[g - 1][0].x, E[g - 1][0].y); }
               E[g][1].y = ex2_approx(T[g][1].y);
-              if (g + 1 < 16) { LG_PB(g + 1) }
+              if (g + 1 < 16) { LG_PB(g + 1) LG_QB(g + 1) }
               if (g > 0) { s1 = __fadd2_rn(s1, E[g - 1][1]); LG_PK(g - 1, 1) = pack_bf16x2(E[g - 1][1].x, E[g - 1][1].y); }
-              E[g][2].x = ex2_approx(T[g][2].x);
-              if (g + 1 < 16) { LG_PC(g + 1) LG_PD(g + 1) }
+              LG_MUFU2X(g)
+              if (g + 1 < 16) { LG_PC(g + 1) LG_QC(g + 1) LG_PD(g + 1) LG_QD(g + 1) }
               if (g > 0) { s2 = __fadd2_rn(s2, E[g - 1][2]); LG_PK(g - 1, 2) = pack_bf16x2(E[g - 1][2].x, E[g - 1][2].y); }
-              E[g][2].y = ex2_approx(T[g][2].y);
-              if (g + 1 < 16) { LG_PE(g + 1) LG_PF(g + 1) LG_PG(g + 1) }
+              LG_MUFU2Y(g)
+              if (g + 1 < 16) { LG_PE(g + 1) LG_QE(g + 1) LG_PF(g + 1) LG_QF(g + 1) LG_PG(g + 1) LG_QG(g + 1) }
               if (g > 0) { s3 = __fadd2_rn(s3, E[g - 1][3]); LG_PK(g - 1, 3) = pack_bf16x2(E[g - 1][3].x, E[g - 1][3].y); }
             }
             s0 = __fadd2_rn(s0, E[15][0]); LG_PK(15, 0) = pack_bf16x2(E[15][0].x, E[15][0].y);
@@ -793,6 +841,9 @@ __global__ void __launch_bounds__(kAttnThreads, 1) attention_kernel(const AttnPa
         }
       }
     }
+#if LG_ALTERNATE
+    if (t == 0 && kv_base > 0) asm volatile("bar.sync 4, 256;" ::: "memory");  // absorbs tile 1's last half-way signal
+#endif
     if (lane == 0) bulk_wait_all();  // outstanding context stores
     if ((threadIdx.x & 127) == 0) DBG(10 + t, 7);
   }

@@ -35,8 +35,9 @@ if (tr[16] > 0).any():
         print(f"blk={j:3d} " + " ".join(f"{t[k + 1] - t[k]:5d}" for k in range(len(t) - 1)))
 
 if (tr[24] > 0).any():
-    print("mma warp per global step G (cycles): loop top -> operands of QK(G+3) ready -> P(G) ready -> PV issued -> QK issued -> commits done | period")
+    print("PV warp per global step G (cycles): loop top -> P(G) ready -> PV issued -> commits done | period | P arrived after loop top | "
+          "similarity warp: S(G+3) issued after this step's loop top")
     for G in range(70, 96):
-        t = [tr[24, G], tr[25, G], tr[6, G], tr[26, G], tr[27, G], tr[7, G]]
-        print(f"G={G:3d} t={G & 1} " + " ".join(f"{t[k + 1] - t[k]:5d}" for k in range(5)) + f" | {tr[24, G + 1] - tr[24, G]:5d}"
-              f"   P arrived {tr[(G & 1) * 3 + 2, G >> 1] - tr[24, G]:6d} after loop top")
+        t = [tr[24, G], tr[6, G], tr[26, G], tr[7, G]]
+        print(f"G={G:3d} t={G & 1} " + " ".join(f"{t[k + 1] - t[k]:5d}" for k in range(3)) + f" | {tr[24, G + 1] - tr[24, G]:5d}"
+              f" | {tr[(G & 1) * 3 + 2, G >> 1] - tr[24, G]:6d} | {tr[27, G + 3] - tr[24, G]:6d}")
