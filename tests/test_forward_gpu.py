@@ -46,7 +46,7 @@ def test_forward_vs_golden(name):
     agree1 = (pred["matches1"].cpu().numpy() == g["matches1"]).mean()
     print(f"{name}: max|dlog_assignment|={err:.3e} match agreement {agree0:.4f}/{agree1:.4f}")
     assert err < BF16_TOL, err
-    assert agree0 > 0.97 and agree1 > 0.97
+    assert agree0 >= 0.995 and agree1 >= 0.995  # measured 1.000
     for k in ("matches0", "matches1", "prune0", "prune1"):
         assert pred[k].cpu().numpy().dtype == g[k].dtype and pred[k].shape == g[k].shape, k
     assert float(pred["prune0"][0, 0]) == 9.0
@@ -116,7 +116,7 @@ def test_forward_varlen_vs_golden():
         assert np.abs(la[p, :a, N] - ref[:a, c]).max() < BF16_TOL
         assert np.abs(la[p, M, :c] - ref[a, :c]).max() < BF16_TOL
         m0 = pred["matches0"][p, :a].cpu().numpy()
-        assert (m0 == g[f"matches0_{p}"][0]).mean() > 0.95
+        assert (m0 == g[f"matches0_{p}"][0]).mean() >= 0.995  # measured 1.000
         assert (pred["matches0"][p, a:] == -1).all()
 
 
@@ -130,7 +130,7 @@ def test_forward_2048_vs_oracle():
     err = (pred["log_assignment"].cpu() - ref["log_assignment"]).abs().max().item()
     agree = (pred["matches0"].cpu() == ref["matches0"]).float().mean().item()
     print(f"2048: max|dlog_assignment|={err:.3e} match agreement {agree:.4f}")
-    assert err < BF16_TOL and agree > 0.97
+    assert err < BF16_TOL and agree >= 0.995  # measured 1.000
 
 
 def test_forward_fp32_path_2048_vs_oracle():
@@ -163,7 +163,7 @@ def test_forward_add_scale_ori_vs_oracle(precision, tol):
     err = (pred["log_assignment"].cpu() - ref["log_assignment"]).abs().max().item()
     print(f"add_scale_ori {precision}: max|dlog_assignment|={err:.3e}")
     assert err < tol
-    assert (pred["matches0"].cpu() == ref["matches0"]).float().mean() > 0.97
+    assert (pred["matches0"].cpu() == ref["matches0"]).float().mean() >= 0.995
 
 
 def test_forward_edge_shapes_vs_oracle():
@@ -177,7 +177,7 @@ def test_forward_edge_shapes_vs_oracle():
         pred = model(_cuda(data))
         assert pred["log_assignment"].shape == ref["log_assignment"].shape == (1, m + 1, n + 1)
         assert (pred["log_assignment"].cpu() - ref["log_assignment"]).abs().max() < BF16_TOL
-        assert (pred["matches0"].cpu() == ref["matches0"]).float().mean() > 0.97
+        assert (pred["matches0"].cpu() == ref["matches0"]).float().mean() >= 0.995
         assert (pred["matching_scores1"].cpu() - ref["matching_scores1"]).abs().max() < BF16_TOL
 
 
@@ -214,53 +214,13 @@ def test_registry_alias_and_errors():
         model(d)
 
 
-@pytest.mark.parametrize("name", ["adaptive_both_512x400", "adaptive_width_300x400", "adaptive_depth_300x400"])
-def test_adaptive_forward_vs_golden(name):
-    """BASELINE config 3 (depth/width confidence): exit layer, pruning indices and the assignment
-    over the kept points against the reference run."""
-    meta, g = load_golden("fwd_" + name)
-    conf, sd, data = _golden_inputs(meta)
-    pred = _model(conf, sd)(_cuda(data))
-    la = pred["log_assignment"].cpu().numpy()
-    p0, p1 = pred["prune0"].cpu().numpy(), pred["prune1"].cpu().numpy()
-    assert p0.dtype == g["prune0"].dtype and p0.shape == g["prune0"].shape
-    agree_p = min((p0 == g["prune0"]).mean(), (p1 == g["prune1"]).mean())
-    print(f"{name}: exit layer {pred['exit_layer']}, la shape {la.shape} (ref {meta['la_shape']}), prune agreement {agree_p:.4f}")
-    assert agree_p > 0.99
-    if list(la.shape) == meta["la_shape"]:
-        err = np.abs(la - g["log_assignment"]).max()
-        print(f"   max|dlog_assignment|={err:.3e}")
-        assert err < BF16_TOL
-        assert (pred["matches0"].cpu().numpy() == g["matches0"]).mean() > 0.97
-    else:  # a marginal keep decision flipped under bf16 attention: sizes must still be within 1 %
-        assert abs(la.shape[1] - meta["la_shape"][1]) <= 0.01 * meta["la_shape"][1] + 1
-        assert abs(la.shape[2] - meta["la_shape"][2]) <= 0.01 * meta["la_shape"][2] + 1
+# The adaptive fixtures (exit layer, prune counters, assignment over the kept points) are checked in
+# tests/test_scale_parity_gpu.py against the reference's own per-layer score tensors: a keep decision may differ from
+# the reference's only for a token within a stated margin of its threshold, and which branch ran is recorded.
 
 
 def _slice_pair(data, b):
     return {k: ({kk: vv[b:b + 1] for kk, vv in v.items()} if isinstance(v, dict) else v[b:b + 1]) for k, v in data.items()}
-
-
-@pytest.mark.parametrize("name", ["adaptive_both_512x400", "adaptive_width_300x400", "adaptive_depth_300x400"])
-def test_adaptive_batched_copies_vs_golden(name):
-    """the batched adaptive forward on a batch made of copies of the golden pair must
-    give, for every copy, what the reference gave for the single pair."""
-    meta, g = load_golden("fwd_" + name)
-    conf, sd, data = _golden_inputs(meta)
-    data = {k: ({kk: vv.repeat(3, 1) for kk, vv in v.items()} if isinstance(v, dict) else v.repeat(3, 1, 1))
-            for k, v in data.items()}
-    pred = _model(conf, sd)(_cuda(data))
-    assert len(pred["log_assignment"]) == 3 and pred["matches0"].shape == (3, meta["m"])
-    for b in range(3):
-        la = pred["log_assignment"][b].cpu().numpy()
-        p0 = pred["prune0"][b:b + 1].cpu().numpy()
-        assert p0.dtype == g["prune0"].dtype and (p0 == g["prune0"]).mean() > 0.99
-        if list(la.shape) == meta["la_shape"]:
-            assert np.abs(la - g["log_assignment"]).max() < BF16_TOL
-            assert (pred["matches0"][b:b + 1].cpu().numpy() == g["matches0"]).mean() > 0.97
-            assert np.abs(pred["matching_scores0"][b:b + 1].cpu().numpy() - g["matching_scores0"]).max() < BF16_TOL
-        else:
-            assert abs(la.shape[1] - meta["la_shape"][1]) <= 0.01 * meta["la_shape"][1] + 1
 
 
 @pytest.mark.parametrize("depth,width", [(0.95, 0.95), (-1, 0.95), (0.95, -1)])
@@ -287,7 +247,7 @@ def test_adaptive_batched_vs_single_and_oracle(depth, width):
     la = pred["log_assignment"][0].cpu()
     if la.shape == ref["log_assignment"].shape:
         assert (la - ref["log_assignment"]).abs().max() < BF16_TOL
-        assert (pred["matches0"][0:1].cpu() == ref["matches0"]).float().mean() > 0.97
+        assert (pred["matches0"][0:1].cpu() == ref["matches0"]).float().mean() >= 0.995
     assert (pred["prune0"][0:1].cpu() == ref["prune0"]).float().mean() > 0.99
 
 
@@ -377,7 +337,7 @@ def test_packed_pairs_reproduce_one_pair_per_call(precision, la_tol):
         want = O.forward(sd, conf, p)  # the reference's own one-pair forward (oracle pinned to it by the goldens)
         err = (want["log_assignment"] - la_b.cpu()).abs().max().item()
         assert err < (BF16_TOL if precision == "bf16" else 1e-4), (i, err)
-        assert (want["matches0"] == got["matches0"].cpu()).float().mean() > 0.97
+        assert (want["matches0"] == got["matches0"].cpu()).float().mean() >= 0.995
 
 
 def test_packed_pairs_at_export_scale():

@@ -372,6 +372,32 @@ def test_prune_plan_bit_exact_on_reference_scores(C, B, N, use_conf):
             assert int(counts[b, 1]) == int((conf[b] < thr).sum())
 
 
+@pytest.mark.parametrize("name", ["fwd_adaptive_both_2048", "trace_adaptive_both_512x400", "trace_adaptive_width_300x400"])
+def test_prune_plan_bit_exact_on_the_reference_run_tensors(C, name):
+    """north_star: pruning indices bit-exact when fed the reference's OWN score tensors -- the token confidences
+    (lightglue.py:102-107), matchability scores (:317-318) and keep masks (:586-593) the reference module produced at
+    every pruning layer of an adaptive run (hooks in oracle/make_golden_scale.py), not synthetic ones."""
+    from conftest import load_golden
+
+    meta, g = load_golden(name)
+    width = meta["conf"]["width_confidence"]
+    min_match = float(np.float32(1 - width))
+    assert meta["layers_pruned"] > 0
+    for i in range(meta["layers_pruned"]):
+        thr = float(meta["confidence_thresholds"][i])
+        for side in (0, 1):
+            match = torch.from_numpy(g[f"L{i}_match{side}"]).cuda()
+            conf = torch.from_numpy(g[f"L{i}_conf{side}"]).cuda() if f"L{i}_conf{side}" in g else None
+            keep = torch.from_numpy(g[f"L{i}_keep{side}"])
+            keep_idx, counts = C.prune_plan(conf, match, thr, min_match)
+            want = torch.where(keep)[1]
+            k = int(counts[0, 0])
+            assert k == want.numel(), (name, i, side)
+            assert torch.equal(keep_idx[0, :k].cpu().long(), want), (name, i, side)
+            if conf is not None:  # the count check_if_stop needs (:595-606)
+                assert int(counts[0, 1]) == int((conf < thr).sum())
+
+
 def test_token_scores_and_gather(C):
     g = _gen(3)
     B, N = 2, 1500
