@@ -49,11 +49,21 @@ def parse():
     ap.add_argument("--batch", type=int, default=32, help="pairs per GPU per step")
     ap.add_argument("--kpts", type=int, default=2048)
     ap.add_argument("--cpu-pairs", type=int, default=4, help="pairs timed for the cpu_baseline sample")
+    ap.add_argument("--flash", action="store_true",
+                    help="--impl eager: the reference's flash=True branch (fp16 SDPA per direction, TF32 allowed)")
+    ap.add_argument("--no-eager", action="store_true", help="skip the gpu_eager_baseline legs of the b200 arm")
     return ap.parse_args()
 
 
 def workload_name(a):
     return f"SuperPoint+LightGlue (9 layers, d=256, 4 heads), {a.batch} pairs x {a.kpts} keypoints per GPU, synthetic"
+
+
+def config_dict(a, world):
+    """The SAME config object in every arm (the driver compares them key by key)."""
+    return {"workload": workload_name(a), "pairs_per_gpu": a.batch, "keypoints": a.kpts,
+            "l2": "inputs+activations per step (>4 GB) exceed the 126 MB L2; no flush needed",
+            "parallelism": f"pairs sharded over {world} GPU(s), no data-path collective"}
 
 
 # ----------------------------------------------------------------------------- CPU arm (oracle port)
@@ -91,45 +101,91 @@ def run_reference(a):
         "impl": "reference", "metric": METRIC, "value": rate, "unit": UNIT, "n_gpus": a.gpus, "steps": a.steps,
         "warmup": a.warmup, "ms_per_step": 1e3 * dt / a.steps, "higher_is_better": True, "scaling": "weak",
         "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-        "config": {"workload": workload_name(a), "note": "CPU arm: oracle port of the reference (Python reference cannot travel)"},
+        "config": config_dict(a, a.gpus),
+        "note": "CPU arm: oracle port of the reference (the Python reference cannot travel to the GPU box); a step is a "
+                "bounded sample of the workload: one pair of the batch",
         "cpu_baseline": {"value": rate, "unit": UNIT, "cores": cores, "kind": "port", "sample": sample},
         "e2e": {"value": rate, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "gpu_launches": 0,
     })
 
 
-def run_eager(a):
-    """Informative arm (SURVEY 8(d) "extra informative baseline"): the reference's algorithm in PyTorch eager fp32 on
-    the SAME B200 -- the oracle port (torch ops in the reference's op order) on cuda tensors, fp32 SDPA as in
-    lightglue.py:146-149, TF32 off.  Not the product and not the reference arm the driver compares against."""
+def _flash_oracle(O):
+    """The reference's flash=True branch on the oracle's op sequence: Attention.forward casts q, k, v to fp16 and calls
+    SDPA (lightglue.py:139-145); CrossBlock runs one such call per direction (:229-233) instead of the shared
+    similarity.  Returns a restore function."""
+    import torch.nn.functional as F
+
+    keep = (O.attention, O.cross_block)
+
+    def attention(q, k, v):
+        return F.scaled_dot_product_attention(q.half().contiguous(), k.half().contiguous(), v.half().contiguous()).to(q.dtype)
+
+    def cross_block(sd, p, x0, x1, heads=4):
+        def split(t):
+            return t.unflatten(-1, (heads, -1)).transpose(1, 2)
+
+        qk0, qk1 = split(O._lin(sd, p + ".to_qk", x0)), split(O._lin(sd, p + ".to_qk", x1))
+        v0, v1 = split(O._lin(sd, p + ".to_v", x0)), split(O._lin(sd, p + ".to_v", x1))
+        m0, m1 = attention(qk0, qk1, v1), attention(qk1, qk0, v0)
+        m0 = O._lin(sd, p + ".to_out", m0.transpose(1, 2).flatten(start_dim=-2))
+        m1 = O._lin(sd, p + ".to_out", m1.transpose(1, 2).flatten(start_dim=-2))
+        return O._ffn(sd, p, x0, m0), O._ffn(sd, p, x1, m1)
+
+    O.attention, O.cross_block = attention, cross_block
+
+    def restore():
+        O.attention, O.cross_block = keep
+
+    return restore
+
+
+def eager_rate(batch, kpts, steps, warmup, flash, dev):
+    """pairs/s of the reference's op sequence in PyTorch eager on the SAME GPU: the oracle port on cuda tensors.
+    flash=False: fp32 SDPA as in lightglue.py:146-149, TF32 off (the reference's most accurate GPU branch);
+    flash=True: its fastest one -- fp16 SDPA per direction (:139-145, :229-233), TF32 matmuls allowed."""
     from oracle import lightglue_oracle as O
 
+    W = importlib.import_module(PKG + ".weights")
+    tf32 = (torch.backends.cuda.matmul.allow_tf32, torch.backends.cudnn.allow_tf32)
+    torch.backends.cuda.matmul.allow_tf32 = torch.backends.cudnn.allow_tf32 = bool(flash)
+    restore = _flash_oracle(O) if flash else (lambda: None)
+    try:
+        sd = {k: v.to(dev) for k, v in W.make_state_dict(CONF, seed=0).items()}
+        data = to_device(W.make_inputs(batch, kpts, kpts, seed=1), dev, non_blocking=False)
+        with torch.no_grad():
+            for _ in range(warmup):
+                O.forward(sd, CONF, data)
+            torch.cuda.synchronize()
+            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            e0.record()
+            for _ in range(steps):
+                O.forward(sd, CONF, data)
+            e1.record()
+            torch.cuda.synchronize()
+        ms = e0.elapsed_time(e1)
+    finally:
+        restore()
+        torch.backends.cuda.matmul.allow_tf32, torch.backends.cudnn.allow_tf32 = tf32
+    return batch * steps / (ms / 1e3), ms / steps
+
+
+def run_eager(a):
+    """Informative arm (SURVEY 8(d) "extra informative baseline"): the reference's algorithm in PyTorch eager on the
+    SAME B200.  Not the product and not the reference arm the driver compares against."""
     rank = int(os.environ.get("RANK", "0"))
     if rank != 0:
         return
-    W = importlib.import_module(PKG + ".weights")
     dev = torch.device("cuda", 0)
-    torch.backends.cuda.matmul.allow_tf32 = False
-    torch.backends.cudnn.allow_tf32 = False
-    sd = {k: v.to(dev) for k, v in W.make_state_dict(CONF, seed=0).items()}
-    data = to_device(W.make_inputs(a.batch, a.kpts, a.kpts, seed=1), dev, non_blocking=False)
-    for _ in range(max(a.warmup, 3)):
-        O.forward(sd, CONF, data)
-    torch.cuda.synchronize()
-    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-    e0.record()
-    for _ in range(a.steps):
-        O.forward(sd, CONF, data)
-    e1.record()
-    torch.cuda.synchronize()
-    ms = e0.elapsed_time(e1)
+    rate, ms = eager_rate(a.batch, a.kpts, a.steps, max(a.warmup, 3), a.flash, dev)
     emit({
-        "impl": "eager", "metric": METRIC, "value": a.batch * a.steps / (ms / 1e3), "unit": UNIT, "n_gpus": 1,
-        "steps": a.steps, "warmup": max(a.warmup, 3), "ms_per_step": ms / a.steps, "higher_is_better": True,
-        "scaling": "weak", "vs_baseline": None, "dtype": "f32 (PyTorch eager, cuBLAS / SDPA, TF32 off)",
-        "data": "synthetic",
-        "config": {"workload": workload_name(a), "note": "oracle port of the reference on cuda tensors: informative only"},
-        "gpu_launches": 0,
+        "impl": "eager", "metric": METRIC, "value": rate, "unit": UNIT, "n_gpus": 1,
+        "steps": a.steps, "warmup": max(a.warmup, 3), "ms_per_step": ms, "higher_is_better": True,
+        "scaling": "weak", "vs_baseline": None,
+        "dtype": "f16 SDPA per direction, TF32 matmuls (PyTorch eager, the reference's flash=True branch)" if a.flash
+                 else "f32 (PyTorch eager, cuBLAS / SDPA, TF32 off)",
+        "data": "synthetic", "config": config_dict(a, 1),
+        "note": "oracle port of the reference on cuda tensors: informative only", "gpu_launches": 0,
     })
 
 
@@ -334,6 +390,7 @@ def run_b200(a):
     except Exception:
         pass
     peak = float(peaks.get("bf16_tflops_sustained", 1400.0))  # kernel timed inside a long step
+    peak_burst = float(peaks.get("bf16_tflops", 1650.0))
     achieved = attn_flops / (attn_ms / 1e3) / 1e12
     traffic = None  # DRAM bytes per launch of this kernel from the committed ncu --set full capture
     try:
@@ -342,7 +399,8 @@ def run_b200(a):
         pass
     roofline = {"kernel": "attention_kernel (tcgen05 flash attention, self + cross)", "bound": "tensor",
                 "flops": "algorithmic: 4*64*nq*nk per self launch, 3*64*nq*nk per cross direction (S counted once)",
-                "achieved": achieved, "peak": peak, "unit": "TFLOP/s", "frac": achieved / peak, "traffic": traffic,
+                "achieved": achieved, "peak": peak, "unit": "TFLOP/s", "frac": achieved / peak, "frac_of_burst_peak": achieved / peak_burst,
+                "traffic": traffic,
                 "peak_source": "MEASURED_PEAKS.json bf16_tflops_sustained" if peaks else "fallback 1.4 PFLOP/s sustained",
                 "launches_timed": len(ev), "avg_launch_ms": attn_ms / max(len(ev), 1),
                 "share_of_step": attn_ms / max(min(a.steps, 3), 1) / (ms / a.steps)}
@@ -375,6 +433,21 @@ def run_b200(a):
                        "frac": assign_gbs / hbm_peak, "ms": assign_ms, "algorithmic_bytes": assign_bytes,
                        "share_of_step": assign_ms / (ms / a.steps)}
 
+    # ---- the reference's op sequence in PyTorch eager on this same GPU (informative; N=1 only): its most accurate
+    # branch (fp32, TF32 off) and its fastest one (flash=True: fp16 SDPA, TF32 on), at the bench batch and one pair per call
+    eager = None
+    if rank == 0 and world == 1 and not a.no_eager:
+        del eng, rows0, rows1, pred, la_batch
+        model.__dict__.pop("_engines", None)
+        torch.cuda.empty_cache()
+        eager = {"unit": UNIT, "what": "oracle port of the reference on cuda tensors, PyTorch eager (cuBLAS / SDPA)"}
+        for name, flash in (("fp32_tf32_off", False), ("flash_fp16_sdpa_tf32_on", True)):
+            r32, ms32 = eager_rate(a.batch, a.kpts, 3, 2, flash, dev)
+            r1, ms1 = eager_rate(1, a.kpts, 10, 3, flash, dev)
+            eager[name] = {"pairs_per_s_batch": r32, "ms_per_step_batch": ms32, "pairs_per_s_one_pair_per_call": r1,
+                           "ms_one_pair": ms1}
+        torch.cuda.empty_cache()
+
     if rank == 0:
         cpu = None  # timed at N=1 only (under torchrun the other ranks' host threads would share the cores)
         if world == 1:
@@ -385,9 +458,7 @@ def run_b200(a):
             "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": a.steps, "warmup": max(a.warmup, 3),
             "ms_per_step": ms / a.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
             "dtype": "bf16 attention operands, 3-term split-bf16 linears and assignment, f32 accumulate / softmax / LayerNorm", "data": "synthetic",
-            "config": {"workload": workload_name(a), "pairs_per_gpu": a.batch, "keypoints": a.kpts,
-                       "l2": "inputs+activations per step (>4 GB) exceed the 126 MB L2; no flush needed",
-                       "parallelism": f"pairs sharded over {world} GPU(s), no data-path collective"},
+            "config": config_dict(a, world),
             "e2e": {"value": e2e, "unit": UNIT, "h2d_bytes_per_step": nbytes(host),
                     "d2h_bytes_per_step": sum(v.numel() * v.element_size() for v in out_host.values()),
                     "ms_per_step": ms_e2e / a.steps, "api": "HostPipeline(model).run(host batches)",
@@ -396,6 +467,7 @@ def run_b200(a):
             "roofline": roofline,
             "roofline_assignment": roofline_assign,
             "cpu_baseline": cpu,
+            "gpu_eager_baseline": eager,
             "check": check,
             "clocks": sampler.summary(),
         }

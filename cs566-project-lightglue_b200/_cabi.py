@@ -119,6 +119,8 @@ def _ptr(t):
 
 
 def _stream():
+    """Current stream of the CURRENT device: callers run under torch.cuda.device(<device of their tensors>)
+    (matcher.forward, HostPipeline.run), so that a model on cuda:1 launches on cuda:1."""
     return torch.cuda.current_stream().cuda_stream
 
 

@@ -446,7 +446,8 @@ static int assign_impl(const float* md0, const float* md1, const float* z0, cons
   float* col_lse = reinterpret_cast<float*>(w); w += align256(static_cast<size_t>(B) * N * 4);
   float* col_ls = reinterpret_cast<float*>(w);
 
-  static bool attr_done = false;
+  static bool attr_done_dev[lg::kMaxDevices] = {};  // per device; a benign race sets it twice
+  bool& attr_done = attr_done_dev[lg::current_device_slot()];
   if (!attr_done) {
     cudaError_t e = cudaFuncSetAttribute(lg::assign_tile_kernel<1>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                          lg::kAssignSmem);

@@ -460,7 +460,8 @@ extern "C" int lg_assign_tiles(const void* a_tiles, const void* b_tiles, int tpa
     rowkey = static_cast<unsigned long long*>(keys_ws);
     colkey = rowkey + static_cast<size_t>(B) * M;
   }
-  static bool attr_done = false;
+  static bool attr_done_dev[lg::kMaxDevices] = {};  // per device; a benign race sets it twice
+  bool& attr_done = attr_done_dev[lg::current_device_slot()];
   if (!attr_done) {
     cudaError_t e = cudaFuncSetAttribute(lg::assign_strip_kernel<1>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                          lg::kStripSmem);

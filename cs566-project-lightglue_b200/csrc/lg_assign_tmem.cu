@@ -471,7 +471,8 @@ extern "C" int lg_assign_tiles_tmem(const void* a_tiles, const void* b_tiles, in
     rowkey = static_cast<unsigned long long*>(keys_ws);
     colkey = rowkey + static_cast<size_t>(B) * M;
   }
-  static bool attr_done = false;
+  static bool attr_done_dev[lg::kMaxDevices] = {};  // per device; a benign race sets it twice
+  bool& attr_done = attr_done_dev[lg::current_device_slot()];
   if (!attr_done) {
     cudaError_t e = cudaFuncSetAttribute(lg::tm::assign_tmem_kernel<1>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                          lg::tm::kSmem);
@@ -506,7 +507,8 @@ int launch_assign_tmem_pass2(const void* a_tiles, const void* b_tiles, int tpa, 
                              const float* col_ls, float* scores, unsigned long long* rowkey,
                              unsigned long long* colkey, float scale, int B, int M, int N, cudaStream_t stream) {
   const int rt = (M + 127) / 128, ct64 = (N + 63) / 64;
-  static bool attr_done = false;
+  static bool attr_done_dev[lg::kMaxDevices] = {};  // per device; a benign race sets it twice
+  bool& attr_done = attr_done_dev[lg::current_device_slot()];
   if (!attr_done) {
     cudaError_t e = cudaFuncSetAttribute(tm::assign_tmem_kernel<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, tm::kSmem);
     if (e != cudaSuccess) return static_cast<int>(e);

@@ -872,15 +872,13 @@ static int check_side(const AttnSideArgs& a, bool tiles) {
 static int launch_attention(const AttnSideArgs* sides, int n_sides, void* out_tiles, int B, int H, float softmax_scale,
                             cudaStream_t stream) {
   if (B <= 0 || H <= 0 || n_sides < 1 || n_sides > 2) return LG_ERR_SHAPE;
-  static bool attr_done = false;  // idempotent attribute; a benign race at worst sets it twice
-  static int sms = 148;
+  static bool attr_done_dev[lg::kMaxDevices] = {};  // per device; a benign race sets it twice
+  bool& attr_done = attr_done_dev[lg::current_device_slot()];
+  const int sms = lg::device_sm_count();
   if (!attr_done) {
     cudaError_t e = cudaFuncSetAttribute(lg::attention_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                          lg::kAttnSmem);
     if (e != cudaSuccess) return static_cast<int>(e);
-    int dev = 0;
-    cudaGetDevice(&dev);
-    if (cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev) != cudaSuccess || sms <= 0) sms = 148;
     attr_done = true;
   }
   lg::AttnParams p{};

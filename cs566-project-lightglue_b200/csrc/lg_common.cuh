@@ -294,4 +294,24 @@ __device__ __forceinline__ float warp_sum(float v) {
   return v;
 }
 
+// ----------------------------------------------------------------------------- host side: per-device launch state
+// Function attributes (opt-in shared memory) and the SM count belong to a DEVICE, not to the process: a second GPU
+// used from the same process must get its own cudaFuncSetAttribute and its own grid size.
+constexpr int kMaxDevices = 64;
+inline int current_device_slot() {
+  int d = 0;
+  if (cudaGetDevice(&d) != cudaSuccess || d < 0 || d >= kMaxDevices) d = 0;
+  return d;
+}
+inline int device_sm_count() {
+  static int n[kMaxDevices] = {};
+  const int d = current_device_slot();
+  if (n[d] == 0) {
+    int v = 0;
+    if (cudaDeviceGetAttribute(&v, cudaDevAttrMultiProcessorCount, d) != cudaSuccess || v <= 0) v = 148;
+    n[d] = v;
+  }
+  return n[d];
+}
+
 }  // namespace lg

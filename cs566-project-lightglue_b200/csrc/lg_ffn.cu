@@ -355,16 +355,14 @@ extern "C" int lg_ffn_ln_gelu(const void* a0, int a0_atoms, const void* a1, int 
   p.out_tiles = static_cast<uint8_t*>(out_tiles);
   p.row_tiles = row_tiles;
 
-  static bool attr_done = false;
-  static int tpcs = 0;
+  static bool attr_done_dev[lg::kMaxDevices] = {};  // per device; a benign race sets it twice
+  bool& attr_done = attr_done_dev[lg::current_device_slot()];
+  const int sms_dev = lg::device_sm_count();
+  const int tpcs = sms_dev > 1 ? sms_dev / 2 : 74;
   if (!attr_done) {
     cudaError_t e =
         cudaFuncSetAttribute(lg::ffn_ln_gelu_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, lg::kFfnSmem);
     if (e != cudaSuccess) return static_cast<int>(e);
-    int dev = 0, sms = 0;
-    cudaGetDevice(&dev);
-    cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
-    tpcs = sms > 1 ? sms / 2 : 74;
     attr_done = true;
   }
   cudaLaunchConfig_t cfg = {};

@@ -167,7 +167,6 @@ extern "C" int lg_filter_from_keys(const void* keys_ws, const int* m_len, const 
 //   * the host-side name of the array is not a device address: the address is resolved once per device with
 //     cudaGetSymbolAddress (that device current) and cached.
 namespace lg {
-constexpr int kMaxDevices = 64;
 static __device__ __align__(256) unsigned long long g_filter_keys[LG_FILTER_STATIC_MAX_KEYS];
 }  // namespace lg
 

@@ -595,22 +595,14 @@ __global__ void __launch_bounds__(256) ln_gelu_tiles_kernel(const float* __restr
   }
 }
 
-static int sm_count() {
-  static int n = 0;
-  if (n == 0) {
-    int dev = 0;
-    cudaGetDevice(&dev);
-    cudaDeviceGetAttribute(&n, cudaDevAttrMultiProcessorCount, dev);
-    if (n <= 0) n = 148;
-  }
-  return n;
-}
+static int sm_count() { return device_sm_count(); }
 
 template <int kNt, int kEpi, int kCtas>
 static int launch_linear_n(const LinearParams& p, cudaStream_t stream) {
   constexpr int smem = linear_smem_bytes<kNt, kEpi, kCtas>();
   static_assert(smem <= kLinSmemMax, "shared memory budget");
-  static bool attr_done = false;
+  static bool attr_done_dev[lg::kMaxDevices] = {};  // per device; a benign race sets it twice
+  bool& attr_done = attr_done_dev[lg::current_device_slot()];
   if (!attr_done) {
     cudaError_t e =
         cudaFuncSetAttribute(linear_kernel<kNt, kEpi, kCtas>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);

@@ -150,6 +150,10 @@ class TileEngine:
                 self.layer(i, l0, l1)
             return
         key = (n_layers, len0 is not None)
+        if key in self.graphs and self.graphs[key] is None:  # capture failed once for this shape: plain launches
+            for i in range(n_layers):
+                self.layer(i, l0, l1)
+            return
         g = self.graphs.get(key)
         if g is None:
             if self.eager_runs == 0:
@@ -160,9 +164,20 @@ class TileEngine:
                 return
             x_before, n0 = self.x, C.LAUNCHES
             graph = torch.cuda.CUDAGraph()
-            with torch.cuda.graph(graph):
+            try:
+                # thread_local: a CUDA call of ANOTHER host thread during the capture (a DataLoader pin_memory
+                # thread of the reference's export / eval loops) must not abort it
+                with torch.cuda.graph(graph, capture_error_mode="thread_local"):
+                    for i in range(n_layers):
+                        self.layer(i, l0, l1)
+            except RuntimeError:
+                # capture failed (e.g. an allocation raced it): this shape runs as plain launches from now on
+                C.LAUNCHES = n0
+                self.graphs[key] = None
+                torch.cuda.synchronize()
                 for i in range(n_layers):
                     self.layer(i, l0, l1)
+                return
             assert self.x is x_before, "an even number of buffer swaps per layer keeps x in place"
             g = self.graphs[key] = (graph, C.LAUNCHES - n0)
             C.LAUNCHES = n0  # capture launched nothing; replays account for the kernels below

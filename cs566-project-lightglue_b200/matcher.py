@@ -270,10 +270,15 @@ class LightGlue(nn.Module):
     def forward(self, data: dict) -> dict:
         for key in self.required_data_keys:
             assert key in data, f"Missing key {key} in data"
-        conf = self.conf
-        kpts0, kpts1 = data["keypoints0"], data["keypoints1"]
+        kpts0 = data["keypoints0"]
         if not kpts0.is_cuda:
             raise RuntimeError("b200glue LightGlue runs on CUDA (sm_100a) only; move the batch to the GPU")
+        with torch.cuda.device(kpts0.device):  # the C ABI launches on the current device's current stream
+            return self._forward(data)
+
+    def _forward(self, data: dict) -> dict:
+        conf = self.conf
+        kpts0, kpts1 = data["keypoints0"], data["keypoints1"]
         b, m, _ = kpts0.shape
         _, n, _ = kpts1.shape
         dev = kpts0.device

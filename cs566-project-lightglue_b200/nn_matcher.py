@@ -38,6 +38,18 @@ class NearestNeighborMatcher(nn.Module):
         if not d0.is_cuda:
             raise RuntimeError("b200glue NearestNeighborMatcher runs on CUDA (sm_100a) only; move the batch to the GPU")
         d0, d1 = d0.contiguous().float(), d1.contiguous().float()
+        D = d0.shape[-1]
+        if D != d1.shape[-1] or D > 256:
+            raise ValueError(f"NearestNeighborMatcher: descriptor width {D} / {d1.shape[-1]}: the similarity kernel takes "
+                             "equal widths up to 256")
+        if D < 256:  # the reference takes any width (its shipped NN configs use 128-d DISK / ALIKED descriptors):
+            # zero columns do not change a dot product
+            d0 = torch.nn.functional.pad(d0, (0, 256 - D))
+            d1 = torch.nn.functional.pad(d1, (0, 256 - D))
+        with torch.cuda.device(d0.device):
+            return self._match(data, d0, d1)
+
+    def _match(self, data, d0, d1):
         lens = [None if data.get(k) is None else torch.as_tensor(data[k], device=d0.device).to(torch.int32).contiguous()
                 for k in ("num_keypoints0", "num_keypoints1")]
         sim, la = C.nn_assign(d0, d1, *lens)

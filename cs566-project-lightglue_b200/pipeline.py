@@ -102,21 +102,24 @@ def unpack_pred(pred, batch):
 
 class HostPipeline:
     """`for pred in HostPipeline(model).run(batches)`: `batches` yields reference-style data dicts of (pinned) host
-    tensors, all of one shape; `pred` holds pinned host tensors for `keys`, valid until `depth` more batches have
-    been yielded."""
+    tensors; `pred` holds pinned host tensors for `keys`, valid until `depth` more batches have been yielded (the
+    results rotate through depth + 1 pinned slots).  The shape may change between batches (groups of
+    `pack_pairs` / `group_by_length` pad to different lengths): the batch in flight is drained and handed out first,
+    then the slots are re-allocated for the new shape."""
 
     def __init__(self, model, depth: int = 2, keys=RESULT_KEYS):
         self.model, self.depth, self.keys = model, max(2, int(depth)), tuple(keys)
         self.dev = next(model.parameters()).device
         if self.dev.type != "cuda":
             raise RuntimeError("HostPipeline needs the model on a CUDA device: there is no CPU path")
-        self.copy_in = torch.cuda.Stream(self.dev)
-        self.copy_out = torch.cuda.Stream(self.dev)
-        self.slots = None     # per slot: device input dict
-        self.outs = None      # per slot: pinned host result dict
-        self.in_ready = [torch.cuda.Event() for _ in range(self.depth)]
-        self.fwd_done = [torch.cuda.Event() for _ in range(self.depth)]
-        self.out_done = [torch.cuda.Event() for _ in range(self.depth)]
+        with torch.cuda.device(self.dev):
+            self.copy_in = torch.cuda.Stream(self.dev)
+            self.copy_out = torch.cuda.Stream(self.dev)
+            self.in_ready = [torch.cuda.Event() for _ in range(self.depth)]
+            self.fwd_done = [torch.cuda.Event() for _ in range(self.depth)]
+            self.out_done = [torch.cuda.Event() for _ in range(self.depth + 1)]
+        self.slots = None     # per input slot: device input dict
+        self.outs = None      # per output slot (depth + 1 of them): pinned host result dict
 
     def _alloc(self, batch):
         self.slots = [_map(batch, lambda v: torch.empty(v.shape, dtype=v.dtype, device=self.dev))
@@ -124,14 +127,24 @@ class HostPipeline:
         self.shapes = _map(batch, lambda v: (tuple(v.shape), v.dtype))
 
     def run(self, batches):
+        with torch.cuda.device(self.dev):
+            yield from self._run(batches)
+
+    def _run(self, batches):
         main = torch.cuda.current_stream(self.dev)
-        pending = None  # slot whose results have been queued but not yet yielded
-        for i, batch in enumerate(batches):
-            s = i % self.depth
+        pending = None  # output slot whose results have been queued but not yet yielded
+        i = 0           # batches since the last (re-)allocation: input slot i % depth, output slot i % (depth + 1)
+        for batch in batches:
             if self.slots is None or _map(batch, lambda v: (tuple(v.shape), v.dtype)) != self.shapes:
+                if pending is not None:  # hand out the batch in flight BEFORE its pinned slot is replaced
+                    self.out_done[pending].synchronize()
+                    yield self.outs[pending]
+                    pending = None
                 torch.cuda.synchronize(self.dev)
                 self._alloc(batch)
                 self.outs = None
+                i = 0
+            s, o = i % self.depth, i % (self.depth + 1)
             with torch.cuda.stream(self.copy_in):
                 if i >= self.depth:
                     self.copy_in.wait_event(self.fwd_done[s])   # forward(i - depth) has consumed this slot
@@ -144,17 +157,18 @@ class HostPipeline:
             self.fwd_done[s].record(main)
             if self.outs is None:
                 self.outs = [{k: torch.empty(pred[k].shape, dtype=pred[k].dtype).pin_memory() for k in self.keys}
-                             for _ in range(self.depth)]
+                             for _ in range(self.depth + 1)]
             with torch.cuda.stream(self.copy_out):
                 self.copy_out.wait_event(self.fwd_done[s])
                 for k in self.keys:
                     pred[k].record_stream(self.copy_out)
-                    self.outs[s][k].copy_(pred[k], non_blocking=True)
-                self.out_done[s].record(self.copy_out)
+                    self.outs[o][k].copy_(pred[k], non_blocking=True)
+                self.out_done[o].record(self.copy_out)
             if pending is not None:
                 self.out_done[pending].synchronize()
                 yield self.outs[pending]
-            pending = s
+            pending = o
+            i += 1
         if pending is not None:
             self.out_done[pending].synchronize()
             main.wait_stream(self.copy_out)

@@ -307,6 +307,30 @@ def test_host_pipeline_matches_direct_calls():
             assert torch.equal(a[k], b[k]), (i, k)
 
 
+def test_host_pipeline_shape_change_and_result_lifetime():
+    """A run whose batches change shape (groups of pack_pairs pad to different lengths): the batch in flight is handed
+    out before the pinned slots are re-allocated, nothing is lost or returned uninitialised; and a yielded result
+    stays valid, WITHOUT a clone, until `depth` more batches have been yielded."""
+    P = pkg("pipeline")
+    conf = {"filter_threshold": 0.1}
+    model = _model(conf, W.make_state_dict(conf, seed=0))
+    shapes = [(260, 190), (260, 190), (400, 300), (400, 300), (400, 300), (130, 260), (260, 190)]
+    batches = [W.make_inputs(2, m, n, seed=20 + i, correlated=0.6) for i, (m, n) in enumerate(shapes)]
+    want = [{k: model(_cuda(b))[k].cpu() for k in P.RESULT_KEYS} for b in batches]
+    pinned = [{k: ({kk: vv.pin_memory() for kk, vv in v.items()} if isinstance(v, dict) else v.pin_memory())
+               for k, v in b.items()} for b in batches]
+    depth, held, checked = 2, [], 0
+    for i, pred in enumerate(P.HostPipeline(model, depth=depth).run(iter(pinned))):
+        for k in P.RESULT_KEYS:
+            assert torch.equal(want[i][k], pred[k]), (i, k)
+        held.append((i, pred))
+        for j, old in held[-depth:]:  # the last `depth` results are still intact (same shape group or not)
+            for k in P.RESULT_KEYS:
+                assert torch.equal(want[j][k], old[k]), ("held", j, k)
+                checked += 1
+    assert len(held) == len(batches) and checked > 0
+
+
 @pytest.mark.parametrize("precision,la_tol", [("bf16", 1e-4), ("fp32", 1e-5)])
 def test_packed_pairs_reproduce_one_pair_per_call(precision, la_tol):
     """pipeline.pack_pairs + conf b200.condition = "valid": pairs with unequal keypoint counts in ONE padded batch give,

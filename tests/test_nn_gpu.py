@@ -79,3 +79,20 @@ def test_nn_matcher_large_batch_equals_one_pair_calls():
         one = model({"descriptors0": d0[b:b + 1], "descriptors1": d1[b:b + 1]})
         assert torch.equal(one["matches0"][0], pred["matches0"][b]) and torch.equal(one["matches1"][0], pred["matches1"][b])
         assert (one["log_assignment"][0] - pred["log_assignment"][b]).abs().max() < 1e-5
+
+
+def test_nn_matcher_128d_descriptors_vs_oracle():
+    """The reference's shipped NN configs (disk+NN, aliked+NN) use 128-d descriptors: any width up to 256 is taken
+    (zero-padded to the kernel's 256 columns); wider ones are refused with a clear error."""
+    conf = {"ratio_thresh": 0.9, "mutual_check": True}
+    data = W.make_inputs(2, 300, 257, d_in=128, seed=21, correlated=0.7)
+    ref = nn_oracle.forward(conf, data)
+    pred = pkg("nn_matcher").NearestNeighborMatcher(conf)(_cuda(data))
+    assert pred["similarity"].shape == ref["similarity"].shape
+    assert (pred["similarity"].cpu() - ref["similarity"]).abs().max() < 5e-6
+    assert (pred["log_assignment"].cpu() - ref["log_assignment"]).abs().max() < 3e-5
+    for k in ("matches0", "matches1"):
+        assert (pred[k].cpu() == ref[k]).float().mean() >= 0.998, k
+    wide = {"descriptors0": torch.zeros(1, 8, 320).cuda(), "descriptors1": torch.zeros(1, 8, 320).cuda()}
+    with pytest.raises(ValueError, match="width"):
+        pkg("nn_matcher").NearestNeighborMatcher(conf)(wide)
