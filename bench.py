@@ -428,7 +428,7 @@ def run_b200(a):
     assign_bytes = a.batch * ((a.kpts + 1) ** 2 * 4 + 2 * a.kpts * 256 * 4)
     hbm_peak = float(peaks.get("hbm_gbs", 6500.0))
     assign_gbs = assign_bytes / (assign_ms / 1e3) / 1e9
-    roofline_assign = {"kernel": "assign_strip_kernel<1> + reduce + assign_tmem_kernel<2> + filter_finalize (final_proj and logits included)",
+    roofline_assign = {"kernel": "assign_f16_kernel<1> (rows) + <1> (columns) + merge + assign_f16_kernel<2> + filter_finalize (final_proj and logits included)",
                        "bound": "hbm", "achieved": assign_gbs, "peak": hbm_peak, "unit": "GB/s",
                        "frac": assign_gbs / hbm_peak, "ms": assign_ms, "algorithmic_bytes": assign_bytes,
                        "share_of_step": assign_ms / (ms / a.steps)}
@@ -457,7 +457,7 @@ def run_b200(a):
         line = {
             "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": a.steps, "warmup": max(a.warmup, 3),
             "ms_per_step": ms / a.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
-            "dtype": "bf16 attention operands, 3-term split-bf16 linears and assignment, f32 accumulate / softmax / LayerNorm", "data": "synthetic",
+            "dtype": "bf16 attention operands, 3-term split-bf16 linears, fp16 similarity operands, f32 accumulate / softmax / LayerNorm", "data": "synthetic",
             "config": config_dict(a, world),
             "e2e": {"value": e2e, "unit": UNIT, "h2d_bytes_per_step": nbytes(host),
                     "d2h_bytes_per_step": sum(v.numel() * v.element_size() for v in out_host.values()),

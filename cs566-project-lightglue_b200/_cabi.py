@@ -43,6 +43,7 @@ SIGNATURES = {
     "lg_ffn_ln_gelu": (_I, [_P, _I, _P, _I, _P, _P, _P, _P, _F, _P, _I, _P]),
     "lg_linear_split": (_I, [_P, _I, _P, _I, _I, _P, _P, _P, _P, _I, _I, _P]),
     "lg_linear_f32": (_I, [_P, _I, _P, _I, _I, _P, _P, _P, _L, _I, _I, _P]),
+    "lg_linear_f16": (_I, [_P, _I, _P, _I, _I, _P, _P, _P, _I, _I, _P]),
     "lg_linear_qkv_self": (_I, [_P, _P, _P, _P, _P, _P, _P, _P, _P, _P, _I, _I, _I, _I, _P]),
     "lg_linear_qkv_cross": (_I, [_P, _P, _P, _P, _P, _P, _P, _I, _I, _I, _I, _P]),
     "lg_attention_tiles": (_I, [_P, _P, _P, _P, _I, _P, _P, _I, _I, _I, _I, _I, _I, _F, _P]),
@@ -53,8 +54,7 @@ SIGNATURES = {
     "lg_assign_keys": (_I, [_P, _P, _P, _P, _P, _P, _F, _P, _P, _P, _I, _I, _I, _P]),
     "lg_filter_from_keys": (_I, [_P, _P, _P, _F, _P, _P, _P, _P, _I, _I, _I, _P]),
     "lg_assign_tiles_ws_bytes": (_c.c_size_t, [_I, _I, _I]),
-    "lg_assign_tiles": (_I, [_P, _P, _I, _I, _P, _P, _P, _P, _F, _P, _P, _P, _I, _I, _I, _P]),
-    "lg_assign_tiles_tmem": (_I, [_P, _P, _I, _I, _P, _P, _P, _P, _F, _P, _P, _P, _I, _I, _I, _P]),
+    "lg_assign_tiles": (_I, [_P, _P, _I, _I, _P, _P, _P, _P, _F, _P, _L, _P, _P, _I, _I, _I, _P]),
     "lg_logit_rows": (_I, [_P, _P, _P, _P, _L, _P]),
     "lg_nn_assign": (_I, [_P, _P, _P, _P, _P, _P, _P, _I, _I, _I, _P]),
     "lg_nn_ws_bytes": (_c.c_size_t, [_I, _I, _I]),
@@ -238,9 +238,11 @@ def assign(md0, md1, z0, z1, m_len=None, n_len=None, prescale=0.25):
 
 
 def filter_matches(scores, th: float, m_len=None, n_len=None):
-    """scores (B, M+1, N+1) f32 contiguous -> m0 (B,M) i64, m1 (B,N) i64, ms0, ms1 f32."""
-    _f32c(scores, "scores")
+    """scores (B, M+1, N+1) f32, contiguous or a view of pitched rows (alloc_scores) -> m0 (B,M) i64, m1 (B,N) i64,
+    ms0, ms1 f32."""
+    assert scores.is_cuda and scores.dtype == torch.float32 and scores.stride(2) == 1
     B, M1, N1 = scores.shape
+    assert scores.stride(0) == M1 * scores.stride(1), "image pitch = (M+1) * row pitch"
     M, N = M1 - 1, N1 - 1
     dev = scores.device
     m0 = torch.empty(B, M, device=dev, dtype=torch.int64)
@@ -250,7 +252,7 @@ def filter_matches(scores, th: float, m_len=None, n_len=None):
     if M == 0 or N == 0:
         raise RuntimeError("filter_matches: empty inner matrix (the reference's max() raises too)")
     ws = torch.empty(lib().lg_filter_ws_bytes(B, M, N), device=dev, dtype=torch.uint8)
-    _check(lib().lg_filter_matches(_ptr(scores), N1, _ptr(_i32(m_len)), _ptr(_i32(n_len)), float(th), _ptr(m0),
+    _check(lib().lg_filter_matches(_ptr(scores), scores.stride(1), _ptr(_i32(m_len)), _ptr(_i32(n_len)), float(th), _ptr(m0),
                                    _ptr(m1), _ptr(ms0), _ptr(ms1), _ptr(ws), B, M, N, _stream()), "lg_filter_matches")
     _count(2)
     return m0, m1, ms0, ms1
@@ -310,23 +312,34 @@ def logit_rows(x, w, bias):
     return out
 
 
-def assign_tiles(a_tiles, b_tiles, tpa, tpb, z0, z1, th=None, m_len=None, n_len=None, scale=1.0 / 16, impl=None):
-    """lg_assign_tiles: split tiles of final_proj(desc0 / desc1) (image b at row tile b*tpa / b*tpb), z0 (B,M), z1 (B,N)
-    -> log assignment (B,M+1,N+1); with `th` also the filter_matches outputs (keys gathered in pass 2).
-    impl="tmem" calls the variant that keeps the image-0 row tile in tensor memory (lg_assign_tiles_tmem)."""
-    assert impl in (None, "tmem")
-    entry = "lg_assign_tiles_tmem" if impl == "tmem" else "lg_assign_tiles"
+def scores_pitch(n: int) -> int:
+    """Row pitch (floats) of a log_assignment buffer with n+1 columns: a multiple of 32, so that every row and every
+    64-byte segment the assignment kernel stores starts on a 128-byte line."""
+    return (n + 1 + 31) // 32 * 32
+
+
+def alloc_scores(B: int, M: int, N: int, device):
+    """-> (storage (B, M+1, pitch), the (B, M+1, N+1) view callers see).  The reference's contract is shape and dtype
+    (lightglue.py:567-577); the padding columns are never written."""
+    buf = torch.empty(B, M + 1, scores_pitch(N), device=device, dtype=torch.float32)
+    return buf, buf[:, :, : N + 1]
+
+
+def assign_tiles(a_tiles, b_tiles, tpa, tpb, z0, z1, th=None, m_len=None, n_len=None, scale=1.0 / 16):
+    """lg_assign_tiles: fp16 tiles of final_proj(desc0 / desc1) (linear_f16; image b at row tile b*tpa / b*tpb), z0 (B,M),
+    z1 (B,N) -> log assignment (B,M+1,N+1) (a view of rows pitched to 128 bytes); with `th` also the filter_matches
+    outputs (keys gathered while the values are written)."""
     B, M = z0.shape
     N = z1.shape[1]
     dev = z0.device
-    scores = torch.empty(B, M + 1, N + 1, device=dev, dtype=torch.float32)
+    buf, scores = alloc_scores(B, M, N, dev)
     ws = torch.empty(lib().lg_assign_tiles_ws_bytes(B, M, N), device=dev, dtype=torch.uint8)
     keys = None if th is None else torch.empty(lib().lg_filter_ws_bytes(B, M, N), device=dev, dtype=torch.uint8)
     ml, nl = _i32(m_len), _i32(n_len)
-    _check(getattr(lib(), entry)(_ptr(a_tiles), _ptr(b_tiles), int(tpa), int(tpb), _ptr(_f32c(z0, "z0")),
-                                 _ptr(_f32c(z1, "z1")), _ptr(ml), _ptr(nl), float(scale), _ptr(scores), _ptr(ws),
-                                 _ptr(keys), B, M, N, _stream()), entry)
-    _count(3)
+    _check(lib().lg_assign_tiles(_ptr(a_tiles), _ptr(b_tiles), int(tpa), int(tpb), _ptr(_f32c(z0, "z0")),
+                                 _ptr(_f32c(z1, "z1")), _ptr(ml), _ptr(nl), float(scale), _ptr(buf), buf.shape[2],
+                                 _ptr(ws), _ptr(keys), B, M, N, _stream()), "lg_assign_tiles")
+    _count(4)
     if th is None:
         return scores
     m0 = torch.empty(B, M, device=dev, dtype=torch.int64)
@@ -382,7 +395,7 @@ SPLIT_ATOM = 32768
 
 
 def alloc_bf16_tiles(row_tiles: int, k: int, device):
-    """Plain bf16 activation tiles [row_tiles][k/64][16 KB] (hi-only GEMM operand)."""
+    """Plain 16-bit activation tiles [row_tiles][k/64][16 KB] (bf16 hi-only GEMM operand, or the fp16 tiles of linear_f16)."""
     return torch.empty(row_tiles, k // 64, TILE_BYTES, device=device, dtype=torch.uint8)
 
 
@@ -458,6 +471,17 @@ def linear_split(a0, w, bias, n_out: int, a1=None, resid=None, out=None, a1_hi_o
     _check(lib().lg_linear_split(_ptr(a0), a0.shape[1], _ptr(a1), 0 if a1 is None else a1.shape[1], int(a1_hi_only), _ptr(w),
                                  _ptr(_f32c(bias, "bias")), _ptr(resid), _ptr(out), rt, n_out, _stream()),
            "lg_linear_split")
+    _count(1)
+    return out
+
+
+def linear_f16(a0, w, bias, n_out: int, a1=None, out=None, a1_hi_only=False):
+    """[a0 | a1] . w^T + bias -> plain fp16 tiles (row_tiles, n_out/64, 16 KB): the operands of assign_tiles."""
+    rt = a0.shape[0]
+    if out is None:
+        out = alloc_bf16_tiles(rt, n_out, a0.device)
+    _check(lib().lg_linear_f16(_ptr(a0), a0.shape[1], _ptr(a1), 0 if a1 is None else a1.shape[1], int(a1_hi_only), _ptr(w),
+                               _ptr(_f32c(bias, "bias")), _ptr(out), rt, n_out, _stream()), "lg_linear_f16")
     _count(1)
     return out
 

@@ -28,6 +28,7 @@
 #include <cstdlib>
 
 #include "lg_common.cuh"
+#include <cuda_fp16.h>
 #include "lg_tiles.cuh"
 #include "lg_b200.h"
 
@@ -38,7 +39,7 @@ constexpr int kLinMaxStages = 4;
 constexpr int kLinSmemMax = 232448;  // 227 KB per CTA
 constexpr int kStageOut = 32768;    // epilogue staging (one split atom, or two bf16 tiles)
 
-enum LinearEpilogue { kEpiSplit = 0, kEpiF32 = 1, kEpiQkvSelf = 2, kEpiQkvCross = 3 };
+enum LinearEpilogue { kEpiSplit = 0, kEpiF32 = 1, kEpiQkvSelf = 2, kEpiQkvCross = 3, kEpiF16 = 4 };
 
 struct LinearParams {
   const uint8_t* a0;       // A source 0: [row_tiles][a0_atoms][32 KB]
@@ -386,6 +387,36 @@ __global__ void __launch_bounds__(kLinThreads, 1) linear_kernel(const LinearPara
           epi_bar_sync();
           if (leader) { bulk_s2g(p.out_tiles + goff, ob, kSplitAtom); bulk_commit(); }
         }
+      } else if (kEpi == kEpiF16) {
+        // ---------------------------------------------------------------- plain fp16 tiles [rt][n_out/64][16 KB]
+        // (final_proj for the single-product fp16 similarity of lg_assign_tiles; values clamped to the fp16 range)
+        const int out_atoms = p.n_tiles * kGroups;
+#pragma unroll 1
+        for (int j = 0; j < kGroups; ++j) {
+          uint8_t* sb = stg + (sbi++ & 1) * kHalfAtom;
+          if (leader) bulk_wait_read<1>();  // the store issued two atoms ago has drained this half
+          epi_bar_sync();
+          next_group(j);
+#pragma unroll
+          for (int c = 0; c < 4; ++c) {
+            float2 x[4];
+            biased8(j, c, x);
+            uint32_t h[4];
+#pragma unroll
+            for (int i = 0; i < 4; ++i) {
+              const __half2 v = __floats2half2_rn(fminf(fmaxf(x[i].x, -65504.f), 65504.f),
+                                                  fminf(fmaxf(x[i].y, -65504.f), 65504.f));
+              h[i] = *reinterpret_cast<const uint32_t*>(&v);
+            }
+            *reinterpret_cast<uint4*>(sb + sw128_offset(r, g * 4 + c)) = make_uint4(h[0], h[1], h[2], h[3]);
+          }
+          fence_proxy_async_smem();
+          epi_bar_sync();
+          if (leader) {
+            bulk_s2g(p.out_tiles + (static_cast<size_t>(rt) * out_atoms + nt * kGroups + j) * kHalfAtom, sb, kHalfAtom);
+            bulk_commit();
+          }
+        }
       } else {
         // ---------------------------------------------------------------- attention operand tiles
         // kEpiQkvSelf : n tile == head; columns [q 64 | k 64 | v 64]; rotary on q, k
@@ -708,6 +739,18 @@ extern "C" int lg_linear_split(const void* a0, int a0_atoms, const void* a1, int
   p.w = static_cast<const uint8_t*>(w); p.bias = bias; p.row_tiles = row_tiles; p.n_tiles = n_out / 256;
   p.out_tiles = static_cast<uint8_t*>(out_tiles); p.resid_tiles = static_cast<const uint8_t*>(resid_tiles);
   return lg::launch_linear<256, lg::kEpiSplit>(p, stream);
+}
+
+extern "C" int lg_linear_f16(const void* a0, int a0_atoms, const void* a1, int a1_atoms, int a1_hi_only, const void* w,
+                             const float* bias, void* out_tiles, int row_tiles, int n_out, cudaStream_t stream) {
+  if (int e = check_linear(a0, a0_atoms, a1, a1_atoms, w, bias, row_tiles, n_out, 256)) return e;
+  if (!out_tiles) return LG_ERR_NULL;
+  lg::LinearParams p{};
+  p.a0 = static_cast<const uint8_t*>(a0); p.a1 = static_cast<const uint8_t*>(a1);
+  p.a0_atoms = a0_atoms; p.a1_atoms = a1_atoms; p.a1_hi_only = a1_hi_only;
+  p.w = static_cast<const uint8_t*>(w); p.bias = bias; p.row_tiles = row_tiles; p.n_tiles = n_out / 256;
+  p.out_tiles = static_cast<uint8_t*>(out_tiles);
+  return lg::launch_linear<256, lg::kEpiF16>(p, stream);
 }
 
 extern "C" int lg_linear_f32(const void* a0, int a0_atoms, const void* a1, int a1_atoms, int a1_hi_only, const void* w,

@@ -191,12 +191,12 @@ class TileEngine:
                 C.tiles_to_rows(self.x[self.rt0:], self.B, self.N, 256, self.tp1))
 
     def final_proj_tiles(self, i: int):
-        """MatchAssignment.final_proj of head i (lightglue.py:310) as split tiles, the operand format of lg_assign_tiles:
+        """MatchAssignment.final_proj of head i (lightglue.py:310) as fp16 tiles, the operand format of lg_assign_tiles:
         -> (tiles of image side 0, tiles of side 1), image b at row tile b*tp0 / b*tp1."""
         w, b = self.pk.final[i]
         if getattr(self, "md", None) is None:
-            self.md = C.alloc_split(self.rt, 256, self.dev)
-        C.linear_split(self.x, w, b, 256, out=self.md)
+            self.md = C.alloc_bf16_tiles(self.rt, 256, self.dev)
+        C.linear_f16(self.x, w, b, 256, out=self.md)
         return self.md[: self.rt0], self.md[self.rt0:]
 
     def final_proj(self, i: int):

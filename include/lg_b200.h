@@ -117,6 +117,10 @@ int lg_linear_split(const void* a0, int a0_atoms, const void* a1, int a1_atoms, 
                     const void* resid_tiles, void* out_tiles, int row_tiles, int n_out, cudaStream_t stream);
 int lg_linear_f32(const void* a0, int a0_atoms, const void* a1, int a1_atoms, int a1_hi_only, const void* w, const float* bias,
                   float* out, int64_t ld, int row_tiles, int n_out, cudaStream_t stream);
+/* the same with the output as plain fp16 tiles [row_tiles][n_out/64][16 KB] (values clamped to the fp16 range): the
+ * operand format of lg_assign_tiles (final_proj, lightglue.py:310) */
+int lg_linear_f16(const void* a0, int a0_atoms, const void* a1, int a1_atoms, int a1_hi_only, const void* w, const float* bias,
+                  void* out_tiles, int row_tiles, int n_out, cudaStream_t stream);
 
 /* SelfBlock Wqkv + head split + rotary (lightglue.py:184-188) -> lg_attention operand tiles.  a: split tiles
  * of x, K = 256, rows = image-0 batch (B*tp0 tiles) then image-1 batch (B*tp1 tiles; tp1 may be 0).
@@ -186,24 +190,19 @@ int lg_assign_keys(const float* md0, const float* md1, const float* z0, const fl
 int lg_filter_from_keys(const void* keys_ws, const int* m_len, const int* n_len, float th, int64_t* m0, int64_t* m1,
                         float* ms0, float* ms1, int B, int M, int N, cudaStream_t stream);
 
-/* (3)+(4) from split tiles: the same MatchAssignment (lightglue.py:306-315) + sigmoid_log_double_softmax
- * (:284-296) (+ filter keys when keys_ws != NULL, lg_filter_ws_bytes(B,M,N) bytes, zeroed by the call), but the
- * operands are the split-bf16 row tiles lg_linear_split writes for final_proj (image b of side 0 starts at row
- * tile b*tpa of a_tiles, side 1 at b*tpb of b_tiles; 256 columns = 4 atoms): no fp32 rows, no pack pass, the
- * row tile of image 0 stays resident in shared memory while the column tiles stream.  similarity =
- * scale * <a_row, b_row> (scale = d^-1/2 for the reference's two d^-1/4 factors, lightglue.py:311-312), 3-term
- * split-bf16 products (~1e-5 abs on |sim| ~ 10; lg_assign keeps the TF32x3 variant).  z0 (B,M), z1 (B,N) =
- * matchability logits (lg_logit_rows).  ws: lg_assign_tiles_ws_bytes(B,M,N) bytes. */
+/* (3)+(4) from fp16 tiles, the matcher's path: MatchAssignment (lightglue.py:306-315) + sigmoid_log_double_softmax
+ * (:284-296) (+ filter keys when keys_ws != NULL, lg_filter_ws_bytes(B,M,N) bytes, zeroed by the call).  Operands are
+ * the fp16 tiles lg_linear_f16 writes for final_proj ([row tile][4 atoms][16 KB]; image b of side 0 starts at row
+ * tile b*tpa of a_tiles, side 1 at b*tpb of b_tiles): no fp32 rows, no pack pass, ONE tcgen05 kind::f16 product per
+ * K step (11-bit operands: ~1e-3 on log_assignment inside the bf16 path's 2e-2 bound; lg_assign keeps TF32x3 for the
+ * fp32 path).  similarity = scale * <a_row, b_row> (scale = d^-1/2 for the reference's two d^-1/4 factors,
+ * lightglue.py:311-312).  z0 (B,M), z1 (B,N) = matchability logits (lg_logit_rows).  scores: (B, M+1, pitch) f32,
+ * row pitch in floats >= N+1 and a multiple of 4 (16-byte vector stores; a multiple of 32 makes every stored 64-byte
+ * segment two whole sectors); columns N+1 .. pitch-1 are never written.  ws: lg_assign_tiles_ws_bytes(B,M,N) bytes. */
 size_t lg_assign_tiles_ws_bytes(int B, int M, int N);
 int lg_assign_tiles(const void* a_tiles, const void* b_tiles, int tpa, int tpb, const float* z0, const float* z1,
-                    const int* m_len, const int* n_len, float scale, float* scores, void* ws, void* keys_ws, int B,
-                    int M, int N, cudaStream_t stream);
-/* Same contract, the variant that keeps the image-0 row tile in TENSOR MEMORY (tcgen05.mma A operand from TMEM, 64-
- * column tiles of image 1 streamed through shared memory).  lg_assign_tiles dispatches here when the environment has
- * LG_ASSIGN_IMPL=tmem; exported so that the parity tests can call both. */
-int lg_assign_tiles_tmem(const void* a_tiles, const void* b_tiles, int tpa, int tpb, const float* z0, const float* z1,
-                         const int* m_len, const int* n_len, float scale, float* scores, void* ws, void* keys_ws,
-                         int B, int M, int N, cudaStream_t stream);
+                    const int* m_len, const int* n_len, float scale, float* scores, int64_t pitch, void* ws,
+                    void* keys_ws, int B, int M, int N, cudaStream_t stream);
 
 /* Linear(256 -> 1) logits of every row: out[i] = <x[i,:], w> + bias[0]  (MatchAssignment.matchability,
  * lightglue.py:304,313-314, before the log-sigmoid).  x (rows, 256) f32 contiguous. */

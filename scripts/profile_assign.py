@@ -1,15 +1,20 @@
-"""Assignment + filter at the bench shape (32 pairs x 2048 x 2048): TF32x3 tile kernels vs the split-bf16 strip
-kernels (the matcher's path).  ncu: -k regex:assign_strip -c 2 captures pass 1 and pass 2 of the first strip call."""
+"""Assignment + filter at the bench shape (32 pairs x 2048 x 2048): the fp16-tile kernels of the matcher's path
+(lg_assign_f16.cu) and, with LG_PROFILE_TF32=1, the TF32x3 kernels of the fp32 path.
+ncu: -k regex:assign_f16 -c 4 captures stats<rows>, stats<cols>, merge is a separate kernel, write."""
 import importlib, os, sys
 import torch
 sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 C = importlib.import_module("cs566-project-lightglue_b200._cabi")
-B, N = 32, 2048
+B = int(sys.argv[1]) if len(sys.argv) > 1 else 32
+N = int(sys.argv[2]) if len(sys.argv) > 2 else 2048
 g = torch.Generator().manual_seed(0)
-md0, md1 = torch.randn(B, N, 256, generator=g).cuda(), torch.randn(B, N, 256, generator=g).cuda()
+x0, x1 = torch.randn(B, N, 256, generator=g).cuda(), torch.randn(B, N, 256, generator=g).cuda()
 z0, z1 = torch.randn(B, N, generator=g).cuda(), torch.randn(B, N, generator=g).cuda()
 tp = C.tiles_pad(N)
-a, b = C.rows_to_tiles(md0, tp), C.rows_to_tiles(md1, tp)
+w = C.pack_weight((torch.randn(256, 256, generator=g) / 16).cuda())
+bias = torch.zeros(256).cuda()
+a = C.linear_f16(C.rows_to_tiles(x0, tp), w, bias, 256)  # fp16 operand tiles, as final_proj writes them
+b = C.linear_f16(C.rows_to_tiles(x1, tp), w, bias, 256)
 
 
 def timeit(fn, reps=10):
@@ -25,10 +30,13 @@ def timeit(fn, reps=10):
     return e0.elapsed_time(e1) / reps
 
 
-IMPL = "tmem" if os.environ.get("LG_PROFILE_IMPL") == "tmem" else None  # ncu: -k regex:assign_tmem for this variant
-print(f"assign_tiles + keys        {timeit(lambda: C.assign_tiles(a, b, tp, tp, z0, z1, 0.1, impl=IMPL)):.3f} ms")
-print(f"assign_tiles               {timeit(lambda: C.assign_tiles(a, b, tp, tp, z0, z1, impl=IMPL)):.3f} ms")
+t_keys = timeit(lambda: C.assign_tiles(a, b, tp, tp, z0, z1, 0.1))
+t_plain = timeit(lambda: C.assign_tiles(a, b, tp, tp, z0, z1))
+gb = B * (N + 1) * (N + 1) * 4 / 1e9
+print(f"assign_tiles + keys        {t_keys:.3f} ms   ({gb / t_keys * 1e3:.0f} GB/s of log_assignment written)")
+print(f"assign_tiles               {t_plain:.3f} ms   ({gb / t_plain * 1e3:.0f} GB/s)")
 if os.environ.get("LG_PROFILE_TF32"):
+    md0, md1 = x0, x1
     s = C.assign(md0, md1, z0, z1)
     print(f"assign (tf32x3)            {timeit(lambda: C.assign(md0, md1, z0, z1)):.3f} ms")
     print(f"filter_matches             {timeit(lambda: C.filter_matches(s, 0.1)):.3f} ms")
