@@ -31,9 +31,12 @@ namespace af {
 constexpr int kAtom = 16384;                 // [128 rows][64 halves]
 constexpr int kKAtoms = 4;                   // K = 256
 constexpr int kTileBytes = kKAtoms * kAtom;  // 64 KB: one 128 x 256 operand tile
-constexpr int kRT = 2;                       // row tiles per item
-constexpr int kStages1 = 3, kStages2 = 2;    // ring of column atoms: stats pass / write pass (HBM-bound: the 16 KB it
-                                             // gives up hold the per-warp column keys)
+// Stats pass: TWO row tiles per item stay resident (each streamed column atom feeds two MMAs: 32 KB of L2 -> SM
+// traffic per 128 x 128 tile) behind a 5-atom ring.  Write pass: bound by the HBM write of 64 KB per tile, not by
+// operand delivery: ONE row tile per item, a 6-atom ring, and four accumulators = four warpgroups in flight (each
+// takes every fourth tile), so the tensor core runs three tiles ahead of the stores.
+constexpr int kRT1 = 2, kRT2 = 1;
+constexpr int kStages1 = 5, kStages2 = 6;
 constexpr int kWGs = 4;
 constexpr int kEpiWarps = 4 * kWGs;
 constexpr int kThreads = 32 * (kEpiWarps + 2);
@@ -58,13 +61,13 @@ struct Params {
   unsigned long long* rowkey;
   unsigned long long* colkey;
   float scale;             // similarity = scale * <a, b>
-  int B, M, N, rt, ct, rt2, cw, chunks;
+  int B, M, N, rt, ct, rt2, cw, chunks;  // rt2: groups of kRT row tiles
 };
 
 struct __align__(8) Barriers {
   uint64_t a_full[kKAtoms], a_empty[kKAtoms];  // per K atom (both row tiles): the next item's rows stream in behind the last step
-  uint64_t full[kStages1], empty[kStages1];
-  uint64_t acc_full[2];      // per step parity: both accumulators of the step
+  uint64_t full[8], empty[8];
+  uint64_t acc_full[kWGs];   // stats pass: [step parity] (both accumulators of the step); write pass: [accumulator]
   uint64_t acc_empty[kWGs];  // per accumulator
   uint32_t tmem_base;
 };
@@ -72,17 +75,17 @@ struct __align__(8) Barriers {
 // write pass scratch: column terms [4 warpgroups][128] f32 + column keys [16 warps][128] u64 (one slot per warp: plain
 // stores, merged by the warpgroup at the end of the tile -- a 64-bit shared-memory atomicMax is a CAS loop)
 constexpr int kScratch = kWGs * kTile * 4 + kEpiWarps * kTile * 8;
-constexpr int kSmem = 1024 + kRT * kTileBytes + kStages1 * kAtom + kEpiWarps * kWarpStage + kWGs * kTile * 4 +
-                      static_cast<int>(sizeof(Barriers));
-static_assert(kSmem <= 232448, "shared memory budget");
-static_assert(1024 + kRT * kTileBytes + kStages2 * kAtom + kEpiWarps * kWarpStage + kScratch + static_cast<int>(sizeof(Barriers)) <= kSmem,
-              "the write pass fits the same allocation");
+constexpr int kSmem1 = 1024 + kRT1 * kTileBytes + kStages1 * kAtom + static_cast<int>(sizeof(Barriers));
+constexpr int kSmem2 = 1024 + kRT2 * kTileBytes + kStages2 * kAtom + kEpiWarps * kWarpStage + kScratch +
+                       static_cast<int>(sizeof(Barriers));
+static_assert(kSmem1 <= 232448 && kSmem2 <= 232448, "shared memory budget");
 
 struct Item {
-  int b, rp, c0, c1, n, nrt, nreal;  // row tiles 2rp, 2rp+1; nrt of them hold valid rows; the first nreal column tiles hold valid columns
-  int vrows[kRT];
+  int b, rp, c0, c1, n, nrt, nreal;  // row tiles RT*rp ..; nrt of them hold valid rows; the first nreal column tiles hold valid columns
+  int vrows[2];
 };
 
+template <int RT>
 __device__ __forceinline__ Item decode(const Params& p, int it) {
   Item t;
   const int chunk = it % p.chunks, br = it / p.chunks;
@@ -90,8 +93,8 @@ __device__ __forceinline__ Item decode(const Params& p, int it) {
   t.b = br / p.rt2;
   const int m = p.m_len ? min(p.m_len[t.b], p.M) : p.M;
   t.n = p.n_len ? min(p.n_len[t.b], p.N) : p.N;
-  t.vrows[0] = max(0, min(kTile, m - 2 * t.rp * kTile));
-  t.vrows[1] = max(0, min(kTile, m - (2 * t.rp + 1) * kTile));
+  t.vrows[0] = max(0, min(kTile, m - RT * t.rp * kTile));
+  t.vrows[1] = RT == 2 ? max(0, min(kTile, m - (RT * t.rp + 1) * kTile)) : 0;
   t.nrt = (t.vrows[0] > 0) + (t.vrows[1] > 0);
   t.c0 = chunk * p.cw;
   t.c1 = min(p.ct, t.c0 + p.cw);
@@ -124,12 +127,13 @@ template <int kPass>
 __global__ void __launch_bounds__(kThreads, 1) assign_f16_kernel(const Params p) {
   extern __shared__ uint8_t smem_raw[];
   uint8_t* base = smem_raw + ((1024u - (smem_u32(smem_raw) & 1023u)) & 1023u);
-  uint8_t* a_res = base;                                  // [2 row tiles][4 atoms][16 KB]
+  uint8_t* a_res = base;                                  // [RT row tiles][4 atoms][16 KB]
+  constexpr int RT = kPass == 1 ? kRT1 : kRT2;
   constexpr int kStages = kPass == 1 ? kStages1 : kStages2;
-  uint8_t* ring = a_res + kRT * kTileBytes;
-  uint8_t* wstage = ring + kStages * kAtom;
+  uint8_t* ring = a_res + RT * kTileBytes;
+  uint8_t* wstage = ring + kStages * kAtom;               // write pass only
   uint8_t* scratch = wstage + kEpiWarps * kWarpStage;
-  Barriers* bar = reinterpret_cast<Barriers*>(scratch + (kPass == 1 ? kWGs * kTile * 4 : kScratch));
+  Barriers* bar = reinterpret_cast<Barriers*>(kPass == 1 ? wstage : scratch + kScratch);
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int items = p.B * p.rt2 * p.chunks;
@@ -137,7 +141,7 @@ __global__ void __launch_bounds__(kThreads, 1) assign_f16_kernel(const Params p)
   if (threadIdx.x == 0) {
     for (int s = 0; s < kKAtoms; ++s) { mbar_init(&bar->a_full[s], 1); mbar_init(&bar->a_empty[s], 1); }
     for (int s = 0; s < kStages; ++s) { mbar_init(&bar->full[s], 1); mbar_init(&bar->empty[s], 1); }
-    for (int s = 0; s < 2; ++s) mbar_init(&bar->acc_full[s], 1);
+    for (int s = 0; s < kWGs; ++s) mbar_init(&bar->acc_full[s], 1);
     for (int s = 0; s < kWGs; ++s) mbar_init(&bar->acc_empty[s], kTile);
     fence_mbar_init();
   }
@@ -152,9 +156,9 @@ __global__ void __launch_bounds__(kThreads, 1) assign_f16_kernel(const Params p)
     if (lane == 0) {
       uint32_t g = 0, loaded = 0;
       for (int it = blockIdx.x; it < items; it += gridDim.x) {
-        const Item t = decode(p, it);
+        const Item t = decode<RT>(p, it);
         if (t.nreal == 0) continue;
-        const uint8_t* ga = p.a_tiles + (static_cast<size_t>(t.b) * p.tpa + 2 * t.rp) * kTileBytes;
+        const uint8_t* ga = p.a_tiles + (static_cast<size_t>(t.b) * p.tpa + RT * t.rp) * kTileBytes;
         for (int j = 0; j < t.nreal; ++j) {
           const uint8_t* gb = p.b_tiles + (static_cast<size_t>(t.b) * p.tpb + t.c0 + j) * kTileBytes;
           for (int ka = 0; ka < kKAtoms; ++ka) {
@@ -182,16 +186,21 @@ __global__ void __launch_bounds__(kThreads, 1) assign_f16_kernel(const Params p)
     const bool leader = elect_one();
     uint32_t g = 0, step = 0, loaded = 0;
     for (int it = blockIdx.x; it < items; it += gridDim.x) {
-      const Item t = decode(p, it);
+      const Item t = decode<RT>(p, it);
       if (t.nreal == 0) continue;
       for (int j = 0; j < t.nreal; ++j, ++step) {
-        const uint32_t par = step & 1;
-        // BOTH warpgroups of the parity have released the step before the last one -- also the row-tile-1 warpgroup of an
-        // item with one valid row tile, which holds no data but waits and arrives all the same: a warpgroup that
-        // skipped completions of acc_full[par] could no longer wait on it by parity
-        if (step >= 2) {
-          mbar_wait(&bar->acc_empty[2 * par], ((step >> 1) - 1) & 1);
-          mbar_wait(&bar->acc_empty[2 * par + 1], ((step >> 1) - 1) & 1);
+        // stats pass: accumulators 2*par + r of step parity par; write pass: accumulator step % 4
+        const uint32_t par = step & 1, acc0 = kPass == 1 ? 2 * par : (step & 3);
+        if (kPass == 1) {
+          // BOTH warpgroups of the parity have released the step before the last one -- also the row-tile-1 warpgroup of
+          // an item with one valid row tile, which holds no data but waits and arrives all the same: a warpgroup that
+          // skipped completions of acc_full[par] could no longer wait on it by parity
+          if (step >= 2) {
+            mbar_wait(&bar->acc_empty[2 * par], ((step >> 1) - 1) & 1);
+            mbar_wait(&bar->acc_empty[2 * par + 1], ((step >> 1) - 1) & 1);
+          }
+        } else if (step >= 4) {
+          mbar_wait(&bar->acc_empty[acc0], ((step >> 2) - 1) & 1);
         }
         tc_fence_after();
         for (int ka = 0; ka < kKAtoms; ++ka) {
@@ -205,7 +214,7 @@ __global__ void __launch_bounds__(kThreads, 1) assign_f16_kernel(const Params p)
               const uint64_t da = umma_desc_kmajor_sw128(a_addr + (r * kKAtoms + ka) * kAtom);
 #pragma unroll
               for (int kk = 0; kk < 4; ++kk)
-                umma_bf16_ss(tmem + (2 * par + r) * kTile, da + 2 * kk, db + 2 * kk, idesc, (ka > 0 || kk > 0));
+                umma_bf16_ss(tmem + (acc0 + r) * kTile, da + 2 * kk, db + 2 * kk, idesc, (ka > 0 || kk > 0));
             }
             umma_commit(&bar->empty[s]);
             if (j == t.nreal - 1) umma_commit(&bar->a_empty[ka]);  // this item is done with atom ka of its rows
@@ -213,7 +222,7 @@ __global__ void __launch_bounds__(kThreads, 1) assign_f16_kernel(const Params p)
           __syncwarp();
           ++g;
         }
-        if (leader) umma_commit(&bar->acc_full[par]);
+        if (leader) umma_commit(&bar->acc_full[kPass == 1 ? par : acc0]);
         __syncwarp();
       }
       ++loaded;
@@ -221,8 +230,8 @@ __global__ void __launch_bounds__(kThreads, 1) assign_f16_kernel(const Params p)
   } else {
     // ------------------------------------------------------------------ epilogue: thread == row (TMEM lane)
     const int wg = warp >> 2, wq = warp & 3;
-    const int r = wg & 1;                 // row tile of the item
-    const uint32_t par = wg >> 1;         // steps of this parity
+    const int r = wg & 1;                 // stats pass: row tile of the item ...
+    const uint32_t par = wg >> 1;         // ... and steps of this parity; write pass: warpgroup == accumulator == step % 4
     const int row = wq * 32 + lane;
     const uint32_t t_acc = tmem + (static_cast<uint32_t>(wq * 32) << 16) + wg * kTile;
     uint32_t gstep = 0;
@@ -232,7 +241,7 @@ __global__ void __launch_bounds__(kThreads, 1) assign_f16_kernel(const Params p)
       const float2 c2 = make_float2(c, c);
       const int np = 2 * p.chunks;
       for (int it = blockIdx.x; it < items; it += gridDim.x) {
-        const Item t = decode(p, it);
+        const Item t = decode<RT>(p, it);
         const int chunk = it % p.chunks;
         const int grow = (2 * t.rp + r) * kTile + row;
         const bool row_ok = row < t.vrows[r];
@@ -321,27 +330,21 @@ __global__ void __launch_bounds__(kThreads, 1) assign_f16_kernel(const Params p)
       const int64_t pitch = p.pitch;
       uint32_t pad = 0;
       for (int it = blockIdx.x; it < items; it += gridDim.x) {
-        const Item t = decode(p, it);
-        const int row0 = (2 * t.rp + r) * kTile;
+        const Item t = decode<RT>(p, it);
+        const int row0 = t.rp * kTile;
         const int grow = row0 + row;
-        const int vrows = t.vrows[r];
+        const int vrows = t.vrows[0];
         const bool row_ok = row < vrows;
-        const bool live = r < t.nrt;
+        const bool live = t.nrt > 0;
         float* out = p.scores + static_cast<int64_t>(t.b) * (p.M + 1) * pitch;
         const float rc = row_ok ? p.rowc[static_cast<size_t>(t.b) * p.M + grow] : 0.f;
         float rv = -INFINITY;
         uint32_t rci = kNone;
         for (int ctile = t.c0; ctile < t.c1; ++ctile) {
           const int j = ctile - t.c0, col0 = ctile * kTile;
-          if (!live && j < t.nreal && ((gstep + j) & 1) == par) {  // keep the hand-shake of the step going
-            mbar_wait(&bar->acc_full[par], ((gstep + j) >> 1) & 1);
-            tc_fence_before();
-            mbar_arrive(&bar->acc_empty[wg]);
-          }
           if (!live || j >= t.nreal) {
-            // rows or columns entirely in the padding of a variable-count batch: -inf, the two warpgroups of the row
-            // tile take turns
-            if ((pad++ & 1) != par) continue;
+            // rows or columns entirely in the padding of a variable-count batch: -inf, the warpgroups take turns
+            if ((pad++ & 3) != static_cast<uint32_t>(wg)) continue;
             for (int i = wq; i < kTile; i += 4)
               for (int q = 0; q < 4; ++q) {
                 const int rr = row0 + i, cc = col0 + q * 32 + lane;
@@ -350,11 +353,11 @@ __global__ void __launch_bounds__(kThreads, 1) assign_f16_kernel(const Params p)
             continue;
           }
           const uint32_t s = gstep + j;
-          if ((s & 1) != par) continue;
+          if ((s & 3) != static_cast<uint32_t>(wg)) continue;
           const int vcols = min(kTile, t.n - col0);        // columns that hold similarities
           const int scols = min(kTile, p.N - col0);        // columns that exist in the matrix
           s_colc[row] = row < vcols ? p.colc[static_cast<size_t>(t.b) * p.N + col0 + row] : 0.f;
-          mbar_wait(&bar->acc_full[par], (s >> 1) & 1);
+          mbar_wait(&bar->acc_full[wg], (s >> 2) & 1);
           tc_fence_after();
           asm volatile("bar.sync %0, 128;" ::"r"(bar_id) : "memory");  // column terms / key slots are in place
           // every element of this warp's 32 x 128 block valid and inside the matrix: no masks, vector stores
@@ -528,19 +531,20 @@ static inline size_t af_align256(size_t x) { return (x + 255) & ~static_cast<siz
 
 // column tiles per item: the fewer items, the less often the two row tiles (128 KB) are re-staged; the more items, the
 // better the last wave fills the SMs.  Minimise (bytes per tile) / (fill of the last wave).
-static int af_pick_cw(int B, int rt2, int ct, int sms) {
+static int af_pick_cw(int B, int rt2, int ct, int sms, int rt_per_item) {
+  const double stream_kb = 64.0 / rt_per_item;  // column-operand bytes per 128 x 128 tile
   int best = 1;
   double best_cost = 1e30;
   for (int cw = 1; cw <= ct; cw *= 2) {
     const long long items = static_cast<long long>(B) * rt2 * ((ct + cw - 1) / cw);
     const long long waves = (items + sms - 1) / sms;
     const double fill = static_cast<double>(items) / static_cast<double>(waves * sms);
-    const double cost = (32.0 + 64.0 / cw) / fill;
+    const double cost = (stream_kb + 64.0 / cw) / fill;
     if (cost < best_cost) { best_cost = cost; best = cw; }
     if (cw * 2 > ct && cw != ct) {  // also try "all column tiles in one item"
       const long long it2 = static_cast<long long>(B) * rt2;
       const long long w2 = (it2 + sms - 1) / sms;
-      const double c2 = (32.0 + 64.0 / ct) / (static_cast<double>(it2) / static_cast<double>(w2 * sms));
+      const double c2 = (stream_kb + 64.0 / ct) / (static_cast<double>(it2) / static_cast<double>(w2 * sms));
       if (c2 < best_cost) { best_cost = c2; best = ct; }
     }
   }
@@ -585,13 +589,13 @@ extern "C" int lg_assign_tiles(const void* a_tiles, const void* b_tiles, int tpa
   static bool attr_done_dev[lg::kMaxDevices] = {};
   bool& attr_done = attr_done_dev[lg::current_device_slot()];
   if (!attr_done) {
-    cudaError_t e = cudaFuncSetAttribute(assign_f16_kernel<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmem);
-    if (e == cudaSuccess) e = cudaFuncSetAttribute(assign_f16_kernel<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmem);
+    cudaError_t e = cudaFuncSetAttribute(assign_f16_kernel<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmem1);
+    if (e == cudaSuccess) e = cudaFuncSetAttribute(assign_f16_kernel<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmem2);
     if (e != cudaSuccess) return static_cast<int>(e);
     attr_done = true;
   }
   const int sms = lg::device_sm_count();
-  auto make = [&](bool swapped) {
+  auto make = [&](bool swapped, int rt_per_item) {
     Params p{};
     p.a_tiles = static_cast<const uint8_t*>(swapped ? b_tiles : a_tiles);
     p.b_tiles = static_cast<const uint8_t*>(swapped ? a_tiles : b_tiles);
@@ -599,8 +603,8 @@ extern "C" int lg_assign_tiles(const void* a_tiles, const void* b_tiles, int tpa
     p.m_len = swapped ? n_len : m_len; p.n_len = swapped ? m_len : n_len;
     p.scale = scale; p.B = B;
     p.M = swapped ? N : M; p.N = swapped ? M : N;
-    p.rt = (p.M + 127) / 128; p.ct = (p.N + 127) / 128; p.rt2 = (p.rt + 1) / 2;
-    p.cw = af_pick_cw(B, p.rt2, p.ct, sms);
+    p.rt = (p.M + 127) / 128; p.ct = (p.N + 127) / 128; p.rt2 = (p.rt + rt_per_item - 1) / rt_per_item;
+    p.cw = af_pick_cw(B, p.rt2, p.ct, sms, rt_per_item);
     p.chunks = (p.ct + p.cw - 1) / p.cw;
     return p;
   };
@@ -608,18 +612,18 @@ extern "C" int lg_assign_tiles(const void* a_tiles, const void* b_tiles, int tpa
     const long long items = static_cast<long long>(p.B) * p.rt2 * p.chunks;
     return static_cast<int>(items < sms ? items : sms);
   };
-  Params pr = make(false), pc = make(true);
-  if (static_cast<long long>(B) * pr.rt2 * pr.chunks > 0x7fffffffLL || static_cast<long long>(B) * pc.rt2 * pc.chunks > 0x7fffffffLL)
+  Params pr = make(false, kRT1), pc = make(true, kRT1), pw = make(false, kRT2);
+  if (static_cast<long long>(B) * pr.rt2 * pr.chunks > 0x7fffffffLL || static_cast<long long>(B) * pc.rt2 * pc.chunks > 0x7fffffffLL ||
+      static_cast<long long>(B) * pw.rt2 * pw.chunks > 0x7fffffffLL)
     return LG_ERR_SHAPE;
   pr.part = rpart;
   pc.part = cpart;
-  assign_f16_kernel<1><<<grid_of(pr), kThreads, kSmem, stream>>>(pr);
-  assign_f16_kernel<1><<<grid_of(pc), kThreads, kSmem, stream>>>(pc);
+  assign_f16_kernel<1><<<grid_of(pr), kThreads, kSmem1, stream>>>(pr);
+  assign_f16_kernel<1><<<grid_of(pc), kThreads, kSmem1, stream>>>(pc);
   const int pts = M > N ? M : N;
   assign_f16_merge_kernel<<<dim3((pts + 255) / 256, B), 256, 0, stream>>>(rpart, 2 * pr.chunks, cpart, 2 * pc.chunks, z0, z1,
                                                                          m_len, n_len, rowc, colc, scores, pitch, M, N);
-  Params pw = pr;
   pw.rowc = rowc; pw.colc = colc; pw.scores = scores; pw.pitch = pitch; pw.rowkey = rowkey; pw.colkey = colkey;
-  assign_f16_kernel<2><<<grid_of(pw), kThreads, kSmem, stream>>>(pw);
+  assign_f16_kernel<2><<<grid_of(pw), kThreads, kSmem2, stream>>>(pw);
   return static_cast<int>(cudaGetLastError());
 }
