@@ -22,6 +22,7 @@
 //     pass: the block's row sum bounds its largest P; only if a row sum reaches 2^60 is the block max
 //     computed, O and l rescaled and the sweep repeated (rare: a logit 2^60 above the row's reference).
 //     Epilogue O / l -> split bf16 tiles (or fp32 rows) overlaps the next item's first MMAs.
+#include <cstdlib>
 #include "lg_common.cuh"
 #include "lg_b200.h"
 
@@ -58,6 +59,12 @@ constexpr uint32_t kColS = 0, kColO = 384;  // TMEM column map: 3 rotating S buf
 #endif
 #ifndef LG_POLY_PAIRS
 #define LG_POLY_PAIRS 2  // pairs of every 4 (8 columns) whose exp2 runs as a polynomial on the FMA pipe: 1 = 25 %, 2 = 50 %
+#endif
+#ifndef LG_SPLIT_POLY
+#define LG_SPLIT_POLY 1  // split-row softmax: pairs of every 4 whose exp2 runs as a polynomial (0 .. 2)
+#endif
+#ifndef LG_SPLIT_ALT
+#define LG_SPLIT_ALT 0
 #endif
 #ifndef LG_STAGGER
 #define LG_STAGGER 0
@@ -173,6 +180,7 @@ struct __align__(8) AttnBarriers {
   uint64_t t0_free[2];  // [key block parity]: PV_0(j) retired, its S buffer may be overwritten
   uint64_t o_free[2];
   uint32_t tmem_base;
+  uint32_t oflag[4];  // split-row softmax: [tile][key block parity] a row sum of the block reached the limit
 };
 
 constexpr int kOutStage = 8 * 4096;  // per softmax warp: 32 rows x 128 B of the context tile, for bulk stores
@@ -201,7 +209,12 @@ __device__ __forceinline__ AttnItem attn_item(const AttnParams& p, int w) {
   return it;
 }
 
-__global__ void __launch_bounds__(kAttnThreads, 1) attention_kernel(const AttnParams p) {
+// kSplit: FOUR softmax warpgroups instead of two -- every query row is shared by two threads (64 of the 128 key
+// columns of a block each), so each scheduler holds four softmax warps whose MUFU / FMA work interleaves (two warps per
+// scheduler could not keep the MUFU unit busy: every warp sits in a dependent FFMA -> MUFU -> FADD chain).
+template <bool kSplit>
+__global__ void __launch_bounds__(kSplit ? 640 : kAttnThreads, 1) attention_kernel(const AttnParams p) {
+  constexpr int kSoft = kSplit ? 16 : 8;  // softmax warps; then producer, PV issuer, similarity issuer
   extern __shared__ uint8_t smem_raw[];
   uint8_t* base = smem_raw + ((1024u - (smem_u32(smem_raw) & 1023u)) & 1023u);  // 1 KB aligned, still provably shared
   uint8_t* sQ = base;                               // 2 buffers x (2 x 16 KB)
@@ -215,22 +228,25 @@ __global__ void __launch_bounds__(kAttnThreads, 1) attention_kernel(const AttnPa
   if (threadIdx.x == 0) {
     for (int i = 0; i < 2; ++i) {
       mbar_init(&bar->q_full[i], 1); mbar_init(&bar->q_empty[i], 1);
-      mbar_init(&bar->p_full[2 * i], LG_WARP_ARRIVE ? 4 : 1); mbar_init(&bar->p_full[2 * i + 1], LG_WARP_ARRIVE ? 4 : 1);
-      mbar_init(&bar->pv_done[i], 1); mbar_init(&bar->t0_free[i], 1); mbar_init(&bar->o_free[i], 128);
+      mbar_init(&bar->p_full[2 * i], kSplit ? 8 : (LG_WARP_ARRIVE ? 4 : 1));
+      mbar_init(&bar->p_full[2 * i + 1], kSplit ? 8 : (LG_WARP_ARRIVE ? 4 : 1));
+      mbar_init(&bar->pv_done[i], 1); mbar_init(&bar->t0_free[i], 1); mbar_init(&bar->o_free[i], kSplit ? 256 : 128);
+      bar->oflag[2 * i] = 0u; bar->oflag[2 * i + 1] = 0u;
     }
     for (int s = 0; s < kStages; ++s) { mbar_init(&bar->kv_full[s], 1); mbar_init(&bar->kv_empty[s], 1); }
     for (int i = 0; i < 3; ++i) mbar_init(&bar->s_full[i], 1);
     fence_mbar_init();
   }
-  if (warp == 9) tmem_alloc<512>(&bar->tmem_base);
+  if (warp == kSoft + 1) tmem_alloc<512>(&bar->tmem_base);
   tc_fence_before();
   __syncthreads();
   tc_fence_after();
   const uint32_t tmem = bar->tmem_base;
 
-  if (warp >= 8) {
-    reg_dec<88>();  // pool = 384 x 168: 128*(208+208+88) registers
-    if (warp == 8) {
+  if (warp >= kSoft) {
+    if (kSplit) reg_dec<64>();  // pool = 640 x 96: 512 * 104 + 128 * 64 registers
+    else reg_dec<88>();         // pool = 384 x 168: 128 * (208 + 208 + 88) registers
+    if (warp == kSoft) {
       // ---------------------------------------------------------------- producer
       if (lane == 0) {
         uint32_t kvi = 0;  // running K/V block counter (ring position), across items
@@ -260,7 +276,7 @@ __global__ void __launch_bounds__(kAttnThreads, 1) attention_kernel(const AttnPa
           ++cnt;
         }
       }
-    } else if (warp == 10) {
+    } else if (warp == kSoft + 2) {
       // ---------------------------------------------------------------- similarity issuer: S(G) = Q_t K_j^T
       // Two issuing warps (this one and the PV warp) instead of one: a single issuer measured 1250 cycles per half
       // step against 512 cycles of tensor work -- every ready mbarrier wait costs ~90 cycles, every tcgen05.commit
@@ -309,7 +325,7 @@ __global__ void __launch_bounds__(kAttnThreads, 1) attention_kernel(const AttnPa
         kv0 += it.nkt;
         ++cnt;
       }
-    } else if (warp == 9) {
+    } else if (warp == kSoft + 1) {
       // ---------------------------------------------------------------- PV issuer: O_t += P_t(j) V_j
       const bool leader = elect_one();
       constexpr uint32_t idesc_pv = umma_idesc(kFmtBF16, 128, 64);
@@ -359,6 +375,250 @@ __global__ void __launch_bounds__(kAttnThreads, 1) attention_kernel(const AttnPa
         ++p_cnt;
       }
     }
+  } else if constexpr (kSplit) {
+    reg_inc<104>();
+    // ------------------------------------------------------------------ softmax, two threads per row
+    // warpgroup = (tile t, column half h): thread (row r, half h) owns columns [64 h, 64 h + 64) of every S block of its
+    // row and columns [32 h, 32 h + 32) of O.  Both halves of a row use ONE reference max (exchanged through the
+    // pair's staging slice at the first block and in the rare rescale), keep their own partial row sums (added in the
+    // epilogue), and meet at a 256-thread barrier per block before P overwrites S: half 1's P lands on columns of S
+    // that half 0 reads.
+    const int wgid = warp >> 2, t = wgid >> 1, h = wgid & 1, wq = warp & 3;
+    const int r = wq * 32 + lane;                  // row == TMEM lane
+    const uint32_t lane_addr = static_cast<uint32_t>(wq * 32) << 16;
+    const uint32_t tS0 = tmem + lane_addr + kColS;
+    const uint32_t tO = tmem + lane_addr + kColO + t * 64 + h * 32;
+    const float c = p.scale_log2;
+    const float2 c2 = make_float2(c, c);
+    const uint32_t tile_bar = 9 + t;               // named barrier of the tile's 256 threads
+    uint8_t* slice = sOut + (t * 4 + wq) * 4096;   // the pair's staging slice: 32 rows x 128 B of the context tile image
+    float* xch = reinterpret_cast<float*>(slice);  // exchange words [half][lane] (only between bulk stores)
+    const bool issuer = h == 0 && lane == 0;       // issues the pair's bulk stores
+    uint32_t pk[32];                               // P of the block: this thread's 64 columns as packed bf16 pairs
+    uint32_t v[32];
+    uint32_t kv_base = 0, item_cnt = 0;
+    auto tile_sync = [&]() { asm volatile("bar.sync %0, 256;" ::"r"(tile_bar) : "memory"); };
+
+    for (int w = blockIdx.x; w < p.items; w += gridDim.x) {
+      const AttnItem it = attn_item(p, w);
+      const int row = (it.qt0 + t) * kTile + r;
+      const AttnSide& sd = p.side[it.s];
+      const int side_nq = sd.nq;
+      uint8_t* dt = p.out_tiles
+                        ? p.out_tiles + ((static_cast<size_t>(sd.out_rt_base + it.b * sd.tq_pad + it.qt0 + t) * p.H + it.h) * 32768)
+                        : nullptr;
+      float4* drow = sd.out ? reinterpret_cast<float4*>(sd.out + (static_cast<size_t>(it.b) * sd.nq + row) * row_stride +
+                                                        it.h * kHeadDim + h * 32)
+                            : nullptr;
+      if (it.skip) {  // nothing to attend from / to: rows are zero (reference: nan_to_num of an all-masked softmax)
+        if (dt) {
+#pragma unroll
+          for (int ch = 4 * h; ch < 4 * h + 4; ++ch) {
+            *reinterpret_cast<uint4*>(dt + sw128_offset(r, ch)) = make_uint4(0u, 0u, 0u, 0u);
+            *reinterpret_cast<uint4*>(dt + 16384 + sw128_offset(r, ch)) = make_uint4(0u, 0u, 0u, 0u);
+          }
+        } else if (row < side_nq) {
+#pragma unroll
+          for (int i = 0; i < 8; ++i) drow[i] = make_float4(0.f, 0.f, 0.f, 0.f);
+        }
+        continue;
+      }
+
+      float m_used = -INFINITY, l = 0.f;
+      for (int j = 0; j < it.nkt; ++j) {
+        const int rem = it.k_len - j * kTile - 64 * h;  // valid keys among this thread's 64 columns (may be <= 0)
+        const bool partial = rem < 64;
+        const uint32_t G = 2 * (kv_base + j) + t;       // global step: S buffer G % 3
+        const uint32_t tS = tS0 + (G % 3) * 128 + 64 * h;
+        uint32_t* oflag = &bar->oflag[2 * t + ((kv_base + j) & 1)];
+        if ((threadIdx.x & 127) == 0 && h == 0) TRACE(t * 3, kv_base + j);
+#if LG_SPLIT_ALT
+        // The two tiles take turns on the MUFU unit: tile 1 starts block n when tile 0 is half way through its block n,
+        // tile 0 starts block n+1 when tile 1 is half way through block n.  Left alone, tile 1 trails tile 0 by the
+        // latency of its similarity (~300 cycles): both sweep together at half the MUFU rate each and then sit in
+        // their P hand-off (barrier, TMEM store, wait for the next similarity: ~770 cycles) with the unit idle.
+        if (t == 1) asm volatile("bar.sync 11, 512;" ::: "memory");
+        else if (kv_base + j > 0) asm volatile("bar.sync 12, 512;" ::: "memory");
+        bool signalled = false;
+#endif
+        mbar_wait(&bar->s_full[G % 3], (G / 3) & 1);
+        tc_fence_after();
+        if ((threadIdx.x & 127) == 0 && h == 0) TRACE(t * 3 + 1, kv_base + j);
+        const bool first = j == 0;
+        float tile_sum = 0.f;
+
+        // one pass over this thread's 64 columns: P = exp2(S c - m c), half of the exponentials as polynomials
+        auto sweep = [&]() {
+          const float ms = m_used * c;
+          const float2 nms2 = make_float2(-ms, -ms);
+          const float cs252 = c * (1.f / 252.f), bs252 = fmaf(-ms, 1.f / 252.f, 0.5f);
+          float2 s0 = make_float2(0.f, 0.f), s1 = s0;
+#pragma unroll
+          for (int cb = 0; cb < 2; ++cb) {
+            tmem_ld32(tS + cb * 32, v);
+            tmem_wait_ld();
+            if (partial) {
+#pragma unroll
+              for (int i = 0; i < 32; ++i)
+                if (cb * 32 + i >= rem) v[i] = 0xff800000u;  // -inf: exp2 -> 0
+            }
+#if LG_SPLIT_POLY == 2
+#pragma unroll
+            for (int q = 0; q < 8; ++q) {  // 4 columns: one MUFU pair, one polynomial pair
+              const float2 ta = __ffma2_rn(make_float2(__uint_as_float(v[4 * q]), __uint_as_float(v[4 * q + 1])), c2, nms2);
+              const float2 ea = make_float2(ex2_approx(ta.x), ex2_approx(ta.y));
+              const float2 eb = exp2_poly2(__uint_as_float(v[4 * q + 2]), __uint_as_float(v[4 * q + 3]), cs252, bs252);
+              s0 = __fadd2_rn(s0, ea);
+              s1 = __fadd2_rn(s1, eb);
+              pk[cb * 16 + 2 * q] = pack_bf16x2(ea.x, ea.y);
+              pk[cb * 16 + 2 * q + 1] = pack_bf16x2(eb.x, eb.y);
+            }
+#else
+#pragma unroll
+            for (int q = 0; q < 4; ++q) {  // 8 columns: LG_SPLIT_POLY of the 4 pairs as polynomials, the others on MUFU
+#pragma unroll
+              for (int pi = 0; pi < 4; ++pi) {
+                const float xa = __uint_as_float(v[8 * q + 2 * pi]), xb = __uint_as_float(v[8 * q + 2 * pi + 1]);
+                float2 e;
+                if (pi < LG_SPLIT_POLY) {
+                  e = exp2_poly2(xa, xb, cs252, bs252);
+                } else {
+                  const float2 tt = __ffma2_rn(make_float2(xa, xb), c2, nms2);
+                  e = make_float2(ex2_approx(tt.x), ex2_approx(tt.y));
+                }
+                if (pi & 1) s1 = __fadd2_rn(s1, e); else s0 = __fadd2_rn(s0, e);
+                pk[cb * 16 + 4 * q + pi] = pack_bf16x2(e.x, e.y);
+              }
+            }
+#endif
+#if LG_SPLIT_ALT
+            if (cb == 0 && !signalled) {  // half way: once per block
+              signalled = true;
+              if (t == 0) asm volatile("bar.arrive 11, 512;" ::: "memory");
+              else asm volatile("bar.arrive 12, 512;" ::: "memory");
+            }
+#endif
+          }
+          tile_sum = (s0.x + s0.y) + (s1.x + s1.y);
+        };
+
+        bool exact = first;
+        if (!first) {
+          sweep();
+          if (threadIdx.x == 0) TRACE(16, kv_base + j);
+          // every P <= its row sum: below the limit nothing can have overflowed the bf16 / fp32 ranges
+          if (__any_sync(0xffffffffu, !(tile_sum < kSumLimit)) && lane == 0) *reinterpret_cast<volatile uint32_t*>(oflag) = 1u;
+          tile_sync();  // both halves are done reading S; the flag is visible
+          if (threadIdx.x == 0) TRACE(17, kv_base + j);
+          exact = *reinterpret_cast<volatile uint32_t*>(oflag) != 0u;
+        }
+        if (exact) {
+          // exact block max of the row (first block of an item, or a row sum that reached the limit): new reference
+          float mx = -INFINITY;
+#pragma unroll
+          for (int cb = 0; cb < 2; ++cb) {
+            tmem_ld32(tS + cb * 32, v);
+            tmem_wait_ld();
+#pragma unroll
+            for (int i = 0; i < 32; i += 2) {
+              const bool k0 = !partial || cb * 32 + i < rem, k1 = !partial || cb * 32 + i + 1 < rem;
+              mx = fmax3(mx, k0 ? __uint_as_float(v[i]) : -INFINITY, k1 ? __uint_as_float(v[i + 1]) : -INFINITY);
+            }
+          }
+          if (issuer) bulk_wait_read_all();  // the slice may still be read by the previous item's context stores
+          tile_sync();
+          const bool over = !(tile_sum < kSumLimit);  // (tile_sum is 0 in a first block)
+          xch[(h * 32 + lane) * 2] = mx;
+          xch[(h * 32 + lane) * 2 + 1] = over ? 1.f : 0.f;
+          tile_sync();
+          mx = fmaxf(mx, xch[((1 - h) * 32 + lane) * 2]);
+          // a ROW takes the new reference if either of its halves reached the limit (then the block max exceeds the old
+          // reference and alpha < 1); the other rows of the tile keep theirs -- a lower reference would scale O up
+          const bool need = first || over || xch[((1 - h) * 32 + lane) * 2 + 1] != 0.f;
+          float alpha = 1.f;
+          if (need) { alpha = first ? 0.f : ex2_approx((m_used - mx) * c); m_used = mx; }
+          l *= alpha;
+          if (!first) {
+            // O_t must be quiescent: PV_t(j-1) retired (kv_empty of block j-1 completes behind PV_1(j-1))
+            mbar_wait(&bar->kv_empty[(kv_base + j - 1) % kStages], ((kv_base + j - 1) / kStages) & 1);
+            tc_fence_after();
+            tmem_ld32(tO, v);
+            tmem_wait_ld();
+#pragma unroll
+            for (int i = 0; i < 32; ++i) v[i] = __float_as_uint(__uint_as_float(v[i]) * alpha);
+            tmem_st32(tO, v);
+            tmem_wait_st();
+          }
+          sweep();
+          tile_sync();  // both halves are done reading S (and with the exchange words)
+          if (!first && issuer && wq == 0) *reinterpret_cast<volatile uint32_t*>(oflag) = 0u;
+        }
+        l += tile_sum;
+        // P overwrites the first 64 columns of the S buffer (half h: columns 32 h .. 32 h + 31 = keys 64 h .. 64 h + 63)
+        tmem_st32(tS0 + (G % 3) * 128 + 32 * h, pk);
+        tmem_wait_st();
+        tc_fence_before();
+        __syncwarp();
+        if (lane == 0) mbar_arrive(&bar->p_full[2 * t + ((kv_base + j) & 1)]);  // 8 warp arrivals per block
+        if ((threadIdx.x & 127) == 0 && h == 0) TRACE(t * 3 + 2, kv_base + j);
+      }
+
+      // epilogue: O / l
+      mbar_wait(&bar->pv_done[t], item_cnt & 1);
+      ++item_cnt;
+      tc_fence_after();
+      tmem_ld32(tO, v);
+      tmem_wait_ld();
+      tc_fence_before();
+      mbar_arrive(&bar->o_free[t]);
+      kv_base += it.nkt;
+      // the row sum: this half's + the partner's
+      if (issuer) bulk_wait_read_all();
+      tile_sync();
+      xch[h * 32 + lane] = l;
+      tile_sync();
+      l += xch[(1 - h) * 32 + lane];
+      tile_sync();  // the staging below overwrites the exchange words
+      const float inv = (row < it.q_len) ? 1.f / l : 0.f;  // padded query rows -> 0
+      if (dt) {
+        // this thread's 32 context columns = 16-byte chunks 4 h .. 4 h + 3 of its row in the hi and the lo tile image
+        const uint32_t stg_row = smem_u32(slice) + lane * 128;
+        uint32_t lo_w[16];
+#pragma unroll
+        for (int q = 0; q < 4; ++q) {
+          uint32_t hh[4];
+#pragma unroll
+          for (int i = 0; i < 4; ++i) {
+            const float x0 = __uint_as_float(v[8 * q + 2 * i]) * inv, x1 = __uint_as_float(v[8 * q + 2 * i + 1]) * inv;
+            const __nv_bfloat16 h0 = __float2bfloat16_rn(x0), h1 = __float2bfloat16_rn(x1);
+            hh[i] = static_cast<uint32_t>(__bfloat16_as_ushort(h0)) | (static_cast<uint32_t>(__bfloat16_as_ushort(h1)) << 16);
+            lo_w[q * 4 + i] = pack_bf16x2(x0 - __bfloat162float(h0), x1 - __bfloat162float(h1));
+          }
+          st_shared_v4(stg_row + (((4 * h + q) ^ (lane & 7)) << 4), make_uint4(hh[0], hh[1], hh[2], hh[3]));
+        }
+        fence_proxy_async_smem();
+        tile_sync();
+        uint8_t* gdst = dt + wq * 4096;
+        if (issuer) { bulk_s2g(gdst, slice, 4096); bulk_commit(); bulk_wait_read_all(); }
+        tile_sync();
+#pragma unroll
+        for (int q = 0; q < 4; ++q)
+          st_shared_v4(stg_row + (((4 * h + q) ^ (lane & 7)) << 4),
+                       make_uint4(lo_w[4 * q], lo_w[4 * q + 1], lo_w[4 * q + 2], lo_w[4 * q + 3]));
+        fence_proxy_async_smem();
+        tile_sync();
+        if (issuer) { bulk_s2g(gdst + 16384, slice, 4096); bulk_commit(); }
+      } else if (row < side_nq) {
+#pragma unroll
+        for (int i = 0; i < 8; ++i)
+          drow[i] = make_float4(__uint_as_float(v[4 * i]) * inv, __uint_as_float(v[4 * i + 1]) * inv,
+                                __uint_as_float(v[4 * i + 2]) * inv, __uint_as_float(v[4 * i + 3]) * inv);
+      }
+    }
+#if LG_SPLIT_ALT
+    if (t == 0 && kv_base > 0) asm volatile("bar.sync 12, 512;" ::: "memory");  // absorbs tile 1's last half-way signal
+#endif
+    if (issuer) bulk_wait_all();  // outstanding context stores
   } else {
     reg_inc<208>();
     // ------------------------------------------------------------------ softmax warpgroups
@@ -849,7 +1109,7 @@ __global__ void __launch_bounds__(kAttnThreads, 1) attention_kernel(const AttnPa
   }
   tc_fence_before();
   __syncthreads();
-  if (warp == 9) tmem_dealloc<512>(tmem);
+  if (warp == kSoft + 1) tmem_dealloc<512>(tmem);
 }
 
 }  // namespace lg
@@ -876,8 +1136,10 @@ static int launch_attention(const AttnSideArgs* sides, int n_sides, void* out_ti
   bool& attr_done = attr_done_dev[lg::current_device_slot()];
   const int sms = lg::device_sm_count();
   if (!attr_done) {
-    cudaError_t e = cudaFuncSetAttribute(lg::attention_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+    cudaError_t e = cudaFuncSetAttribute(lg::attention_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                          lg::kAttnSmem);
+    if (e == cudaSuccess)
+      e = cudaFuncSetAttribute(lg::attention_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, lg::kAttnSmem);
     if (e != cudaSuccess) return static_cast<int>(e);
     attr_done = true;
   }
@@ -895,7 +1157,12 @@ static int launch_attention(const AttnSideArgs* sides, int n_sides, void* out_ti
   }
   if (items > 0x7fffffffLL) return LG_ERR_SHAPE;
   p.items = static_cast<int>(items);
-  lg::attention_kernel<<<p.items < sms ? p.items : sms, lg::kAttnThreads, lg::kAttnSmem, stream>>>(p);
+  static const bool split = [] {  // LG_ATTN_SPLIT=0: the two-warpgroup softmax (one thread per row)
+    const char* e = getenv("LG_ATTN_SPLIT");
+    return !(e && e[0] == '0');
+  }();
+  if (split) lg::attention_kernel<true><<<p.items < sms ? p.items : sms, 640, lg::kAttnSmem, stream>>>(p);
+  else lg::attention_kernel<false><<<p.items < sms ? p.items : sms, lg::kAttnThreads, lg::kAttnSmem, stream>>>(p);
   return static_cast<int>(cudaGetLastError());
 }
 

@@ -46,6 +46,8 @@ struct LinearParams {
   const uint8_t* a1;       // A source 1 (concatenated along K after a0), may be null
   int a0_atoms, a1_atoms;
   int a1_hi_only;          // a1 holds plain bf16 tiles [row_tiles][a1_atoms][16 KB] (no lo half): 2-term product
+  int one_term;            // hi . hi only: the lo halves of A and W are not even staged (half the operand bytes, a third
+                           // of the MMAs) -- for outputs that are rounded to bf16 attention operands anyway
   const uint8_t* w;        // [n_tiles][k_atoms][hi | lo][Nt*128]
   const float* bias;       // [n_tiles * Nt] (same row order as w)
   int row_tiles, n_tiles;
@@ -179,15 +181,18 @@ __global__ void __launch_bounds__(kLinThreads, 1) linear_kernel(const LinearPara
                                   ? p.a0 + (static_cast<size_t>(rt) * p.a0_atoms + ka) * kSplitAtom
                                   : p.a1 + (static_cast<size_t>(rt) * p.a1_atoms + (ka - p.a0_atoms)) *
                                                (hi_only ? kHalfAtom : kSplitAtom);
-          const uint32_t a_bytes = hi_only ? kHalfAtom : kSplitAtom;
-          mbar_arrive_expect_tx(&bar->full[s], a_bytes + 2 * kWPart);
+          const bool one = p.one_term != 0;
+          const uint32_t a_bytes = (hi_only || one) ? kHalfAtom : kSplitAtom;
+          mbar_arrive_expect_tx(&bar->full[s], a_bytes + (one ? 1 : 2) * kWPart);
           bulk_g2s(ring + s * kStage, ga, a_bytes, &bar->full[s]);
-          if (kCtas == 1) {
-            bulk_g2s(ring + s * kStage + kSplitAtom, gw + static_cast<size_t>(ka) * kWAtom, kWAtom, &bar->full[s]);
+          if (kCtas == 1) {  // hi block first, lo block behind it
+            bulk_g2s(ring + s * kStage + kSplitAtom, gw + static_cast<size_t>(ka) * kWAtom, one ? kWAtom / 2 : kWAtom,
+                     &bar->full[s]);
           } else {  // this CTA's half of the output columns: rows [rank * Nt/2, +Nt/2) of the hi and of the lo block
             bulk_g2s(ring + s * kStage + kSplitAtom, gw + static_cast<size_t>(ka) * kWAtom, kWPart, &bar->full[s]);
-            bulk_g2s(ring + s * kStage + kSplitAtom + kWPart, gw + static_cast<size_t>(ka) * kWAtom + kNt * 128, kWPart,
-                     &bar->full[s]);
+            if (!one)
+              bulk_g2s(ring + s * kStage + kSplitAtom + kWPart, gw + static_cast<size_t>(ka) * kWAtom + kNt * 128, kWPart,
+                       &bar->full[s]);
           }
         }
       }
@@ -228,6 +233,7 @@ __global__ void __launch_bounds__(kLinThreads, 1) linear_kernel(const LinearPara
             mbar_wait(&bar->peer_full[s], (it / kLinStages) & 1);
           }
           tc_fence_after();
+          const bool one = p.one_term != 0;
           const bool hi_only = ka >= p.a0_atoms && p.a1_hi_only;
           const uint32_t a_hi = ring_a + s * kStage, a_lo = a_hi + kHalfAtom;
           const uint32_t w_hi = a_hi + kSplitAtom, w_lo = w_hi + kWPart;
@@ -236,13 +242,13 @@ __global__ void __launch_bounds__(kLinThreads, 1) linear_kernel(const LinearPara
 #pragma unroll
           for (int kk = 0; kk < 4; ++kk) {  // 64 bf16 per atom = 4 x K16, 32 B per step
             if (kCtas == 2) {
-              if (leader && !hi_only) umma_bf16_ss_pair(acc, dal + 2 * kk, dwh + 2 * kk, idesc, (ka > 0 || kk > 0));
-              if (leader) umma_bf16_ss_pair(acc, dah + 2 * kk, dwl + 2 * kk, idesc, hi_only ? (ka > 0 || kk > 0) : 1);
-              if (leader) umma_bf16_ss_pair(acc, dah + 2 * kk, dwh + 2 * kk, idesc, 1);
+              if (leader && !hi_only && !one) umma_bf16_ss_pair(acc, dal + 2 * kk, dwh + 2 * kk, idesc, (ka > 0 || kk > 0));
+              if (leader && !one) umma_bf16_ss_pair(acc, dah + 2 * kk, dwl + 2 * kk, idesc, hi_only ? (ka > 0 || kk > 0) : 1);
+              if (leader) umma_bf16_ss_pair(acc, dah + 2 * kk, dwh + 2 * kk, idesc, one ? (ka > 0 || kk > 0) : 1);
             } else {
-              if (leader && !hi_only) umma_bf16_ss(acc, dal + 2 * kk, dwh + 2 * kk, idesc, (ka > 0 || kk > 0));
-              if (leader) umma_bf16_ss(acc, dah + 2 * kk, dwl + 2 * kk, idesc, hi_only ? (ka > 0 || kk > 0) : 1);
-              if (leader) umma_bf16_ss(acc, dah + 2 * kk, dwh + 2 * kk, idesc, 1);
+              if (leader && !hi_only && !one) umma_bf16_ss(acc, dal + 2 * kk, dwh + 2 * kk, idesc, (ka > 0 || kk > 0));
+              if (leader && !one) umma_bf16_ss(acc, dah + 2 * kk, dwl + 2 * kk, idesc, hi_only ? (ka > 0 || kk > 0) : 1);
+              if (leader) umma_bf16_ss(acc, dah + 2 * kk, dwh + 2 * kk, idesc, one ? (ka > 0 || kk > 0) : 1);
             }
           }
           if (leader) { if (kCtas == 2) umma_commit_pair(&bar->empty[s]); else umma_commit(&bar->empty[s]); }
@@ -657,6 +663,16 @@ static int launch_linear_n(const LinearParams& p, cudaStream_t stream) {
   return static_cast<int>(cudaLaunchKernelEx(&cfg, linear_kernel<kNt, kEpi, kCtas>, p));
 }
 
+// LG_QKV_TERMS=1 in the environment: Wqkv / to_qk|to_v as single hi.hi products (experiment)
+static int qkv_one_term() {
+  static int v = -1;
+  if (v < 0) {
+    const char* e = getenv("LG_QKV_TERMS");
+    v = (e && e[0] == '1') ? 1 : 0;
+  }
+  return v;
+}
+
 // LG_LINEAR_PAIR=0 in the environment forces the single-CTA kernels (A/B measurements)
 static bool pair_enabled() {
   static int v = -1;
@@ -779,6 +795,7 @@ extern "C" int lg_linear_qkv_self(const void* a, const void* w, const float* bia
   p.q_tiles[1] = static_cast<uint8_t*>(q1); p.k_tiles[1] = static_cast<uint8_t*>(k1); p.v_tiles[1] = static_cast<uint8_t*>(v1);
   p.rot_tiles = static_cast<const uint8_t*>(rot_tiles);
   p.B = B; p.H = H; p.tp0 = tp0; p.tp1 = tp1;
+  p.one_term = lg::qkv_one_term();
   return lg::launch_linear<192, lg::kEpiQkvSelf>(p, stream);
 }
 
@@ -793,5 +810,6 @@ extern "C" int lg_linear_qkv_cross(const void* a, const void* w, const float* bi
   p.q_tiles[0] = static_cast<uint8_t*>(qk0); p.v_tiles[0] = static_cast<uint8_t*>(v0);
   p.q_tiles[1] = static_cast<uint8_t*>(qk1); p.v_tiles[1] = static_cast<uint8_t*>(v1);
   p.B = B; p.H = H; p.tp0 = tp0; p.tp1 = tp1;
+  p.one_term = lg::qkv_one_term();
   return lg::launch_linear<256, lg::kEpiQkvCross>(p, stream);
 }

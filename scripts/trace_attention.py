@@ -27,7 +27,12 @@ print("item epilogues (per item: start, pv_done, o_free, stored) wg0 | wg1")
 for i in range(0, nb, 16):
     print(f"kv_base={i:3d} wg0 " + " ".join(f"{tr[8 + k, i] - t0:6d}" for k in range(4)) + " | wg1 " + " ".join(f"{tr[12 + k, i] - t0:6d}" for k in range(4)))
 
-if (tr[16] > 0).any():
+if os.environ.get("LG_TRACE_SPLIT"):
+    print("split softmax, tile 0 half 0 warp 0, cycles: wait S | sweep | tile barrier | P store + arrive | to next block || tile 1 lag")
+    for j in range(33, 47):
+        print(f"blk={j:3d} {tr[1, j] - tr[0, j]:5d} {tr[16, j] - tr[1, j]:5d} {tr[17, j] - tr[16, j]:5d} {tr[2, j] - tr[17, j]:5d} {tr[0, j + 1] - tr[2, j]:5d}"
+              f" || {tr[5, j] - tr[2, j]:6d}   period {tr[0, j + 1] - tr[0, j]:5d}")
+elif (tr[16] > 0).any():
     print("wg0 warp 0 inside a block, cycles after gotS: first chunk loaded | groups 0-2 | 3-6 | 7-10 | 11-15 + sums | P st issued | "
           "st waited + fenced | bar.sync + arrive | (pre of the next block)")
     for j in range(33, 47):
