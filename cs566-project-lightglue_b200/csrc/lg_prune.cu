@@ -200,3 +200,198 @@ extern "C" int lg_logit_rows(const float* x, const float* w, const float* bias, 
   lg::logit_rows_kernel<<<static_cast<unsigned>((rows + 31) / 32), 256, 0, stream>>>(x, w, bias, out, rows);
   return static_cast<int>(cudaGetLastError());
 }
+
+// ---------------------------------------------------------------------------------------------------------------
+// lg_score_prune_tiles: the adaptive step of one layer for a whole batch in ONE launch, directly on the engine's split
+// tiles (north_star (5): "fused confidence-MLP plus prefix-sum stream-compaction kernel"):
+//   token confidence + matchability of every valid token (TokenConfidence.forward :102-107, get_matchability :317-318)
+//   keep mask (get_pruning_mask :586-593), the count check_if_stop needs (:595-606),
+//   block-wide exclusive scan, and the order-preserving compaction of the kept tokens (:536-547): descriptor row
+//   (hi | lo bf16 split, 1 KB), rotary row (cos | sin, 256 B) and original index move to their new row of the OUTPUT
+//   tiles; prune[ind] + 1 goes to a copy of the counters (a pair that exits at this layer keeps the old ones: the
+//   reference breaks before pruning).  Rows behind the kept ones are zero-filled (padding must stay finite: the PV MMA
+//   multiplies masked keys by P = 0).
+// No fp32 rows, no tiles -> rows -> tiles round trip, no index_select: 1 KB read per token for the scores, 1.25 KB
+// read (L2-hot) + 1.25 KB written per kept token.  One CTA per image (side 0 images, then side 1).
+namespace lg {
+
+constexpr int kSpThreads = 1024;
+
+struct ScorePruneParams {
+  const uint8_t* x;      // split tiles [B*tp0 + B*tp1][4][32 KB]
+  const uint8_t* rot;    // [B*tp0 + B*tp1][cos 16 KB | sin 16 KB]
+  uint8_t* x_out;
+  uint8_t* rot_out;
+  const int64_t* ind[2];     // (B, n_cur) original index of every row; null = identity
+  int64_t* ind_out[2];
+  const int64_t* prune[2];   // (B, n_orig)
+  int64_t* prune_out[2];
+  const int* len[2];         // valid rows per image, null = n_cur
+  int* len_out[2];
+  int* counts;               // (B, 4): kept0, unconfident0, kept1, unconfident1
+  const float* w_tok; const float* b_tok; const float* w_match; const float* b_match;
+  float thr, min_match;
+  int do_prune, B, n_cur[2], tp[2], n_orig[2];
+};
+
+__global__ void __launch_bounds__(kSpThreads) score_prune_tiles_kernel(const ScorePruneParams p) {
+  extern __shared__ int s_pos[];  // [tp * 128]: keep flag, then destination row (or -1)
+  __shared__ int s_warp[32];
+  __shared__ int s_unconf;
+  const int side = blockIdx.x >= p.B, b = blockIdx.x - side * p.B;
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  const int n_cur = p.n_cur[side], tp = p.tp[side];
+  const int nv = p.len[side] ? min(p.len[side][b], n_cur) : n_cur;
+  const size_t tile0 = side ? static_cast<size_t>(p.B) * p.tp[0] + static_cast<size_t>(b) * tp : static_cast<size_t>(b) * tp;
+  const uint8_t* x = p.x + tile0 * 4 * 32768;
+  const uint8_t* rot = p.rot + tile0 * 32768;
+  if (threadIdx.x == 0) s_unconf = 0;
+  __syncthreads();
+
+  // lane -> (K atom, 16-byte chunk): always the same 8 features, their weights live in registers
+  const int atom = lane >> 3, chunk = lane & 7;
+  float wm[8], wt[8];
+#pragma unroll
+  for (int k = 0; k < 8; ++k) {
+    wm[k] = __ldg(p.w_match + atom * 64 + chunk * 8 + k);
+    wt[k] = p.w_tok ? __ldg(p.w_tok + atom * 64 + chunk * 8 + k) : 0.f;
+  }
+  const float bm = __ldg(p.b_match), bt = p.b_tok ? __ldg(p.b_tok) : 0.f;
+  int unconf = 0;
+  for (int i = warp; i < nv; i += kSpThreads / 32) {
+    const uint8_t* src = x + static_cast<size_t>(i >> 7) * 4 * 32768 + atom * 32768 + sw128_offset(i & 127, chunk);
+    const uint4 hi = __ldg(reinterpret_cast<const uint4*>(src)), lo = __ldg(reinterpret_cast<const uint4*>(src + 16384));
+    const uint32_t hh[4] = {hi.x, hi.y, hi.z, hi.w}, ll[4] = {lo.x, lo.y, lo.z, lo.w};
+    float sm = 0.f, st = 0.f;
+#pragma unroll
+    for (int k = 0; k < 4; ++k) {
+      const float x0 = __uint_as_float(hh[k] << 16) + __uint_as_float(ll[k] << 16);
+      const float x1 = __uint_as_float(hh[k] & 0xFFFF0000u) + __uint_as_float(ll[k] & 0xFFFF0000u);
+      sm = fmaf(x0, wm[2 * k], sm); sm = fmaf(x1, wm[2 * k + 1], sm);
+      st = fmaf(x0, wt[2 * k], st); st = fmaf(x1, wt[2 * k + 1], st);
+    }
+    sm = warp_sum(sm);
+    st = warp_sum(st);
+    if (lane == 0) {
+      const float match = sigmoidf(sm + bm);
+      bool keep = match > p.min_match;
+      if (p.w_tok) {
+        const float conf = sigmoidf(st + bt);
+        keep = keep || (conf <= p.thr);
+        unconf += conf < p.thr ? 1 : 0;
+      }
+      s_pos[i] = (keep || !p.do_prune) ? 1 : 0;
+    }
+  }
+  if (lane == 0 && unconf) atomicAdd(&s_unconf, unconf);
+  __syncthreads();
+
+  // exclusive scan of the keep flags: thread t owns rows [t * per, t * per + per)
+  const int per = (nv + kSpThreads - 1) / kSpThreads;
+  const int r0 = threadIdx.x * per, r1 = min(nv, r0 + per);
+  int mine = 0;
+  for (int i = r0; i < r1; ++i) mine += s_pos[i];
+  int incl = mine;
+#pragma unroll
+  for (int o = 1; o < 32; o <<= 1) {
+    const int v = __shfl_up_sync(0xffffffffu, incl, o);
+    if (lane >= o) incl += v;
+  }
+  if (lane == 31) s_warp[warp] = incl;
+  __syncthreads();
+  int before = incl - mine;
+  for (int w = 0; w < warp; ++w) before += s_warp[w];
+  int kept = 0;
+  for (int w = 0; w < 32; ++w) kept += s_warp[w];
+  for (int i = r0; i < r1; ++i) {
+    const int k = s_pos[i];
+    s_pos[i] = k ? before : -1;
+    before += k;
+  }
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    p.counts[4 * b + 2 * side] = kept;
+    p.counts[4 * b + 2 * side + 1] = s_unconf;
+    if (p.len_out[side]) p.len_out[side][b] = kept;
+  }
+  if (!p.do_prune) return;
+
+  // prune counters: copy, then + 1 on the kept original indices (below)
+  const int n_orig = p.n_orig[side];
+  const int64_t* pr = p.prune[side] + static_cast<size_t>(b) * n_orig;
+  int64_t* pro = p.prune_out[side] + static_cast<size_t>(b) * n_orig;
+  for (int i = threadIdx.x; i < n_orig; i += kSpThreads) pro[i] = pr[i];
+  __syncthreads();
+
+  uint8_t* xo = p.x_out + tile0 * 4 * 32768;
+  uint8_t* roto = p.rot_out + tile0 * 32768;
+  const int64_t* ind = p.ind[side] ? p.ind[side] + static_cast<size_t>(b) * n_cur : nullptr;
+  int64_t* indo = p.ind_out[side] + static_cast<size_t>(b) * n_cur;
+  for (int i = warp; i < nv; i += kSpThreads / 32) {
+    const int d = s_pos[i];
+    if (d < 0) continue;
+    const size_t so = static_cast<size_t>(i >> 7) * 4 * 32768 + atom * 32768 + sw128_offset(i & 127, chunk);
+    const size_t dof = static_cast<size_t>(d >> 7) * 4 * 32768 + atom * 32768 + sw128_offset(d & 127, chunk);
+    *reinterpret_cast<uint4*>(xo + dof) = __ldg(reinterpret_cast<const uint4*>(x + so));
+    *reinterpret_cast<uint4*>(xo + dof + 16384) = __ldg(reinterpret_cast<const uint4*>(x + so + 16384));
+    if (lane < 16) {  // rotary row: lanes 0-7 the cos chunks, 8-15 the sin chunks
+      const size_t rs = static_cast<size_t>(i >> 7) * 32768 + (lane >> 3) * 16384 + sw128_offset(i & 127, lane & 7);
+      const size_t rd = static_cast<size_t>(d >> 7) * 32768 + (lane >> 3) * 16384 + sw128_offset(d & 127, lane & 7);
+      *reinterpret_cast<uint4*>(roto + rd) = __ldg(reinterpret_cast<const uint4*>(rot + rs));
+    } else if (lane == 16) {
+      const int64_t orig = ind ? ind[i] : i;
+      indo[d] = orig;
+      pro[orig] = pr[orig] + 1;  // kept original indices are distinct: no race
+    }
+  }
+  // rows behind the kept ones: zeros (descriptors and rotary rows), up to the padded length of the image
+  for (int d = kept + warp; d < tp * 128; d += kSpThreads / 32) {
+    const size_t dof = static_cast<size_t>(d >> 7) * 4 * 32768 + atom * 32768 + sw128_offset(d & 127, chunk);
+    *reinterpret_cast<uint4*>(xo + dof) = make_uint4(0u, 0u, 0u, 0u);
+    *reinterpret_cast<uint4*>(xo + dof + 16384) = make_uint4(0u, 0u, 0u, 0u);
+    if (lane < 16)
+      *reinterpret_cast<uint4*>(roto + static_cast<size_t>(d >> 7) * 32768 + (lane >> 3) * 16384 +
+                                sw128_offset(d & 127, lane & 7)) = make_uint4(0u, 0u, 0u, 0u);
+    else if (lane == 16 && d < n_cur) indo[d] = 0;
+  }
+}
+
+}  // namespace lg
+
+extern "C" int lg_score_prune_tiles(const void* x_tiles, const void* rot_tiles, void* x_out, void* rot_out,
+                                    const int64_t* ind0, const int64_t* ind1, int64_t* ind0_out, int64_t* ind1_out,
+                                    const int64_t* prune0, const int64_t* prune1, int64_t* prune0_out,
+                                    int64_t* prune1_out, const int* len0, const int* len1, int* len0_out, int* len1_out,
+                                    int* counts, const float* w_tok, const float* b_tok, const float* w_match,
+                                    const float* b_match, float thr, float min_match, int do_prune, int B, int n0,
+                                    int n1, int tp0, int tp1, int n0_orig, int n1_orig, cudaStream_t stream) {
+  if (!x_tiles || !counts || !w_match || !b_match) return LG_ERR_NULL;
+  if ((w_tok == nullptr) != (b_tok == nullptr)) return LG_ERR_NULL;
+  if (do_prune && (!rot_tiles || !x_out || !rot_out || !ind0_out || !ind1_out || !prune0 || !prune1 || !prune0_out ||
+                   !prune1_out))
+    return LG_ERR_NULL;
+  if (B <= 0 || n0 <= 0 || n1 <= 0 || tp0 * 128 < n0 || tp1 * 128 < n1 || n0_orig < n0 || n1_orig < n1) return LG_ERR_SHAPE;
+  const int tpm = tp0 > tp1 ? tp0 : tp1;
+  const int smem = tpm * 128 * static_cast<int>(sizeof(int));
+  if (smem > 200 * 1024) return LG_ERR_SHAPE;  // 51200 rows per image
+  if (smem > 48 * 1024) {
+    static bool attr_done_dev[lg::kMaxDevices] = {};
+    bool& attr_done = attr_done_dev[lg::current_device_slot()];
+    if (!attr_done) {
+      cudaError_t e = cudaFuncSetAttribute(lg::score_prune_tiles_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024);
+      if (e != cudaSuccess) return static_cast<int>(e);
+      attr_done = true;
+    }
+  }
+  lg::ScorePruneParams p{};
+  p.x = static_cast<const uint8_t*>(x_tiles); p.rot = static_cast<const uint8_t*>(rot_tiles);
+  p.x_out = static_cast<uint8_t*>(x_out); p.rot_out = static_cast<uint8_t*>(rot_out);
+  p.ind[0] = ind0; p.ind[1] = ind1; p.ind_out[0] = ind0_out; p.ind_out[1] = ind1_out;
+  p.prune[0] = prune0; p.prune[1] = prune1; p.prune_out[0] = prune0_out; p.prune_out[1] = prune1_out;
+  p.len[0] = len0; p.len[1] = len1; p.len_out[0] = len0_out; p.len_out[1] = len1_out;
+  p.counts = counts; p.w_tok = w_tok; p.b_tok = b_tok; p.w_match = w_match; p.b_match = b_match;
+  p.thr = thr; p.min_match = min_match; p.do_prune = do_prune; p.B = B;
+  p.n_cur[0] = n0; p.n_cur[1] = n1; p.tp[0] = tp0; p.tp[1] = tp1; p.n_orig[0] = n0_orig; p.n_orig[1] = n1_orig;
+  lg::score_prune_tiles_kernel<<<2 * B, lg::kSpThreads, smem, stream>>>(p);
+  return static_cast<int>(cudaGetLastError());
+}

@@ -262,6 +262,23 @@ int lg_prune_gather(const float* desc, const float* cos_t, const float* sin_t, c
                     const int* keep_idx, const int* counts, float* desc_o, float* cos_o, float* sin_o, int64_t* ind_o,
                     int64_t* prune, int B, int N, int N_out, int N_orig, cudaStream_t stream);
 
+/* (5) fused, on the engine's split tiles: the adaptive step of one layer for a whole batch in ONE launch --
+ * token confidence + matchability (lightglue.py:102-107, :317-318), keep mask (:586-593), the count check_if_stop
+ * needs (:595-606), exclusive scan and the order-preserving compaction (:536-547) of descriptor rows (x_tiles ->
+ * x_out), rotary rows (rot_tiles -> rot_out) and original indices (ind -> ind_out; ind NULL = identity), with
+ * prune_out = prune + 1 on the kept points (prune itself untouched: a pair that exits at this layer keeps its old
+ * counters, the reference breaks before pruning).  Tiles: side 0 images at row tile b*tp0, side 1 at B*tp0 + b*tp1.
+ * counts (B,4) i32 = {kept0, #(conf0 < thr), kept1, #(conf1 < thr)}; len_out = kept.  do_prune = 0: scores and
+ * counts only (depth-only mode; the *_out / rot / prune arguments may then be NULL).  w_tok NULL: no confidence head.
+ * Rows of x_out / rot_out behind the kept ones are zero-filled up to tp*128. */
+int lg_score_prune_tiles(const void* x_tiles, const void* rot_tiles, void* x_out, void* rot_out, const int64_t* ind0,
+                         const int64_t* ind1, int64_t* ind0_out, int64_t* ind1_out, const int64_t* prune0,
+                         const int64_t* prune1, int64_t* prune0_out, int64_t* prune1_out, const int* len0,
+                         const int* len1, int* len0_out, int* len1_out, int* counts, const float* w_tok,
+                         const float* b_tok, const float* w_match, const float* b_match, float thr, float min_match,
+                         int do_prune, int B, int n0, int n1, int tp0, int tp1, int n0_orig, int n1_orig,
+                         cudaStream_t stream);
+
 #ifdef __cplusplus
 }
 #endif

@@ -467,6 +467,75 @@ def test_token_scores_and_gather(C):
         assert torch.equal(pr[b].cpu(), want)
 
 
+@pytest.mark.parametrize("B,M,N,varlen,use_conf", [(2, 1500, 1100, False, True), (3, 700, 2048, True, True), (1, 129, 5, False, False)])
+def test_score_prune_tiles_equals_the_row_kernels(C, B, M, N, varlen, use_conf):
+    """lg_score_prune_tiles (scores + keep mask + scan + compaction in one launch, directly on split tiles) against the
+    chain it replaces -- tiles_to_rows, lg_token_scores, lg_prune_plan, lg_prune_gather, rows_to_tiles -- and with it
+    the oracle's mask: kept counts, unconfident counts, original indices, prune counters and the compacted descriptor /
+    rotary rows, image by image; rows behind the kept ones are zero."""
+    g = _gen(B + M + N)
+    sd = W.make_state_dict({}, seed=0, adaptive_fixture=True)
+    wt = sd["token_confidence.3.token.0.weight"].cuda().reshape(-1) if use_conf else None
+    bt = sd["token_confidence.3.token.0.bias"].cuda() if use_conf else None
+    wm, bm = sd["log_assignment.3.matchability.weight"].cuda().reshape(-1), sd["log_assignment.3.matchability.bias"].cuda()
+    thr, min_match = 0.85, float(np.float32(0.05))
+    tp = [C.tiles_pad(M), C.tiles_pad(N)]
+    n_cur, n_orig = [M, N], [2 * M, 2 * N]
+    lens = [torch.tensor([M, max(1, M // 3), max(1, M - 77)][:B], dtype=torch.int32).cuda(),
+            torch.tensor([max(1, N - 131), N, 1][:B], dtype=torch.int32).cuda()] if varlen else [None, None]
+    desc = [torch.randn(B, n, 256, generator=g).cuda() for n in n_cur]
+    cos = [torch.randn(B, n, 32, generator=g).cuda() for n in n_cur]
+    sin = [torch.randn(B, n, 32, generator=g).cuda() for n in n_cur]
+    ind = [torch.stack([torch.randperm(no, generator=g)[:n].sort().values for _ in range(B)]).cuda()
+           for n, no in zip(n_cur, n_orig)]
+    prune = [torch.randint(1, 4, (B, no), generator=g).cuda() for no in n_orig]
+    rt0 = B * tp[0]
+    x = C.alloc_split(B * (tp[0] + tp[1]), 256, "cuda")
+    rot = torch.empty(B * (tp[0] + tp[1]), C.SPLIT_ATOM, device="cuda", dtype=torch.uint8)
+    C.rows_to_tiles(desc[0], tp[0], out=x[:rt0]); C.rows_to_tiles(desc[1], tp[1], out=x[rt0:])
+    C.rotary_tiles(cos[0], sin[0], tp[0], out=rot[:rt0]); C.rotary_tiles(cos[1], sin[1], tp[1], out=rot[rt0:])
+    x_out, rot_out = torch.full_like(x, 0x7f), torch.full_like(rot, 0x7f)  # NaN-ish bytes: zero fill must cover them
+    ind_out = [torch.full_like(t, -5) for t in ind]
+    prune_out = [torch.zeros_like(t) for t in prune]
+    lens_out = [torch.zeros(B, dtype=torch.int32, device="cuda") for _ in range(2)]
+    counts = torch.zeros(B, 4, dtype=torch.int32, device="cuda")
+    C.score_prune_tiles(x, rot, x_out, rot_out, ind, ind_out, prune, prune_out, lens, lens_out, counts, wt, bt, wm, bm,
+                        thr, min_match, True, B, M, N, tp[0], tp[1], n_orig[0], n_orig[1])
+    rows_out = [C.tiles_to_rows(x_out[:rt0], B, tp[0] * 128, 256, tp[0]), C.tiles_to_rows(x_out[rt0:], B, tp[1] * 128, 256, tp[1])]
+    for side in range(2):
+        n = n_cur[side]
+        rows_in = C.tiles_to_rows(x[:rt0] if side == 0 else x[rt0:], B, n, 256, tp[side])  # what the tiles hold (hi + lo)
+        conf, match = C.token_scores(rows_in, wt, bt, wm, bm, lens[side])
+        keep_idx, cnt = C.prune_plan(conf, match, thr, min_match, lens[side])
+        for b in range(B):
+            nv = n if lens[side] is None else int(lens[side][b])
+            k = int(cnt[b, 0])
+            assert int(counts[b, 2 * side]) == k and int(lens_out[side][b]) == k, (side, b)
+            if use_conf:
+                assert int(counts[b, 2 * side + 1]) == int(cnt[b, 1])
+                mask = O.pruning_mask(conf[b:b + 1, :nv].cpu(), match[b:b + 1, :nv].cpu(), thr, 0.95)
+                assert int(mask.sum()) == k
+            sel = keep_idx[b, :k].long()
+            assert torch.equal(ind_out[side][b, :k], ind[side][b].index_select(0, sel))
+            want_pr = prune[side][b].clone()
+            want_pr[ind[side][b].index_select(0, sel)] += 1
+            assert torch.equal(prune_out[side][b], want_pr)
+            assert torch.equal(rows_out[side][b, :k], rows_in[b].index_select(0, sel))
+            assert (rows_out[side][b, k:] == 0).all()
+        # rotary rows: compare through a second compaction by the row kernels
+        d_o, c_o, s_o, _ = C.prune_gather(rows_in.contiguous(), cos[side], sin[side], ind[side], keep_idx, cnt,
+                                          prune[side].clone(), zero=True)
+        want_rot = C.rotary_tiles(c_o, s_o, tp[side]).view(B, tp[side] * 2, 128, 128)  # (image, tile x {cos, sin}, row, 128 B)
+        got_rot = (rot_out[:rt0] if side == 0 else rot_out[rt0:]).view(B, tp[side] * 2, 128, 128)
+        for b in range(B):
+            k = int(cnt[b, 0])
+            rows = torch.arange(tp[side] * 128, device="cuda").view(tp[side], 1, 128).expand(tp[side], 2, 128).reshape(-1, 128)
+            live = (rows < k)[:, :, None].expand(-1, -1, 128)
+            assert torch.equal(got_rot[b][live], want_rot[b][live])
+            assert (got_rot[b][~live] == 0).all()  # padding rows: zeros (finite; the rotary of a padding row is never used)
+    assert torch.equal(prune[0], prune[0]) and (x_out.view(torch.int16) != 0x7f7f).any()
+
+
 @pytest.mark.parametrize("B,M,N,varlen", [(1, 300, 200, False), (2, 257, 640, True), (1, 128, 128, False), (2, 97, 130, True)])
 def test_assign_keys_equals_assign_plus_filter(B, M, N, varlen):
     """lg_assign_keys + lg_filter_from_keys == lg_assign + lg_filter_matches, bit for bit (scores and all four
