@@ -119,10 +119,33 @@ def _ptr(t):
     return None if t is None else t.data_ptr()
 
 
+_STREAM = None  # stream handle pinned for the duration of one forward (see pinned_stream)
+
+
 def _stream():
     """Current stream of the CURRENT device: callers run under torch.cuda.device(<device of their tensors>)
     (matcher.forward, HostPipeline.run), so that a model on cuda:1 launches on cuda:1."""
+    if _STREAM is not None:
+        return _STREAM
     return torch.cuda.current_stream().cuda_stream
+
+
+class pinned_stream:
+    """`with pinned_stream():` -- look the current stream up ONCE for the ~100 launches of a forward
+    (torch.cuda.current_stream() costs ~15 us: 1 ms of host time per one-pair call).  `pinned_stream(None)` suspends
+    the pin (CUDA graph capture runs on its own stream)."""
+
+    def __init__(self, handle="current"):
+        self.handle = handle
+
+    def __enter__(self):
+        global _STREAM
+        self.prev = _STREAM
+        _STREAM = torch.cuda.current_stream().cuda_stream if self.handle == "current" else self.handle
+
+    def __exit__(self, *exc):
+        global _STREAM
+        _STREAM = self.prev
 
 
 def _f32c(t, name):

@@ -56,7 +56,13 @@ class PackedWeights:
 
     @staticmethod
     def sign(model):
-        return tuple((p.data_ptr(), p._version) for p in model.parameters())
+        """(address, version) of every parameter: a load_state_dict, a .to(device) or an in-place update re-packs.  The
+        Parameter objects of a module persist, so their list is cached (walking model.parameters() costs ~0.3 ms per
+        forward: a fifth of a one-pair call)."""
+        plist = model.__dict__.get("_lg_params")
+        if plist is None:
+            plist = model.__dict__["_lg_params"] = list(model.parameters())
+        return tuple((p.data_ptr(), p._version) for p in plist)
 
     @staticmethod
     def _ffn(ffn, proj, d):
@@ -167,8 +173,8 @@ class TileEngine:
             try:
                 # thread_local: a CUDA call of ANOTHER host thread during the capture (a DataLoader pin_memory
                 # thread of the reference's export / eval loops) must not abort it
-                with torch.cuda.graph(graph, capture_error_mode="thread_local"):
-                    for i in range(n_layers):
+                with C.pinned_stream(None), torch.cuda.graph(graph, capture_error_mode="thread_local"):
+                    for i in range(n_layers):  # (the capture runs on its own stream: no pinned handle)
                         self.layer(i, l0, l1)
             except RuntimeError:
                 # capture failed (e.g. an allocation raced it): this shape runs as plain launches from now on
@@ -183,6 +189,17 @@ class TileEngine:
             C.LAUNCHES = n0  # capture launched nothing; replays account for the kernels below
         g[0].replay()
         C._count(g[1])
+
+    # ------------------------------------------------------------------ adaptive width (lg_score_prune_tiles)
+    def rot_alt(self):
+        """Second rotary-table buffer: the compaction of a layer writes x_alt / rot_alt, swap_pruned() makes them current."""
+        if getattr(self, "_rot_alt", None) is None:
+            self._rot_alt = torch.empty_like(self.rot)
+        return self._rot_alt
+
+    def swap_pruned(self):
+        self.x, self.x_alt = self.x_alt, self.x
+        self.rot, self._rot_alt = self._rot_alt, self.rot
 
     # ------------------------------------------------------------------ read-out
     def rows(self):

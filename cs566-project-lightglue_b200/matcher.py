@@ -273,7 +273,7 @@ class LightGlue(nn.Module):
         kpts0 = data["keypoints0"]
         if not kpts0.is_cuda:
             raise RuntimeError("b200glue LightGlue runs on CUDA (sm_100a) only; move the batch to the GPU")
-        with torch.cuda.device(kpts0.device):  # the C ABI launches on the current device's current stream
+        with torch.cuda.device(kpts0.device), C.pinned_stream():  # the C ABI launches on the current device's current stream
             return self._forward(data)
 
     def _forward(self, data: dict) -> dict:
@@ -310,14 +310,14 @@ class LightGlue(nn.Module):
             if do_early_stop or do_point_pruning:
                 raise NotImplementedError("b200.precision='fp32' runs the full depth (no early exit / pruning)")
             return self._forward_fp32(desc0, desc1, cs0, cs1, len0, len1)
-        eng = self._engine(b, m, n, dev, cached=not (do_early_stop or do_point_pruning))
+        eng = self._engine(b, m, n, dev, cached=True)  # (the adaptive path moves to smaller, uncached engines as it prunes)
         eng.load(desc0, desc1, cs0, cs1)
 
         if do_early_stop or do_point_pruning:
-            from .adaptive import forward_adaptive, forward_adaptive_batched
+            from .adaptive import forward_adaptive_batched, forward_adaptive_one
 
             if b == 1 and len0 is None:
-                return forward_adaptive(self, eng, cs0, cs1)
+                return forward_adaptive_one(self, eng, cs0, cs1)
             return forward_adaptive_batched(self, eng, cs0, cs1, len0, len1)
 
         L = conf.n_layers

@@ -53,7 +53,9 @@ def config3(B=32, N=2048, steps=5):
 
 
 def config4(B=8, NPAD=4096, steps=5):
-    conf = {"filter_threshold": 0.1, "input_dim": 128}
+    # filter_threshold 0: a random-init network never passes 0.1 at 4096 points, and a configuration without matches
+    # says nothing about the indices (parity at this size: tests/test_scale_parity_gpu.py::test_forward_varlen_4096_vs_golden)
+    conf = {"filter_threshold": 0.0, "input_dim": 128}
     sd = W.make_state_dict(conf, seed=0)
     model = M.LightGlue(conf)
     model.load_state_dict(sd)
