@@ -355,7 +355,7 @@ __global__ void __launch_bounds__(kSplit ? 640 : kAttnThreads, 1) attention_kern
           if (leader) {
 #pragma unroll
             for (int kk = 0; kk < 8; ++kk)  // K = 128 keys = 8 x 16: 8 TMEM columns / 32 B of a V^T row per step
-              umma_bf16_ts(tmem + kColO + t * 64, tP + kk * 8,
+              umma_bf16_ts(tmem + kColO + t * 64, tP + (kSplit ? (kk & 3) * 8 + (kk >> 2) * 64 : kk * 8),
                            dv + static_cast<uint64_t>((kk >> 2) * (kTileBytes / 2 >> 4) + (kk & 3) * 2), idesc_pv,
                            (j > 0 || kk > 0));
             TRACE(26, G_p);
@@ -381,8 +381,10 @@ __global__ void __launch_bounds__(kSplit ? 640 : kAttnThreads, 1) attention_kern
     // warpgroup = (tile t, column half h): thread (row r, half h) owns columns [64 h, 64 h + 64) of every S block of its
     // row and columns [32 h, 32 h + 32) of O.  Both halves of a row use ONE reference max (exchanged through the
     // pair's staging slice at the first block and in the rare rescale), keep their own partial row sums (added in the
-    // epilogue), and meet at a 256-thread barrier per block before P overwrites S: half 1's P lands on columns of S
-    // that half 0 reads.
+    // epilogue), and meet at a 256-thread barrier per block where they agree on the (rare) rescale.  P of half h goes
+    // to the first 32 columns of the half's OWN 64 S columns (keys 0-63 at columns 0-31, keys 64-127 at 64-95: the PV
+    // warp addresses them accordingly), so a thread only ever overwrites S values it has read itself and the store
+    // is issued before the barrier.
     const int wgid = warp >> 2, t = wgid >> 1, h = wgid & 1, wq = warp & 3;
     const int r = wq * 32 + lane;                  // row == TMEM lane
     const uint32_t lane_addr = static_cast<uint32_t>(wq * 32) << 16;
@@ -502,27 +504,39 @@ __global__ void __launch_bounds__(kSplit ? 640 : kAttnThreads, 1) attention_kern
           tile_sum = (s0.x + s0.y) + (s1.x + s1.y);
         };
 
-        bool exact = first;
+        bool exact = first, stored = false;
         if (!first) {
           sweep();
-          if (threadIdx.x == 0) TRACE(16, kv_base + j);
           // every P <= its row sum: below the limit nothing can have overflowed the bf16 / fp32 ranges
-          if (__any_sync(0xffffffffu, !(tile_sum < kSumLimit)) && lane == 0) *reinterpret_cast<volatile uint32_t*>(oflag) = 1u;
-          tile_sync();  // both halves are done reading S; the flag is visible
+          const bool warp_over = __any_sync(0xffffffffu, !(tile_sum < kSumLimit));
+          if (!warp_over) {  // P over the first 32 of this thread's own S columns, before the barrier
+            tmem_st32(tS, pk);
+            stored = true;
+          } else if (lane == 0) {
+            *reinterpret_cast<volatile uint32_t*>(oflag) = 1u;
+          }
+          if (threadIdx.x == 0) TRACE(16, kv_base + j);
+          tile_sync();  // the flag is visible: both halves of every row agree on the (rare) rescale below
           if (threadIdx.x == 0) TRACE(17, kv_base + j);
           exact = *reinterpret_cast<volatile uint32_t*>(oflag) != 0u;
         }
         if (exact) {
-          // exact block max of the row (first block of an item, or a row sum that reached the limit): new reference
+          // New reference for the rows that need one: first block of an item, or a row sum that reached the limit.  A
+          // warp that has already stored P (none of ITS rows over the limit) no longer holds S: its rows contribute
+          // nothing to the exchange -- every S value of such a half is below old reference + 60 / c, i.e. below the
+          // exact max of the half that did reach the limit -- and rescale the P they have.
+          const bool intact = !stored;
           float mx = -INFINITY;
+          if (intact) {
 #pragma unroll
-          for (int cb = 0; cb < 2; ++cb) {
-            tmem_ld32(tS + cb * 32, v);
-            tmem_wait_ld();
+            for (int cb = 0; cb < 2; ++cb) {
+              tmem_ld32(tS + cb * 32, v);
+              tmem_wait_ld();
 #pragma unroll
-            for (int i = 0; i < 32; i += 2) {
-              const bool k0 = !partial || cb * 32 + i < rem, k1 = !partial || cb * 32 + i + 1 < rem;
-              mx = fmax3(mx, k0 ? __uint_as_float(v[i]) : -INFINITY, k1 ? __uint_as_float(v[i + 1]) : -INFINITY);
+              for (int i = 0; i < 32; i += 2) {
+                const bool k0 = !partial || cb * 32 + i < rem, k1 = !partial || cb * 32 + i + 1 < rem;
+                mx = fmax3(mx, k0 ? __uint_as_float(v[i]) : -INFINITY, k1 ? __uint_as_float(v[i + 1]) : -INFINITY);
+              }
             }
           }
           if (issuer) bulk_wait_read_all();  // the slice may still be read by the previous item's context stores
@@ -549,13 +563,18 @@ __global__ void __launch_bounds__(kSplit ? 640 : kAttnThreads, 1) attention_kern
             tmem_st32(tO, v);
             tmem_wait_st();
           }
-          sweep();
-          tile_sync();  // both halves are done reading S (and with the exchange words)
-          if (!first && issuer && wq == 0) *reinterpret_cast<volatile uint32_t*>(oflag) = 0u;
+          if (intact) {
+            sweep();  // from S, against the row's (possibly new) reference
+          } else {    // S is gone: P = P_old * 2^((m_old - m_new) c), and so is this block's row sum
+            tile_sum *= alpha;
+#pragma unroll
+            for (int i = 0; i < 32; ++i)
+              pk[i] = pack_bf16x2(__uint_as_float(pk[i] << 16) * alpha, __uint_as_float(pk[i] & 0xFFFF0000u) * alpha);
+          }
+          tmem_st32(tS, pk);
+          if (!first && issuer && wq == 0) *reinterpret_cast<volatile uint32_t*>(oflag) = 0u;  // (read before the last barrier)
         }
         l += tile_sum;
-        // P overwrites the first 64 columns of the S buffer (half h: columns 32 h .. 32 h + 31 = keys 64 h .. 64 h + 63)
-        tmem_st32(tS0 + (G % 3) * 128 + 32 * h, pk);
         tmem_wait_st();
         tc_fence_before();
         __syncwarp();
