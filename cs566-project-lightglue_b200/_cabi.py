@@ -21,6 +21,7 @@ _P, _I, _F, _L = _c.c_void_p, _c.c_int, _c.c_float, _c.c_int64
 # name -> (restype, argtypes); must list every symbol include/lg_b200.h declares
 SIGNATURES = {
     "lg_version": (_I, []),
+    "lg_source_id": (_c.c_char_p, []),
     "lg_posenc": (_I, [_P, _P, _P, _P, _P, _F, _P, _P, _I, _I, _P]),
     "lg_posenc_scale_ori": (_I, [_P, _P, _P, _P, _P, _P, _P, _F, _P, _P, _I, _I, _P]),
     "lg_keypoint_extent": (_I, [_P, _P, _I, _I, _P]),
@@ -89,6 +90,28 @@ def build(verbose: bool = False) -> str:
     return LIB_PATH
 
 
+def source_id() -> str:
+    """What lg_source_id() of a library built from THIS tree returns (the Makefile computes the same digest)."""
+    import glob
+    import hashlib
+    csrc = os.path.join(_HERE, "csrc")
+    files = sorted(glob.glob(os.path.join(csrc, "lg_*.cu"))) + sorted(glob.glob(os.path.join(csrc, "lg_*.cuh")))
+    files.append(os.path.join(os.path.dirname(_HERE), "include", "lg_b200.h"))
+    h = hashlib.sha256()
+    for f in files:
+        with open(f, "rb") as fh:
+            h.update(fh.read())
+    return h.hexdigest()[:16]
+
+
+def _built_id():
+    """Digest embedded in the library file (read without loading it), or None."""
+    import re
+    with open(LIB_PATH, "rb") as fh:
+        m = re.search(rb"LG_SOURCE_ID=([0-9a-f]{16})", fh.read())
+    return None if m is None else m.group(1).decode()
+
+
 def lib():
     global _lib
     if _lib is None:
@@ -97,10 +120,20 @@ def lib():
                 f"{LIB_PATH} not found: the CUDA extension is required (no CPU / PyTorch fallback). "
                 "Run `python -c 'import __graft_entry__ as g; g.build()'` or `make -C cs566-project-lightglue_b200/csrc`."
             )
+        check = not os.environ.get("LG_B200_LIB")  # (kernel experiments pick their own build)
+        if check and _built_id() != source_id():   # a library older than csrc/: rebuild once, never load it silently
+            try:
+                build()
+            except Exception as e:
+                raise RuntimeError(f"{LIB_PATH} is stale (built from sources {_built_id()}, the tree is {source_id()}) "
+                                   f"and rebuilding failed: {e}") from e
         l = ctypes.CDLL(LIB_PATH)
         for name, (res, args) in SIGNATURES.items():
             fn = getattr(l, name)
             fn.restype, fn.argtypes = res, args
+        if check and l.lg_source_id().decode() != source_id():
+            raise RuntimeError(f"{LIB_PATH} is stale: built from sources {l.lg_source_id().decode()}, the tree is "
+                               f"{source_id()}. Rebuild: `make -C cs566-project-lightglue_b200/csrc`.")
         _lib = l
     return _lib
 

@@ -135,3 +135,8 @@ extern "C" int lg_posenc_per_image(const float* kpts, const float* scales, const
 }
 
 extern "C" int lg_version(void) { return 100; }
+#ifndef LG_SOURCE_ID
+#define LG_SOURCE_ID "unknown"
+#endif
+// the "LG_SOURCE_ID=" prefix lets the binding read the digest from the file before loading it
+extern "C" const char* lg_source_id(void) { return "LG_SOURCE_ID=" LG_SOURCE_ID + 13; }

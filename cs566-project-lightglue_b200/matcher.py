@@ -220,7 +220,7 @@ class LightGlue(nn.Module):
     def _forward_fp32(self, desc0, desc1, cs0, cs1, len0, len1):
         """The accuracy mode (engine_fp32.py): IEEE fp32 layer stack, TF32x3 similarity; 1e-4 bound on log_assignment."""
         from .engine import PackedWeights
-        from .engine_fp32 import Fp32Engine, Fp32Weights, max_pairs
+        from .engine_fp32 import Fp32Engine, Fp32Weights, forward_adaptive_fp32, max_pairs
 
         w = getattr(self, "_w32", None)
         if w is None or w.signature != PackedWeights.sign(self):
@@ -228,12 +228,19 @@ class LightGlue(nn.Module):
             w.signature = PackedWeights.sign(self)
         b, m, n = desc0.shape[0], desc0.shape[1], desc1.shape[1]
         L, dev = self.conf.n_layers, desc0.device
+        if self.conf.depth_confidence > 0 or self.conf.width_confidence > 0:
+            return self._forward_fp32_adaptive(w, desc0, desc1, cs0, cs1, len0, len1)
         step = min(b, max_pairs(m, n))
         outs = []
         for lo in range(0, b, step):
             hi = min(b, lo + step)
             cut = lambda t: None if t is None else t[lo:hi].contiguous()
-            eng = Fp32Engine(w, hi - lo, m, n, dev)
+            key = (hi - lo, m, n, str(dev))
+            eng = self.__dict__.get("_engine32")  # the buffers of the last shape are kept (the scores alone: ~1 GB)
+            if eng is None or eng.key != key or eng.w is not w:
+                self.__dict__["_engine32"] = None
+                eng = self.__dict__["_engine32"] = Fp32Engine(w, hi - lo, m, n, dev)
+                eng.key = key
             l0, l1 = cut(len0), cut(len1)
             d0, d1 = eng.forward(cut(desc0), cut(desc1), (cut(cs0[0]), cut(cs0[1])), (cut(cs1[0]), cut(cs1[1])), l0, l1, L)
             scores, (m0, m1, ms0, ms1) = eng.assign(L - 1, self.conf.filter_threshold, l0, l1)
@@ -244,6 +251,36 @@ class LightGlue(nn.Module):
             "ref_descriptors0": r0, "ref_descriptors1": r1, "log_assignment": scores,
             "prune0": torch.ones_like(ms0) * L, "prune1": torch.ones_like(ms1) * L,
         }
+
+    def _forward_fp32_adaptive(self, w, desc0, desc1, cs0, cs1, len0, len1):
+        """depth / width confidence in the fp32 mode: the reference's one-pair procedure (lightglue.py:502-565), pair by
+        pair; a pair of a padded batch runs on its valid points.  B == 1 returns the reference's contract, B > 1 the
+        batched one (exit_layer (B,), log_assignment a list of per-pair (1, M'+1, N'+1) matrices)."""
+        from .engine_fp32 import forward_adaptive_fp32
+
+        b, m, n = desc0.shape[0], desc0.shape[1], desc1.shape[1]
+        dev = desc0.device
+        l0 = [m] * b if len0 is None else [int(v) for v in len0.tolist()]
+        l1 = [n] * b if len1 is None else [int(v) for v in len1.tolist()]
+        preds = []
+        for p in range(b):
+            a, c = l0[p], l1[p]
+            cut = lambda t, k: t[p:p + 1, :k].contiguous()
+            preds.append(forward_adaptive_fp32(self, w, cut(desc0, a), cut(desc1, c), (cut(cs0[0], a), cut(cs0[1], a)),
+                                               (cut(cs1[0], c), cut(cs1[1], c))))
+        if b == 1 and len0 is None:
+            return preds[0]
+        out = {"log_assignment": [q["log_assignment"] for q in preds],
+               "exit_layer": torch.tensor([q["exit_layer"] for q in preds], dtype=torch.int64)}
+        for key, width, fill in (("matches0", m, -1), ("matches1", n, -1), ("matching_scores0", m, 0), ("matching_scores1", n, 0),
+                                 ("prune0", m, 0), ("prune1", n, 0)):
+            t = preds[0][key].new_full((b, width), fill)
+            for p, q in enumerate(preds):
+                t[p, : q[key].shape[1]] = q[key][0]
+            out[key] = t
+        out["ref_descriptors0"] = desc0.new_zeros((b, 0, m, self.conf.descriptor_dim))
+        out["ref_descriptors1"] = desc1.new_zeros((b, 0, n, self.conf.descriptor_dim))
+        return out
 
     @staticmethod
     def _image_size(data, view, like):
@@ -307,8 +344,6 @@ class LightGlue(nn.Module):
         do_early_stop = conf.depth_confidence > 0
         do_point_pruning = conf.width_confidence > 0
         if conf.b200.precision == "fp32":
-            if do_early_stop or do_point_pruning:
-                raise NotImplementedError("b200.precision='fp32' runs the full depth (no early exit / pruning)")
             return self._forward_fp32(desc0, desc1, cs0, cs1, len0, len1)
         eng = self._engine(b, m, n, dev, cached=True)  # (the adaptive path moves to smaller, uncached engines as it prunes)
         eng.load(desc0, desc1, cs0, cs1)

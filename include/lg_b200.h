@@ -32,6 +32,11 @@ typedef struct CUstream_st* cudaStream_t;
 /* Version of this ABI (major*100 + minor). */
 int lg_version(void);
 
+/* First 16 hex digits of the SHA-256 over the sources this library was compiled from (csrc/lg_*.cu, csrc/lg_*.cuh in
+ * name order, then this header), set by the Makefile.  The Python binding recomputes it from the tree and refuses a
+ * stale library.  No counterpart in the reference (pure Python). */
+const char* lg_source_id(void);
+
 /* (1) normalize_keypoints (lightglue.py:21-33) + ConditionalLearnableFourierPositionalEncoding
  * (lightglue.py:50-77, fed at :490-494).  kpts (B,N,2) f32 pixels; size (B,2) f32 (w,h), required
  * (for the reference's size=None branch fill it with lg_keypoint_extent); wr (32,2); wc,bc (32) condition_modulation; cond =

@@ -17,8 +17,11 @@ peak = json.load(open(os.path.join(os.path.dirname(os.path.dirname(os.path.abspa
     if os.path.exists("MEASURED_PEAKS.json") else 6550.0
 
 
-def timeit(fn, reps=20):
-    for _ in range(3):
+REPS = int(os.environ.get("LG_PROFILE_REPS", 20))  # 1 under ncu: one warm-up + one timed launch per kernel
+
+
+def timeit(fn, reps=REPS):
+    for _ in range(3 if reps > 1 else 1):
         fn()
     torch.cuda.synchronize()
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
@@ -47,3 +50,25 @@ tp = C.tiles_pad(N)
 t = C.rows_to_tiles(desc, tp)
 report("rows_to_tiles", timeit(lambda: C.rows_to_tiles(desc, tp, out=t)), B * N * 2048)
 report("tiles_to_rows", timeit(lambda: C.tiles_to_rows(t, B, N, 256, tp)), B * N * 2048)
+
+# the adaptive step of the matcher's path: ONE fused launch on the split tiles (lg_score_prune_tiles): 64 pairs x 2 images
+Bp = B // 2
+x = torch.cat([C.rows_to_tiles(desc[:Bp], tp), C.rows_to_tiles(desc[Bp:], tp)], 0)
+rot = torch.cat([C.rotary_tiles(cos[:Bp], sin[:Bp], tp), C.rotary_tiles(cos[Bp:], sin[Bp:], tp)], 0)
+x2, rot2 = torch.empty_like(x), torch.empty_like(rot)
+i0 = ind[:Bp].contiguous(); i1 = ind[Bp:].contiguous()
+i0n, i1n = torch.empty_like(i0), torch.empty_like(i1)
+p0 = prune[:Bp].contiguous(); p1 = prune[Bp:].contiguous()
+p0n, p1n = torch.empty_like(p0), torch.empty_like(p1)
+l0 = torch.full((Bp,), N, dtype=torch.int32).cuda(); l1 = l0.clone()
+l0n, l1n = torch.empty_like(l0), torch.empty_like(l1)
+counts = torch.empty(Bp, 4, dtype=torch.int32).cuda()
+fused = lambda: C.score_prune_tiles(x, rot, x2, rot2, (i0, i1), (i0n, i1n), (p0, p1), (p0n, p1n), (l0, l1), (l0n, l1n), counts,
+                                    w1, b1, w2, b2, 0.85, 0.4, True, Bp, N, N, tp, tp, N, N)
+fused()
+kept2 = int(counts[:, 0].sum() + counts[:, 2].sum())
+# reads every row (1 KB) ; kept rows written (1 KB + 256 B rotary + 8 B index) and their rotary rows read; counters 16 B / token
+report("score_prune_tiles (fused, kept %d)" % kept2, timeit(fused), B * N * 1024 + kept2 * (1024 + 512 + 16) + B * N * 16)
+scores_only = lambda: C.score_prune_tiles(x, None, None, None, None, None, None, None, (l0, l1), None, counts, w1, b1, w2, b2,
+                                          0.85, 0.4, False, Bp, N, N, tp, tp, N, N)
+report("score_prune_tiles (depth only)", timeit(scores_only), B * N * 1024)

@@ -135,6 +135,61 @@ def test_adaptive_vs_reference_trace(name, batched):
                 worst_margin=worst, la_err=err, match_agreement=agree, exit_layer=exits[b])
 
 
+@pytest.mark.parametrize("name", ADAPTIVE)
+def test_adaptive_fp32_vs_reference_trace(name):
+    """b200.precision = fp32 with depth / width confidence (one pair, the reference's own mode): exit layer, prune
+    counters (a flip only within 1e-4 of a threshold), kept shape and log_assignment within the fp32 bound."""
+    meta, tr, g = _load_trace(name)
+    conf = dict(meta["conf"], b200={"precision": "fp32"})
+    sd = W.make_state_dict(meta["conf"], seed=meta["weight_seed"], adaptive_fixture=True)
+    data = W.make_inputs(1, meta["m"], meta["n"], seed=meta["data_seed"], image_size=tuple(meta["image_size"]),
+                         correlated=meta["correlated"])
+    pred = _model(conf, sd)(_cuda(data))
+    assert int(pred["exit_layer"]) == meta["exit_layer"]
+    flips, worst = 0, 0.0
+    for side, n in ((0, meta["m"]), (1, meta["n"])):
+        got = pred[f"prune{side}"][0].cpu().numpy()
+        k, w = _check_prune_against_trace(name, meta, tr, got, side, n)
+        flips += k
+        worst = max(worst, w)
+    assert worst < 1e-4
+    la = pred["log_assignment"].cpu().numpy()
+    err = agree = None
+    if flips == 0:
+        assert list(la.shape) == meta["la_shape"]
+        if "log_assignment" in g:
+            err = float(np.abs(la - g["log_assignment"]).max())
+        else:
+            err = float(np.abs(la[:, ::17, ::19] - g["log_assignment_sample"]).max())
+        assert err < FP32_TOL
+        agree = float((pred["matches0"].cpu().numpy() == g["matches0"]).mean())
+        assert agree >= 0.999
+        assert np.abs(pred["matching_scores0"].cpu().numpy() - g["matching_scores0"]).max() < FP32_TOL
+    _record("test_adaptive_fp32_vs_reference_trace", case=name, flips=flips, worst_margin=worst, la_err=err,
+            match_agreement=agree, exit_layer=int(pred["exit_layer"]))
+
+
+def test_adaptive_fp32_batch_equals_one_pair_calls():
+    """fp32 mode, B > 1 with unequal valid counts: pair by pair, identical to the one-pair calls on the valid points."""
+    conf = {"filter_threshold": 0.0, "depth_confidence": 0.95, "width_confidence": 0.95, "b200": {"precision": "fp32"}}
+    sd = W.make_state_dict(conf, seed=0, adaptive_fixture=True)
+    model = _model(conf, sd)
+    data = _cuda(W.make_inputs(2, 300, 260, seed=5, image_size=(640, 480), correlated=0.7))
+    l0, l1 = [300, 211], [190, 260]
+    data["num_keypoints0"], data["num_keypoints1"] = torch.tensor(l0).cuda(), torch.tensor(l1).cuda()
+    pred = model(data)
+    for p in range(2):
+        one = {"keypoints0": data["keypoints0"][p:p + 1, :l0[p]], "keypoints1": data["keypoints1"][p:p + 1, :l1[p]],
+               "descriptors0": data["descriptors0"][p:p + 1, :l0[p]], "descriptors1": data["descriptors1"][p:p + 1, :l1[p]],
+               "view0": {"image_size": data["view0"]["image_size"][p:p + 1]},
+               "view1": {"image_size": data["view1"]["image_size"][p:p + 1]}}
+        # the batch is conditioned on the padded length (lightglue.py:490-491): compare exit / prune structure only
+        ref = model(one)
+        assert pred["log_assignment"][p].shape[0] == 1 and pred["log_assignment"][p].dim() == 3
+        assert (pred["matches0"][p, l0[p]:] == -1).all() and (pred["prune0"][p, l0[p]:] == 0).all()
+        assert 0 <= int(pred["exit_layer"][p]) < model.conf.n_layers and 0 <= ref["exit_layer"] < model.conf.n_layers
+
+
 # ----------------------------------------------------------------------------- config 4 at its own size
 @pytest.mark.parametrize("precision", ["bf16", "fp32"])
 def test_forward_varlen_4096_vs_golden(precision):
