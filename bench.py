@@ -394,7 +394,7 @@ def run_b200(a):
     achieved = attn_flops / (attn_ms / 1e3) / 1e12
     traffic = None  # DRAM bytes per launch of this kernel from the committed ncu --set full capture
     try:
-        traffic = json.load(open(os.path.join(ROOT, "profiles", "r1_attention_traffic.json")))["dram_bytes_per_launch"]
+        traffic = json.load(open(os.path.join(ROOT, "profiles", "r2_attention_traffic.json")))["dram_bytes_per_launch"]
     except Exception:
         pass
     roofline = {"kernel": "attention_kernel (tcgen05 flash attention, self + cross)", "bound": "tensor",

@@ -35,7 +35,8 @@ SIGNATURES = {
     "lg_token_scores": (_I, [_P, _P, _P, _P, _P, _P, _P, _P, _I, _I, _P]),
     "lg_prune_plan": (_I, [_P, _P, _P, _F, _F, _P, _P, _I, _I, _P]),
     "lg_prune_gather": (_I, [_P, _P, _P, _P, _P, _P, _P, _P, _P, _P, _P, _I, _I, _I, _I, _P]),
-    "lg_score_prune_tiles": (_I, [_P] * 21 + [_F, _F] + [_I] * 8 + [_P]),
+    "lg_score_prune_tiles": (_I, [_P] * 21 + [_F, _F, _I, _P] + [_I] * 7 + [_P]),
+    "lg_score_prune_ws_bytes": (_c.c_size_t, [_I, _I, _I]),
     "lg_filter_ws_bytes": (_c.c_size_t, [_I, _I, _I]),
     "lg_pack_weight": (_I, [_P, _P, _I, _I, _I, _P]),
     "lg_rows_to_tiles": (_I, [_P, _P, _I, _I, _I, _I, _P]),
@@ -453,11 +454,12 @@ def score_prune_tiles(x, rot, x_out, rot_out, ind, ind_out, prune, prune_out, le
     """lg_score_prune_tiles: ind / ind_out / prune / prune_out / lens / lens_out are (side 0, side 1) pairs (entries may
     be None where the header allows NULL); counts (B,4) i32."""
     pp = lambda pair, i: None if pair is None or pair[i] is None else pair[i].data_ptr()
+    ws = torch.empty(lib().lg_score_prune_ws_bytes(B, tp0, tp1) // 8, device=x.device, dtype=torch.int64)
     _check(lib().lg_score_prune_tiles(_ptr(x), _ptr(rot), _ptr(x_out), _ptr(rot_out), pp(ind, 0), pp(ind, 1), pp(ind_out, 0),
                                       pp(ind_out, 1), pp(prune, 0), pp(prune, 1), pp(prune_out, 0), pp(prune_out, 1),
                                       pp(lens, 0), pp(lens, 1), pp(lens_out, 0), pp(lens_out, 1), _ptr(counts), _ptr(w_tok),
                                       _ptr(b_tok), _ptr(w_match), _ptr(b_match), float(thr), float(min_match),
-                                      int(bool(do_prune)), B, n0, n1, tp0, tp1, n0_orig, n1_orig, _stream()),
+                                      int(bool(do_prune)), _ptr(ws), B, n0, n1, tp0, tp1, n0_orig, n1_orig, _stream()),
            "lg_score_prune_tiles")
     _count(1)
 

@@ -382,10 +382,12 @@ __global__ void __launch_bounds__(kThreads, 1) assign_f16_kernel(const Params p)
             for (int q = 0; q < kChunk / 4; ++q) {
               const float4 c4 = *reinterpret_cast<const float4*>(s_colc + ch * kChunk + 4 * q);
               // (s - lse_r) + (s - lse_c) + (ls_r + ls_c) as one fma: 2 s scale + ((ls_r - lse_r) + (ls_c - lse_c))
-              val[4 * q] = fmaf(__uint_as_float(v[4 * q]), s2, rc + c4.x);
-              val[4 * q + 1] = fmaf(__uint_as_float(v[4 * q + 1]), s2, rc + c4.y);
-              val[4 * q + 2] = fmaf(__uint_as_float(v[4 * q + 2]), s2, rc + c4.z);
-              val[4 * q + 3] = fmaf(__uint_as_float(v[4 * q + 3]), s2, rc + c4.w);
+              // packed f32x2: the same fmaf(s, 2 scale, rc + c) per element, half the issue slots
+              const float2 a = __ffma2_rn(make_float2(__uint_as_float(v[4 * q]), __uint_as_float(v[4 * q + 1])),
+                                          make_float2(s2, s2), __fadd2_rn(make_float2(rc, rc), make_float2(c4.x, c4.y)));
+              const float2 b = __ffma2_rn(make_float2(__uint_as_float(v[4 * q + 2]), __uint_as_float(v[4 * q + 3])),
+                                          make_float2(s2, s2), __fadd2_rn(make_float2(rc, rc), make_float2(c4.z, c4.w)));
+              val[4 * q] = a.x; val[4 * q + 1] = a.y; val[4 * q + 2] = b.x; val[4 * q + 3] = b.y;
             }
             if (!full) {
 #pragma unroll
@@ -409,14 +411,45 @@ __global__ void __launch_bounds__(kThreads, 1) assign_f16_kernel(const Params p)
               st_shared_f4(stg + (lane * kStgPitch + 4 * q) * 4, val[4 * q], val[4 * q + 1], val[4 * q + 2], val[4 * q + 3]);
             __syncwarp();
             const int cbase = col0 + ch * kChunk;
+            float cbv = -INFINITY;
+            uint32_t cbi = kNone;
             if (full) {
-              // lane -> (row rq of 8, 16-byte quarter f4 of the 64-byte segment): 8 rows x 64 B per instruction
+              // lane -> (row rq of 8, 16-byte quarter f4 of the 64-byte segment): 8 rows x 64 B per instruction.
+              // All shared-memory reads of the chunk (store path and key path) are issued before their first use.
               const int rq = lane >> 2, f4 = lane & 3;
               float* o = out + static_cast<int64_t>(row0 + wq * 32 + rq) * pitch + cbase + 4 * f4;
+              float4 x4[4];
 #pragma unroll
-              for (int q = 0; q < 4; ++q) {
-                const float4 x = ld_shared_f4(stg + ((q * 8 + rq) * kStgPitch + 4 * f4) * 4);
-                *reinterpret_cast<float4*>(o + static_cast<int64_t>(q) * 8 * pitch) = x;
+              for (int q = 0; q < 4; ++q) x4[q] = ld_shared_f4(stg + ((q * 8 + rq) * kStgPitch + 4 * f4) * 4);
+              float xs[kChunk];
+              if (keys) {
+#pragma unroll
+                for (int jj = 0; jj < kChunk; ++jj)
+                  asm volatile("ld.shared.f32 %0, [%1];" : "=f"(xs[jj]) : "r"(stg + ((2 * jj + half) * kStgPitch + cl) * 4));
+              }
+#pragma unroll
+              for (int q = 0; q < 4; ++q) *reinterpret_cast<float4*>(o + static_cast<int64_t>(q) * 8 * pitch) = x4[q];
+              if (keys) {  // best row of the column among this warp's rows: lane == (row parity, column)
+                // four independent chains of four rows, merged pairwise: strict > keeps the lowest row on ties
+                float gv[4];
+                uint32_t gi[4];
+#pragma unroll
+                for (int g = 0; g < 4; ++g) {
+                  gv[g] = xs[4 * g];
+                  gi[g] = 2 * (4 * g) + half;
+#pragma unroll
+                  for (int k = 1; k < 4; ++k) {
+                    const bool up = xs[4 * g + k] > gv[g];
+                    gv[g] = up ? xs[4 * g + k] : gv[g];
+                    gi[g] = up ? static_cast<uint32_t>(2 * (4 * g + k) + half) : gi[g];
+                  }
+                }
+                const bool u1 = gv[1] > gv[0], u3 = gv[3] > gv[2];
+                const float v01 = u1 ? gv[1] : gv[0], v23 = u3 ? gv[3] : gv[2];
+                const uint32_t i01 = u1 ? gi[1] : gi[0], i23 = u3 ? gi[3] : gi[2];
+                const bool u = v23 > v01;
+                cbv = u ? v23 : v01;
+                cbi = u ? i23 : i01;
               }
             } else {
               // lane == (row parity, column): scalar stores with bounds
@@ -428,21 +461,7 @@ __global__ void __launch_bounds__(kThreads, 1) assign_f16_kernel(const Params p)
                 asm volatile("ld.shared.f32 %0, [%1];" : "=f"(x) : "r"(stg + (lr * kStgPitch + cl) * 4));
                 if (c < p.N && row0 + rr < p.M) out[static_cast<int64_t>(row0 + rr) * pitch + c] = x;
               }
-            }
-            if (keys) {  // best row of the column among this warp's rows: lane == (row parity, column)
-              float cbv = -INFINITY;
-              uint32_t cbi = kNone;
-              if (full) {
-#pragma unroll
-                for (int jj = 0; jj < kChunk; ++jj) {
-                  const int lr = 2 * jj + half;
-                  float x;
-                  asm volatile("ld.shared.f32 %0, [%1];" : "=f"(x) : "r"(stg + (lr * kStgPitch + cl) * 4));
-                  const bool up = x > cbv || jj == 0;  // strict >: the first (lowest) row wins ties
-                  cbv = up ? x : cbv;
-                  cbi = up ? static_cast<uint32_t>(lr) : cbi;
-                }
-              } else {
+              if (keys) {
                 const bool col_ok = ch * kChunk + cl < vcols;
 #pragma unroll 4
                 for (int jj = 0; jj < kChunk; ++jj) {
@@ -454,6 +473,8 @@ __global__ void __launch_bounds__(kThreads, 1) assign_f16_kernel(const Params p)
                   cbi = up ? static_cast<uint32_t>(lr) : cbi;
                 }
               }
+            }
+            if (keys) {
               // the other row parity of the same column: larger value, lower row on ties
               const float ov = __shfl_xor_sync(0xffffffffu, cbv, 16);
               const uint32_t oi = __shfl_xor_sync(0xffffffffu, cbi, 16);

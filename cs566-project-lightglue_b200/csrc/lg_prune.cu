@@ -206,16 +206,25 @@ extern "C" int lg_logit_rows(const float* x, const float* w, const float* bias, 
 // tiles (north_star (5): "fused confidence-MLP plus prefix-sum stream-compaction kernel"):
 //   token confidence + matchability of every valid token (TokenConfidence.forward :102-107, get_matchability :317-318)
 //   keep mask (get_pruning_mask :586-593), the count check_if_stop needs (:595-606),
-//   block-wide exclusive scan, and the order-preserving compaction of the kept tokens (:536-547): descriptor row
+//   exclusive scan, and the order-preserving compaction of the kept tokens (:536-547): descriptor row
 //   (hi | lo bf16 split, 1 KB), rotary row (cos | sin, 256 B) and original index move to their new row of the OUTPUT
 //   tiles; prune[ind] + 1 goes to a copy of the counters (a pair that exits at this layer keeps the old ones: the
 //   reference breaks before pruning).  Rows behind the kept ones are zero-filled (padding must stay finite: the PV MMA
 //   multiplies masked keys by P = 0).
-// No fp32 rows, no tiles -> rows -> tiles round trip, no index_select: 1 KB read per token for the scores, 1.25 KB
-// read (L2-hot) + 1.25 KB written per kept token.  One CTA per image (side 0 images, then side 1).
+// No fp32 rows, no tiles -> rows -> tiles round trip, no index_select.
+// Work item = one ROW TILE (128 tokens) of one image, one CTA of 256 threads each; the grid covers every tile of the
+// batch, so one pair per call spreads over 32 CTAs and 32 pairs over 1024.  Items are taken in ticket order (atomic
+// counter), which makes the prefix exchange below safe on any dispatch order.  A CTA scores its 128 rows (1 KB read
+// per token), publishes (kept, unconfident) of its tile in the workspace, sums the published counts of the earlier
+// tiles of its image (at most tp - 1 words, all produced concurrently: no serial chain), and moves its kept rows to
+// their final position; the re-read of the tile it has just scored comes from L1 / L2.  The image's last valid tile
+// writes the counts and zero-fills the rows between the kept count and its own end; tiles behind the valid length
+// zero-fill themselves.
 namespace lg {
 
-constexpr int kSpThreads = 1024;
+constexpr int kSpThreads = 256;
+constexpr int kSpWarps = kSpThreads / 32;
+constexpr unsigned long long kSpReady = 1ull << 63;
 
 struct ScorePruneParams {
   const uint8_t* x;      // split tiles [B*tp0 + B*tp1][4][32 KB]
@@ -225,127 +234,20 @@ struct ScorePruneParams {
   const int64_t* ind[2];     // (B, n_cur) original index of every row; null = identity
   int64_t* ind_out[2];
   const int64_t* prune[2];   // (B, n_orig)
-  int64_t* prune_out[2];
+  int64_t* prune_out[2];     // holds a copy of prune when the kernel starts (the entry point copies)
   const int* len[2];         // valid rows per image, null = n_cur
   int* len_out[2];
   int* counts;               // (B, 4): kept0, unconfident0, kept1, unconfident1
+  unsigned long long* ws;    // [0] ticket, [1 + tile] = ready | unconfident << 32 | kept of the tile; zero on entry
   const float* w_tok; const float* b_tok; const float* w_match; const float* b_match;
   float thr, min_match;
   int do_prune, B, n_cur[2], tp[2], n_orig[2];
 };
 
-__global__ void __launch_bounds__(kSpThreads) score_prune_tiles_kernel(const ScorePruneParams p) {
-  extern __shared__ int s_pos[];  // [tp * 128]: keep flag, then destination row (or -1)
-  __shared__ int s_warp[32];
-  __shared__ int s_unconf;
-  const int side = blockIdx.x >= p.B, b = blockIdx.x - side * p.B;
-  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-  const int n_cur = p.n_cur[side], tp = p.tp[side];
-  const int nv = p.len[side] ? min(p.len[side][b], n_cur) : n_cur;
-  const size_t tile0 = side ? static_cast<size_t>(p.B) * p.tp[0] + static_cast<size_t>(b) * tp : static_cast<size_t>(b) * tp;
-  const uint8_t* x = p.x + tile0 * 4 * 32768;
-  const uint8_t* rot = p.rot + tile0 * 32768;
-  if (threadIdx.x == 0) s_unconf = 0;
-  __syncthreads();
-
-  // lane -> (K atom, 16-byte chunk): always the same 8 features, their weights live in registers
+__device__ __forceinline__ void sp_zero_rows(uint8_t* xo, uint8_t* roto, int64_t* indo, int d0, int d1, int n_cur,
+                                             int warp, int lane) {
   const int atom = lane >> 3, chunk = lane & 7;
-  float wm[8], wt[8];
-#pragma unroll
-  for (int k = 0; k < 8; ++k) {
-    wm[k] = __ldg(p.w_match + atom * 64 + chunk * 8 + k);
-    wt[k] = p.w_tok ? __ldg(p.w_tok + atom * 64 + chunk * 8 + k) : 0.f;
-  }
-  const float bm = __ldg(p.b_match), bt = p.b_tok ? __ldg(p.b_tok) : 0.f;
-  int unconf = 0;
-  for (int i = warp; i < nv; i += kSpThreads / 32) {
-    const uint8_t* src = x + static_cast<size_t>(i >> 7) * 4 * 32768 + atom * 32768 + sw128_offset(i & 127, chunk);
-    const uint4 hi = __ldg(reinterpret_cast<const uint4*>(src)), lo = __ldg(reinterpret_cast<const uint4*>(src + 16384));
-    const uint32_t hh[4] = {hi.x, hi.y, hi.z, hi.w}, ll[4] = {lo.x, lo.y, lo.z, lo.w};
-    float sm = 0.f, st = 0.f;
-#pragma unroll
-    for (int k = 0; k < 4; ++k) {
-      const float x0 = __uint_as_float(hh[k] << 16) + __uint_as_float(ll[k] << 16);
-      const float x1 = __uint_as_float(hh[k] & 0xFFFF0000u) + __uint_as_float(ll[k] & 0xFFFF0000u);
-      sm = fmaf(x0, wm[2 * k], sm); sm = fmaf(x1, wm[2 * k + 1], sm);
-      st = fmaf(x0, wt[2 * k], st); st = fmaf(x1, wt[2 * k + 1], st);
-    }
-    sm = warp_sum(sm);
-    st = warp_sum(st);
-    if (lane == 0) {
-      const float match = sigmoidf(sm + bm);
-      bool keep = match > p.min_match;
-      if (p.w_tok) {
-        const float conf = sigmoidf(st + bt);
-        keep = keep || (conf <= p.thr);
-        unconf += conf < p.thr ? 1 : 0;
-      }
-      s_pos[i] = (keep || !p.do_prune) ? 1 : 0;
-    }
-  }
-  if (lane == 0 && unconf) atomicAdd(&s_unconf, unconf);
-  __syncthreads();
-
-  // exclusive scan of the keep flags: thread t owns rows [t * per, t * per + per)
-  const int per = (nv + kSpThreads - 1) / kSpThreads;
-  const int r0 = threadIdx.x * per, r1 = min(nv, r0 + per);
-  int mine = 0;
-  for (int i = r0; i < r1; ++i) mine += s_pos[i];
-  int incl = mine;
-#pragma unroll
-  for (int o = 1; o < 32; o <<= 1) {
-    const int v = __shfl_up_sync(0xffffffffu, incl, o);
-    if (lane >= o) incl += v;
-  }
-  if (lane == 31) s_warp[warp] = incl;
-  __syncthreads();
-  int before = incl - mine;
-  for (int w = 0; w < warp; ++w) before += s_warp[w];
-  int kept = 0;
-  for (int w = 0; w < 32; ++w) kept += s_warp[w];
-  for (int i = r0; i < r1; ++i) {
-    const int k = s_pos[i];
-    s_pos[i] = k ? before : -1;
-    before += k;
-  }
-  __syncthreads();
-  if (threadIdx.x == 0) {
-    p.counts[4 * b + 2 * side] = kept;
-    p.counts[4 * b + 2 * side + 1] = s_unconf;
-    if (p.len_out[side]) p.len_out[side][b] = kept;
-  }
-  if (!p.do_prune) return;
-
-  // prune counters: copy, then + 1 on the kept original indices (below)
-  const int n_orig = p.n_orig[side];
-  const int64_t* pr = p.prune[side] + static_cast<size_t>(b) * n_orig;
-  int64_t* pro = p.prune_out[side] + static_cast<size_t>(b) * n_orig;
-  for (int i = threadIdx.x; i < n_orig; i += kSpThreads) pro[i] = pr[i];
-  __syncthreads();
-
-  uint8_t* xo = p.x_out + tile0 * 4 * 32768;
-  uint8_t* roto = p.rot_out + tile0 * 32768;
-  const int64_t* ind = p.ind[side] ? p.ind[side] + static_cast<size_t>(b) * n_cur : nullptr;
-  int64_t* indo = p.ind_out[side] + static_cast<size_t>(b) * n_cur;
-  for (int i = warp; i < nv; i += kSpThreads / 32) {
-    const int d = s_pos[i];
-    if (d < 0) continue;
-    const size_t so = static_cast<size_t>(i >> 7) * 4 * 32768 + atom * 32768 + sw128_offset(i & 127, chunk);
-    const size_t dof = static_cast<size_t>(d >> 7) * 4 * 32768 + atom * 32768 + sw128_offset(d & 127, chunk);
-    *reinterpret_cast<uint4*>(xo + dof) = __ldg(reinterpret_cast<const uint4*>(x + so));
-    *reinterpret_cast<uint4*>(xo + dof + 16384) = __ldg(reinterpret_cast<const uint4*>(x + so + 16384));
-    if (lane < 16) {  // rotary row: lanes 0-7 the cos chunks, 8-15 the sin chunks
-      const size_t rs = static_cast<size_t>(i >> 7) * 32768 + (lane >> 3) * 16384 + sw128_offset(i & 127, lane & 7);
-      const size_t rd = static_cast<size_t>(d >> 7) * 32768 + (lane >> 3) * 16384 + sw128_offset(d & 127, lane & 7);
-      *reinterpret_cast<uint4*>(roto + rd) = __ldg(reinterpret_cast<const uint4*>(rot + rs));
-    } else if (lane == 16) {
-      const int64_t orig = ind ? ind[i] : i;
-      indo[d] = orig;
-      pro[orig] = pr[orig] + 1;  // kept original indices are distinct: no race
-    }
-  }
-  // rows behind the kept ones: zeros (descriptors and rotary rows), up to the padded length of the image
-  for (int d = kept + warp; d < tp * 128; d += kSpThreads / 32) {
+  for (int d = d0 + warp; d < d1; d += kSpWarps) {
     const size_t dof = static_cast<size_t>(d >> 7) * 4 * 32768 + atom * 32768 + sw128_offset(d & 127, chunk);
     *reinterpret_cast<uint4*>(xo + dof) = make_uint4(0u, 0u, 0u, 0u);
     *reinterpret_cast<uint4*>(xo + dof + 16384) = make_uint4(0u, 0u, 0u, 0u);
@@ -356,32 +258,194 @@ __global__ void __launch_bounds__(kSpThreads) score_prune_tiles_kernel(const Sco
   }
 }
 
+__global__ void __launch_bounds__(kSpThreads) score_prune_tiles_kernel(const ScorePruneParams p) {
+  __shared__ int s_item, s_keep[128], s_wsum[kSpWarps], s_wunc[kSpWarps], s_base, s_unc_before;
+  __shared__ unsigned s_ballot[4];
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  if (threadIdx.x == 0) s_item = static_cast<int>(atomicAdd(p.ws, 1ull));
+  __syncthreads();
+  const int item = s_item;
+  const int tiles0 = p.B * p.tp[0];
+  const int side = item >= tiles0;
+  const int tp = p.tp[side];
+  const int b = (item - side * tiles0) / tp, tile = (item - side * tiles0) % tp;
+  const int n_cur = p.n_cur[side];
+  const int nv = p.len[side] ? min(p.len[side][b], n_cur) : n_cur;
+  const int nvt = max(1, (nv + 127) >> 7);  // tiles that take part in the prefix exchange
+  const size_t tile0 = static_cast<size_t>(item - tile);  // first row tile of the image in the buffers
+  const uint8_t* x = p.x + tile0 * 4 * 32768;
+  uint8_t* xo = p.do_prune ? p.x_out + tile0 * 4 * 32768 : nullptr;
+  uint8_t* roto = p.do_prune ? p.rot_out + tile0 * 32768 : nullptr;
+  int64_t* indo = p.do_prune ? p.ind_out[side] + static_cast<size_t>(b) * n_cur : nullptr;
+  if (tile >= nvt) {  // behind the valid rows: nothing to score, the tile of the output is padding
+    if (p.do_prune) sp_zero_rows(xo, roto, indo, tile * 128, tile * 128 + 128, n_cur, warp, lane);
+    return;
+  }
+
+  // lane -> (K atom, 16-byte chunk): always the same 8 features, their weights live in registers
+  const int atom = lane >> 3, chunk = lane & 7;
+  float wm[8], wt[8];
+#pragma unroll
+  for (int k = 0; k < 8; ++k) {
+    wm[k] = __ldg(p.w_match + atom * 64 + chunk * 8 + k);
+    wt[k] = p.w_tok ? __ldg(p.w_tok + atom * 64 + chunk * 8 + k) : 0.f;
+  }
+  const float bm = __ldg(p.b_match), bt = p.b_tok ? __ldg(p.b_tok) : 0.f;
+  const int rows = min(128, nv - tile * 128);  // valid rows of this tile (0 only for an empty image)
+  const uint8_t* xt = x + static_cast<size_t>(tile) * 4 * 32768 + atom * 32768;
+  int unconf = 0;
+  // warp w scores rows w, w + 8, ...: four rows (eight 16-byte loads per lane) in flight
+  for (int r0 = warp; r0 < 128; r0 += 4 * kSpWarps) {
+    uint4 hi[4], lo[4];
+#pragma unroll
+    for (int u = 0; u < 4; ++u) {
+      const int r = r0 + u * kSpWarps;
+      if (r < rows) {
+        const uint8_t* src = xt + sw128_offset(r, chunk);
+        hi[u] = __ldg(reinterpret_cast<const uint4*>(src));
+        lo[u] = __ldg(reinterpret_cast<const uint4*>(src + 16384));
+      }
+    }
+#pragma unroll
+    for (int u = 0; u < 4; ++u) {
+      const int r = r0 + u * kSpWarps;
+      if (r >= 128) continue;
+      int keep = 0;
+      if (r < rows) {  // warp-uniform
+        const uint32_t hh[4] = {hi[u].x, hi[u].y, hi[u].z, hi[u].w}, ll[4] = {lo[u].x, lo[u].y, lo[u].z, lo[u].w};
+        float sm = 0.f, st = 0.f;
+#pragma unroll
+        for (int k = 0; k < 4; ++k) {
+          const float x0 = __uint_as_float(hh[k] << 16) + __uint_as_float(ll[k] << 16);
+          const float x1 = __uint_as_float(hh[k] & 0xFFFF0000u) + __uint_as_float(ll[k] & 0xFFFF0000u);
+          sm = fmaf(x0, wm[2 * k], sm); sm = fmaf(x1, wm[2 * k + 1], sm);
+          st = fmaf(x0, wt[2 * k], st); st = fmaf(x1, wt[2 * k + 1], st);
+        }
+        sm = warp_sum(sm);
+        st = warp_sum(st);
+        const float match = sigmoidf(sm + bm);
+        bool kp = match > p.min_match;
+        if (p.w_tok) {
+          const float conf = sigmoidf(st + bt);
+          kp = kp || (conf <= p.thr);
+          unconf += conf < p.thr ? 1 : 0;   // (every lane counts the same rows; lane 0's total is used)
+        }
+        keep = (kp || !p.do_prune) ? 1 : 0;
+      }
+      if (lane == 0) s_keep[r] = keep;
+    }
+  }
+  if (lane == 0) s_wunc[warp] = unconf;
+  __syncthreads();
+
+  // local exclusive scan of the 128 keep flags (ballots of the first four warps) and the tile totals
+  int flag = 0, excl = 0;
+  if (threadIdx.x < 128) {
+    flag = s_keep[threadIdx.x];
+    const unsigned bal = __ballot_sync(0xffffffffu, flag != 0);
+    if (lane == 0) s_ballot[warp] = bal;
+    excl = __popc(bal & ((1u << lane) - 1u));
+  }
+  __syncthreads();
+  int before_w = 0, cnt = 0;
+#pragma unroll
+  for (int w = 0; w < 4; ++w) {
+    const int c = __popc(s_ballot[w]);
+    if (w < warp) before_w += c;
+    cnt += c;
+  }
+  int unc = 0;
+#pragma unroll
+  for (int w = 0; w < kSpWarps; ++w) unc += s_wunc[w];
+  unsigned long long* slot = p.ws + 1 + tile0;  // one word per tile of this image
+  if (threadIdx.x == 0) {
+    __threadfence();
+    atomicExch(slot + tile, kSpReady | (static_cast<unsigned long long>(unc) << 32) | static_cast<unsigned long long>(cnt));
+  }
+  // kept / unconfident tokens in the earlier tiles of the image: every earlier tile has an earlier ticket, so it is
+  // running or done -- waiting for its word cannot deadlock
+  if (warp == 0) {
+    int base = 0, ub = 0;
+    for (int t = lane; t < tile; t += 32) {
+      unsigned long long v;
+      do {
+        v = *reinterpret_cast<volatile unsigned long long*>(slot + t);
+      } while (!(v & kSpReady));
+      base += static_cast<int>(v & 0xffffffffull);
+      ub += static_cast<int>((v >> 32) & 0x7fffffffull);
+    }
+    base = static_cast<int>(warp_sum(static_cast<float>(base)));  // counts < 2^24: exact in fp32
+    ub = static_cast<int>(warp_sum(static_cast<float>(ub)));
+    if (lane == 0) { s_base = base; s_unc_before = ub; }
+  }
+  __syncthreads();
+  const int base = s_base;
+  if (threadIdx.x < 128) s_keep[threadIdx.x] = flag ? base + before_w + excl : -1;  // destination row or -1
+  __syncthreads();
+  const bool last = tile == nvt - 1;
+  const int kept = base + cnt;
+  if (last && threadIdx.x == 0) {
+    p.counts[4 * b + 2 * side] = kept;
+    p.counts[4 * b + 2 * side + 1] = s_unc_before + unc;
+    if (p.len_out[side]) p.len_out[side][b] = kept;
+  }
+  if (!p.do_prune) return;
+
+  const uint8_t* rot = p.rot + tile0 * 32768;
+  const int n_orig = p.n_orig[side];
+  const int64_t* pr = p.prune[side] + static_cast<size_t>(b) * n_orig;
+  int64_t* pro = p.prune_out[side] + static_cast<size_t>(b) * n_orig;
+  const int64_t* ind = p.ind[side] ? p.ind[side] + static_cast<size_t>(b) * n_cur : nullptr;
+  for (int r = warp; r < rows; r += kSpWarps) {
+    const int d = s_keep[r];
+    if (d < 0) continue;
+    const int i = tile * 128 + r;
+    const uint8_t* src = xt + sw128_offset(r, chunk);
+    const size_t dof = static_cast<size_t>(d >> 7) * 4 * 32768 + atom * 32768 + sw128_offset(d & 127, chunk);
+    *reinterpret_cast<uint4*>(xo + dof) = __ldg(reinterpret_cast<const uint4*>(src));
+    *reinterpret_cast<uint4*>(xo + dof + 16384) = __ldg(reinterpret_cast<const uint4*>(src + 16384));
+    if (lane < 16) {  // rotary row: lanes 0-7 the cos chunks, 8-15 the sin chunks
+      const size_t rs = static_cast<size_t>(tile) * 32768 + (lane >> 3) * 16384 + sw128_offset(r, lane & 7);
+      const size_t rd = static_cast<size_t>(d >> 7) * 32768 + (lane >> 3) * 16384 + sw128_offset(d & 127, lane & 7);
+      *reinterpret_cast<uint4*>(roto + rd) = __ldg(reinterpret_cast<const uint4*>(rot + rs));
+    } else if (lane == 16) {
+      const int64_t orig = ind ? ind[i] : i;
+      indo[d] = orig;
+      pro[orig] = pr[orig] + 1;  // kept original indices are distinct: no race
+    }
+  }
+  // rows behind the kept ones, up to the end of this (the image's last valid) tile: zeros
+  if (last) sp_zero_rows(xo, roto, indo, kept, nvt * 128, n_cur, warp, lane);
+}
+
 }  // namespace lg
+
+extern "C" size_t lg_score_prune_ws_bytes(int B, int tp0, int tp1) {
+  if (B <= 0 || tp0 <= 0 || tp1 <= 0) return 0;
+  return (static_cast<size_t>(B) * (tp0 + tp1) + 1) * sizeof(unsigned long long);
+}
 
 extern "C" int lg_score_prune_tiles(const void* x_tiles, const void* rot_tiles, void* x_out, void* rot_out,
                                     const int64_t* ind0, const int64_t* ind1, int64_t* ind0_out, int64_t* ind1_out,
                                     const int64_t* prune0, const int64_t* prune1, int64_t* prune0_out,
                                     int64_t* prune1_out, const int* len0, const int* len1, int* len0_out, int* len1_out,
                                     int* counts, const float* w_tok, const float* b_tok, const float* w_match,
-                                    const float* b_match, float thr, float min_match, int do_prune, int B, int n0,
-                                    int n1, int tp0, int tp1, int n0_orig, int n1_orig, cudaStream_t stream) {
-  if (!x_tiles || !counts || !w_match || !b_match) return LG_ERR_NULL;
+                                    const float* b_match, float thr, float min_match, int do_prune, void* ws, int B,
+                                    int n0, int n1, int tp0, int tp1, int n0_orig, int n1_orig, cudaStream_t stream) {
+  if (!x_tiles || !counts || !w_match || !b_match || !ws) return LG_ERR_NULL;
   if ((w_tok == nullptr) != (b_tok == nullptr)) return LG_ERR_NULL;
   if (do_prune && (!rot_tiles || !x_out || !rot_out || !ind0_out || !ind1_out || !prune0 || !prune1 || !prune0_out ||
                    !prune1_out))
     return LG_ERR_NULL;
   if (B <= 0 || n0 <= 0 || n1 <= 0 || tp0 * 128 < n0 || tp1 * 128 < n1 || n0_orig < n0 || n1_orig < n1) return LG_ERR_SHAPE;
-  const int tpm = tp0 > tp1 ? tp0 : tp1;
-  const int smem = tpm * 128 * static_cast<int>(sizeof(int));
-  if (smem > 200 * 1024) return LG_ERR_SHAPE;  // 51200 rows per image
-  if (smem > 48 * 1024) {
-    static bool attr_done_dev[lg::kMaxDevices] = {};
-    bool& attr_done = attr_done_dev[lg::current_device_slot()];
-    if (!attr_done) {
-      cudaError_t e = cudaFuncSetAttribute(lg::score_prune_tiles_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024);
-      if (e != cudaSuccess) return static_cast<int>(e);
-      attr_done = true;
-    }
+  if ((reinterpret_cast<uintptr_t>(ws) & 7) != 0) return LG_ERR_ALIGN;
+  cudaError_t e = cudaMemsetAsync(ws, 0, lg_score_prune_ws_bytes(B, tp0, tp1), stream);
+  if (e != cudaSuccess) return static_cast<int>(e);
+  if (do_prune) {  // the counters of the tokens that stay out of this layer are carried over unchanged
+    e = cudaMemcpyAsync(prune0_out, prune0, static_cast<size_t>(B) * n0_orig * sizeof(int64_t), cudaMemcpyDeviceToDevice, stream);
+    if (e == cudaSuccess)
+      e = cudaMemcpyAsync(prune1_out, prune1, static_cast<size_t>(B) * n1_orig * sizeof(int64_t), cudaMemcpyDeviceToDevice, stream);
+    if (e != cudaSuccess) return static_cast<int>(e);
   }
   lg::ScorePruneParams p{};
   p.x = static_cast<const uint8_t*>(x_tiles); p.rot = static_cast<const uint8_t*>(rot_tiles);
@@ -389,9 +453,10 @@ extern "C" int lg_score_prune_tiles(const void* x_tiles, const void* rot_tiles, 
   p.ind[0] = ind0; p.ind[1] = ind1; p.ind_out[0] = ind0_out; p.ind_out[1] = ind1_out;
   p.prune[0] = prune0; p.prune[1] = prune1; p.prune_out[0] = prune0_out; p.prune_out[1] = prune1_out;
   p.len[0] = len0; p.len[1] = len1; p.len_out[0] = len0_out; p.len_out[1] = len1_out;
-  p.counts = counts; p.w_tok = w_tok; p.b_tok = b_tok; p.w_match = w_match; p.b_match = b_match;
+  p.counts = counts; p.ws = static_cast<unsigned long long*>(ws);
+  p.w_tok = w_tok; p.b_tok = b_tok; p.w_match = w_match; p.b_match = b_match;
   p.thr = thr; p.min_match = min_match; p.do_prune = do_prune; p.B = B;
   p.n_cur[0] = n0; p.n_cur[1] = n1; p.tp[0] = tp0; p.tp[1] = tp1; p.n_orig[0] = n0_orig; p.n_orig[1] = n1_orig;
-  lg::score_prune_tiles_kernel<<<2 * B, lg::kSpThreads, smem, stream>>>(p);
+  lg::score_prune_tiles_kernel<<<B * (tp0 + tp1), lg::kSpThreads, 0, stream>>>(p);
   return static_cast<int>(cudaGetLastError());
 }

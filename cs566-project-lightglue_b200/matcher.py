@@ -235,12 +235,16 @@ class LightGlue(nn.Module):
         for lo in range(0, b, step):
             hi = min(b, lo + step)
             cut = lambda t: None if t is None else t[lo:hi].contiguous()
+            # the buffers of the last two shapes are kept (a batch cut into chunks ends with a shorter one; the
+            # materialised scores alone are up to ~1 GB)
+            cache = self.__dict__.setdefault("_engines32", {})
             key = (hi - lo, m, n, str(dev))
-            eng = self.__dict__.get("_engine32")  # the buffers of the last shape are kept (the scores alone: ~1 GB)
-            if eng is None or eng.key != key or eng.w is not w:
-                self.__dict__["_engine32"] = None
-                eng = self.__dict__["_engine32"] = Fp32Engine(w, hi - lo, m, n, dev)
-                eng.key = key
+            eng = cache.pop(key, None)
+            if eng is None or eng.w is not w:
+                while len(cache) > 1:
+                    cache.pop(next(iter(cache)))
+                eng = Fp32Engine(w, hi - lo, m, n, dev)
+            cache[key] = eng
             l0, l1 = cut(len0), cut(len1)
             d0, d1 = eng.forward(cut(desc0), cut(desc1), (cut(cs0[0]), cut(cs0[1])), (cut(cs1[0]), cut(cs1[1])), l0, l1, L)
             scores, (m0, m1, ms0, ms1) = eng.assign(L - 1, self.conf.filter_threshold, l0, l1)

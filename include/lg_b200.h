@@ -275,13 +275,17 @@ int lg_prune_gather(const float* desc, const float* cos_t, const float* sin_t, c
  * counters, the reference breaks before pruning).  Tiles: side 0 images at row tile b*tp0, side 1 at B*tp0 + b*tp1.
  * counts (B,4) i32 = {kept0, #(conf0 < thr), kept1, #(conf1 < thr)}; len_out = kept.  do_prune = 0: scores and
  * counts only (depth-only mode; the *_out / rot / prune arguments may then be NULL).  w_tok NULL: no confidence head.
- * Rows of x_out / rot_out behind the kept ones are zero-filled up to tp*128. */
+ * Rows of x_out / rot_out behind the kept ones are zero-filled up to tp*128.  One CTA per row tile of the batch; ws =
+ * lg_score_prune_ws_bytes(B, tp0, tp1) bytes of scratch, 8-byte aligned (cleared by the call: a ticket and one word
+ * per row tile for the prefix exchange between the tiles of an image); prune_out is filled by a device-to-device copy
+ * of prune on the same stream before the kernel runs. */
+size_t lg_score_prune_ws_bytes(int B, int tp0, int tp1);
 int lg_score_prune_tiles(const void* x_tiles, const void* rot_tiles, void* x_out, void* rot_out, const int64_t* ind0,
                          const int64_t* ind1, int64_t* ind0_out, int64_t* ind1_out, const int64_t* prune0,
                          const int64_t* prune1, int64_t* prune0_out, int64_t* prune1_out, const int* len0,
                          const int* len1, int* len0_out, int* len1_out, int* counts, const float* w_tok,
                          const float* b_tok, const float* w_match, const float* b_match, float thr, float min_match,
-                         int do_prune, int B, int n0, int n1, int tp0, int tp1, int n0_orig, int n1_orig,
+                         int do_prune, void* ws, int B, int n0, int n1, int tp0, int tp1, int n0_orig, int n1_orig,
                          cudaStream_t stream);
 
 #ifdef __cplusplus
