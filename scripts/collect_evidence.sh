@@ -9,14 +9,18 @@ NCU="ncu --clock-control none"
 set -x
 timeout 600 python bench.py > $out/${tag}_bench_n1.json 2> $out/${tag}_bench_n1.err
 timeout 300 python bench.py --batch 1 --no-eager > $out/${tag}_bench_b1.json 2>> $out/${tag}_bench_n1.err
+timeout 300 python bench.py --kpts 1024 --no-eager > $out/${tag}_bench_kpts1024.json 2>> $out/${tag}_bench_n1.err
 timeout 600 python bench.py --impl reference --steps 2 --warmup 1 > $out/${tag}_bench_reference.json 2>> $out/${tag}_bench_n1.err
 timeout 600 python scripts/bench_configs.py > $out/${tag}_configs.json 2> $out/${tag}_configs.err
+timeout 300 python scripts/bench_configs.py exporter > $out/${tag}_exporter.json 2>> $out/${tag}_configs.err
 timeout 300 python scripts/profile_prune.py > $out/${tag}_hbm_passes.txt 2>&1
 timeout 300 python scripts/profile_assign.py > $out/${tag}_assign_times.txt 2>&1
 timeout 300 python scripts/profile_attention.py 32 2048 20 > $out/${tag}_attention_time.txt 2>&1
 # launch list of one forward (cold-cache, serialised: shares, not absolutes)
 timeout 900 $NCU --metrics gpu__time_duration.sum -c 1500 --csv --log-file $out/${tag}_launches.csv \
   python bench.py --steps 1 --warmup 3 --no-eager > $out/${tag}_launches.log 2>&1
+timeout 600 $NCU --metrics gpu__time_duration.sum -c 1200 --csv --log-file $out/${tag}_launches_b1.csv \
+  python bench.py --batch 1 --steps 1 --warmup 3 --no-eager > $out/${tag}_launches_b1.log 2>&1
 # full captures: attention (self launch of the bench shape), the assignment kernels, the adaptive / pruning kernels
 timeout 600 $NCU --set full --import-source on -k regex:attention_kernel -s 3 -c 1 -f -o $out/${tag}_attention \
   python scripts/profile_attention.py 32 2048 3 > $out/${tag}_ncu_attention.log 2>&1

@@ -62,19 +62,25 @@ dmodel.load_state_dict(sd); dmodel = dmodel.cuda()
 print("depth-only forward                  gpu %.2f ms  wall %.2f ms" % t(lambda: dmodel(data)))
 head = model.log_assignment[0].matchability
 tok = model.token_confidence[0].token[0]
-d0, d1 = eng.rows()
-cs = (torch.zeros(B, N, 32, device="cuda"), torch.zeros(B, N, 32, device="cuda"))
-ind = torch.arange(N, device="cuda")[None].repeat(B, 1)
-pr = torch.ones(B, N, dtype=torch.int64, device="cuda")
+ind0 = torch.arange(N, device="cuda")[None].repeat(B, 1)
+ind1 = ind0.clone()
+pr0 = torch.ones(B, N, dtype=torch.int64, device="cuda")
+pr1 = pr0.clone()
+counts = torch.empty(B, 4, dtype=torch.int32, device="cuda")
+i0n, i1n, p0n, p1n = torch.empty_like(ind0), torch.empty_like(ind1), torch.empty_like(pr0), torch.empty_like(pr1)
+l0n, l1n = torch.empty_like(lens), torch.empty_like(lens)
 
 
-def extras():
-    a0, a1 = eng.rows()
-    for d in (a0, a1):
-        c, mt = C.token_scores(d, tok.weight.reshape(-1), tok.bias, head.weight.reshape(-1), head.bias, lens)
-        keep, cnt = C.prune_plan(c, mt, 0.85, 0.05, lens)
-        g = C.prune_gather(d, cs[0], cs[1], ind, keep, cnt, pr, zero=True)
-    eng.load_rows(a0, a1, cs, cs)
+def fused():  # the adaptive step of one layer: lg_score_prune_tiles into the engine's second buffers
+    C.score_prune_tiles(eng.x, eng.rot, eng.x_alt, eng.rot_alt(), (ind0, ind1), (i0n, i1n), (pr0, pr1), (p0n, p1n),
+                        (lens, lens), (l0n, l1n), counts, tok.weight.reshape(-1), tok.bias, head.weight.reshape(-1),
+                        head.bias, 0.85, 0.05, True, B, N, N, eng.tp0, eng.tp1, N, N)
 
 
-print("per-layer extras             gpu %.2f ms  wall %.2f ms" % t(extras))
+def exit_assign():  # what a layer with exits adds: rows for the logits, final_proj, assignment, filter
+    d0, d1 = eng.rows()
+    model._assign(5, eng, d0, d1, l18, l18, th=0.1)
+
+
+print("adaptive step (fused kernel)        gpu %.3f ms  wall %.3f ms" % t(fused))
+print("exit assignment (lens = 1830)       gpu %.3f ms  wall %.3f ms" % t(exit_assign))

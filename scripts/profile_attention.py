@@ -14,8 +14,11 @@ qt, vt = C.pack_cross_qkv(qk, v, None, 4)
 tp = C.tiles_pad(N)
 out = C.alloc_split(2 * B * tp, 256, "cuda")
 qt1, vt1 = C.pack_cross_qkv(v, qk, None, 4)   # the second image of the pair: its own operand tiles
-s0 = (qt, qt, vt, 0, N, N, None, None)
-s1 = (qt1, qt1, vt1, B * tp, N, N, None, None)
+# LG_PROFILE_LENS=n: per-image valid counts (all n) -- the variable-length path of the kernel
+L = int(os.environ.get("LG_PROFILE_LENS", 0))
+lens = torch.full((B,), L, dtype=torch.int32).cuda() if L else None
+s0 = (qt, qt, vt, 0, N, N, lens, lens)
+s1 = (qt1, qt1, vt1, B * tp, N, N, lens, lens)
 
 
 def launch():  # the layer's launch: both images of a SelfBlock in one kernel
@@ -33,4 +36,4 @@ e1.record()
 torch.cuda.synchronize()
 ms = e0.elapsed_time(e1) / reps
 fl = 2 * 4.0 * 64 * N * N * B * 4
-print(f"attention (both images, one launch) B={B} N={N}: {ms:.4f} ms/launch, {fl / ms / 1e9:.1f} TFLOP/s")
+print(f"attention (both images, one launch) B={B} N={N} lens={L or None}: {ms:.4f} ms/launch, {fl / ms / 1e9:.1f} TFLOP/s")
