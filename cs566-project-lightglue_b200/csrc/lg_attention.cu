@@ -242,6 +242,8 @@ __global__ void __launch_bounds__(kSplit ? 640 : kAttnThreads, 1) attention_kern
   __syncthreads();
   tc_fence_after();
   const uint32_t tmem = bar->tmem_base;
+  pdl_launch_dependents();
+  pdl_wait();  // operand tiles / lengths written by the previous kernels are complete and visible from here on
 
   if (warp >= kSoft) {
     if (kSplit) reg_dec<64>();  // pool = 640 x 96: 512 * 104 + 128 * 64 registers
@@ -1180,9 +1182,16 @@ static int launch_attention(const AttnSideArgs* sides, int n_sides, void* out_ti
     const char* e = getenv("LG_ATTN_SPLIT");
     return !(e && e[0] == '0');
   }();
-  if (split) lg::attention_kernel<true><<<p.items < sms ? p.items : sms, 640, lg::kAttnSmem, stream>>>(p);
-  else lg::attention_kernel<false><<<p.items < sms ? p.items : sms, lg::kAttnThreads, lg::kAttnSmem, stream>>>(p);
-  return static_cast<int>(cudaGetLastError());
+  cudaLaunchConfig_t cfg = {};
+  cfg.gridDim = dim3(static_cast<unsigned>(p.items < sms ? p.items : sms));
+  cfg.blockDim = dim3(split ? 640 : lg::kAttnThreads);
+  cfg.dynamicSmemBytes = lg::kAttnSmem;
+  cfg.stream = stream;
+  cudaLaunchAttribute attr[1];
+  cfg.attrs = attr;
+  cfg.numAttrs = lg::add_pdl_attr(attr, 0);
+  if (split) return static_cast<int>(cudaLaunchKernelEx(&cfg, lg::attention_kernel<true>, p));
+  return static_cast<int>(cudaLaunchKernelEx(&cfg, lg::attention_kernel<false>, p));
 }
 
 extern "C" int lg_attention(const void* q_tiles, const void* k_tiles, const void* v_tiles, float* out,

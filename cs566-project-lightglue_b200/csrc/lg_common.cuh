@@ -2,6 +2,7 @@
 // tcgen05 MMA / TMEM access, UMMA descriptors.  Inline PTX only -- no CUTLASS dependency.
 #pragma once
 #include <cuda_bf16.h>
+#include <cstdlib>
 #include <cuda_runtime.h>
 #include <stdint.h>
 
@@ -294,6 +295,16 @@ __device__ __forceinline__ float warp_sum(float v) {
   return v;
 }
 
+// ----------------------------------------------------------------------------- programmatic dependent launch
+// The layer stack is a chain of ~10 us-to-400 us persistent kernels, each with a prologue (barrier init, TMEM
+// allocation, cluster sync) that touches no global memory.  Launched with the programmatic-stream-serialization
+// attribute, a kernel may become resident while its predecessor drains: it runs its prologue, then waits here until
+// the predecessor grid has completed and its writes are visible.  Every kernel signals "dependents may launch" right
+// after its own prologue; since all grids are persistent (every CTA resident at once), a grid's dependents can only
+// start once the whole grid is resident -- no grid can be starved by its successors.
+__device__ __forceinline__ void pdl_launch_dependents() { asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); }
+__device__ __forceinline__ void pdl_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
+
 // ----------------------------------------------------------------------------- host side: per-device launch state
 // Function attributes (opt-in shared memory) and the SM count belong to a DEVICE, not to the process: a second GPU
 // used from the same process must get its own cudaFuncSetAttribute and its own grid size.
@@ -314,4 +325,20 @@ inline int device_sm_count() {
   return n[d];
 }
 
+// LG_PDL=0 in the environment: plain stream order between the kernels (A/B measurements)
+inline bool pdl_enabled() {
+  static int v = -1;
+  if (v < 0) {
+    const char* e = getenv("LG_PDL");
+    v = (e && e[0] == '0') ? 0 : 1;
+  }
+  return v != 0;
+}
+// Appends the programmatic-serialization attribute to a launch configuration; returns the new attribute count.
+inline unsigned add_pdl_attr(cudaLaunchAttribute* attr, unsigned n) {
+  if (!pdl_enabled()) return n;
+  attr[n].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+  attr[n].val.programmaticStreamSerializationAllowed = 1;
+  return n + 1;
+}
 }  // namespace lg

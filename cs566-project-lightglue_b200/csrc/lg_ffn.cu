@@ -138,6 +138,8 @@ __global__ void __launch_bounds__(kFfnThreads, 1) ffn_ln_gelu_kernel(const FfnPa
   if (warp == 9) tmem_alloc<512>(&bar->tmem_base);
   tc_fence_before();
   cluster_sync_all();  // the peer's barriers exist before the first remote store
+  pdl_launch_dependents();
+  pdl_wait();  // the activations of the previous kernel are complete and visible from here on
   tc_fence_after();
   const uint32_t tmem = bar->tmem_base;
 
@@ -370,13 +372,13 @@ extern "C" int lg_ffn_ln_gelu(const void* a0, int a0_atoms, const void* a1, int 
   cfg.blockDim = dim3(lg::kFfnThreads);
   cfg.dynamicSmemBytes = lg::kFfnSmem;
   cfg.stream = stream;
-  cudaLaunchAttribute attr[1];
+  cudaLaunchAttribute attr[2];
   attr[0].id = cudaLaunchAttributeClusterDimension;
   attr[0].val.clusterDim.x = 2;
   attr[0].val.clusterDim.y = 1;
   attr[0].val.clusterDim.z = 1;
   cfg.attrs = attr;
-  cfg.numAttrs = 1;
+  cfg.numAttrs = lg::add_pdl_attr(attr, 1);
   return static_cast<int>(cudaLaunchKernelEx(&cfg, lg::ffn_ln_gelu_kernel, p));
 }
 

@@ -164,6 +164,8 @@ __global__ void __launch_bounds__(kLinThreads, 1) linear_kernel(const LinearPara
   else __syncthreads();
   tc_fence_after();
   const uint32_t tmem = bar->tmem_base;
+  pdl_launch_dependents();
+  pdl_wait();  // the activations of the previous kernel are complete and visible from here on
 
   if (warp == 8) {
     // ------------------------------------------------------------------ producer
@@ -653,13 +655,13 @@ static int launch_linear_n(const LinearParams& p, cudaStream_t stream) {
   cfg.blockDim = dim3(kLinThreads);
   cfg.dynamicSmemBytes = smem;
   cfg.stream = stream;
-  cudaLaunchAttribute attr[1];
+  cudaLaunchAttribute attr[2];
   attr[0].id = cudaLaunchAttributeClusterDimension;
   attr[0].val.clusterDim.x = kCtas;
   attr[0].val.clusterDim.y = 1;
   attr[0].val.clusterDim.z = 1;
   cfg.attrs = attr;
-  cfg.numAttrs = 1;
+  cfg.numAttrs = add_pdl_attr(attr, 1);
   return static_cast<int>(cudaLaunchKernelEx(&cfg, linear_kernel<kNt, kEpi, kCtas>, p));
 }
 

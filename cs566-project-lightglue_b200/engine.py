@@ -215,11 +215,3 @@ class TileEngine:
             self.md = C.alloc_bf16_tiles(self.rt, 256, self.dev)
         C.linear_f16(self.x, w, b, 256, out=self.md)
         return self.md[: self.rt0], self.md[self.rt0:]
-
-    def final_proj(self, i: int):
-        """MatchAssignment.final_proj of head i (lightglue.py:310) -> md0 (B,M,256), md1 (B,N,256) f32."""
-        w, b = self.pk.final[i]
-        md = C.linear_f32(self.x, w, b, 256)
-        md0 = md[: self.rt0 * C.TILE].view(self.B, self.tp0 * C.TILE, 256)[:, : self.M]
-        md1 = md[self.rt0 * C.TILE:].view(self.B, self.tp1 * C.TILE, 256)[:, : self.N]
-        return md0.contiguous(), md1.contiguous()
