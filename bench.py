@@ -94,7 +94,6 @@ def run_reference(a):
     # each step = a bounded sample of the workload: ONE pair of the 32-pair batch
     for _ in range(max(a.warmup, 1)):
         rate, cores, _ = cpu_forward_rate(a.kpts, 1, warm=0)
-    t0 = time.perf_counter()
     rate, cores, dt = cpu_forward_rate(a.kpts, a.steps, warm=0)
     sample = f"{a.steps} forwards of 1 pair x {a.kpts} kpts (1/{a.batch} of the step's batch), fp32, {cores} threads"
     emit({

@@ -263,7 +263,6 @@ class LightGlue(nn.Module):
         from .engine_fp32 import forward_adaptive_fp32
 
         b, m, n = desc0.shape[0], desc0.shape[1], desc1.shape[1]
-        dev = desc0.device
         l0 = [m] * b if len0 is None else [int(v) for v in len0.tolist()]
         l1 = [n] * b if len1 is None else [int(v) for v in len1.tolist()]
         preds = []
