@@ -396,6 +396,15 @@ def test_forward_large_batch_equals_one_pair_calls():
             single = model(_slice_pair(data, b))
             assert (single["log_assignment"][0] - la[b]).abs().max() < 1e-4, b
             assert torch.equal(single["matches0"][0], pred["matches0"][b])
+    # and against the oracle, not only against itself: two pairs of the batch through the CPU restatement
+    sd = W.make_state_dict(conf, seed=0)
+    host = W.make_inputs(16, 2048, 2048, seed=3, correlated=0.7)
+    for b in (0, 15):
+        ref = O.forward(sd, conf, _slice_pair(host, b))
+        err = (la[b].cpu() - ref["log_assignment"][0]).abs().max().item()
+        agree = (pred["matches0"][b].cpu() == ref["matches0"][0]).float().mean().item()
+        print(f"16 x 2048, pair {b}: max|dlog_assignment|={err:.3e} match agreement {agree:.4f}")
+        assert err < BF16_TOL and agree >= 0.995
 
 
 def test_adaptive_batched_at_scale_vs_single():
