@@ -31,6 +31,7 @@ cases = {
     "qkv_self           K256 N768": (lambda: C.linear_qkv_self(x, wq, b768, rot, B, tp, tp, qkv), 2.0 * rt * 128 * 256 * 768 * 3),
     "qkv_cross          K256 N512": (lambda: C.linear_qkv_cross(x, wc, b512, B, tp, tp, ((q0, v0), (q1, v1))), 2.0 * rt * 128 * 256 * 512 * 3),
     "final linear_f32   K256 N256": (lambda: C.linear_f32(x, w3[: 256 * 256 * 4], b256, 256), 2.0 * rt * 128 * 256 * 256 * 3),
+    "final linear_f16   K256 N256": (lambda: C.linear_f16(x, w3[: 256 * 256 * 4], b256, 256), 2.0 * rt * 128 * 256 * 256 * 3),
     "ffn0+LN+GELU fused K512 N512": (lambda: C.ffn_ln_gelu(x, w0, b512, gamma, beta, 1e-5, a1=ctx, out=h), 2.0 * rt * 128 * 512 * 512 * 3),
     "ln_gelu": (lambda: C.ln_gelu_tiles(hpre, gamma, beta, 1e-5, out=h), 0.0),
 }
