@@ -123,6 +123,21 @@ def forward_adaptive_batched(model, eng, cs0, cs1, len0=None, len1=None):
             exit_layer[b] = layer
         return d0, d1
 
+    sets = {}
+
+    def spare(nact, mc, nc):
+        """Output buffers of the next compaction: two sets per shape, used in turn (the set written last holds the
+        current state, the other one is free again -- the kernel overwrites every entry it hands out)."""
+        key = (nact, mc, nc)
+        if key not in sets:
+            mk = lambda: (torch.empty(nact, mc, device=dev, dtype=torch.int64), torch.empty(nact, nc, device=dev, dtype=torch.int64),
+                          torch.empty(nact, m, device=dev, dtype=torch.int64), torch.empty(nact, n, device=dev, dtype=torch.int64),
+                          torch.empty(nact, device=dev, dtype=torch.int32), torch.empty(nact, device=dev, dtype=torch.int32))
+            sets[key] = [mk(), mk(), 0]
+        entry = sets[key]
+        entry[2] ^= 1
+        return entry[entry[2]]
+
     counts_host = model.__dict__.get("_lg_counts_host")  # pinned once per model (pinning costs ~1 ms)
     if counts_host is None or counts_host.shape[0] < B:
         counts_host = model.__dict__["_lg_counts_host"] = torch.empty(max(B, 64), 4, dtype=torch.int32).pin_memory()
@@ -149,11 +164,7 @@ def forward_adaptive_batched(model, eng, cs0, cs1, len0=None, len1=None):
             # Speculation, queued BEFORE the host waits for the counts: the compacted state of every pair goes to the
             # engine's second buffers; if nobody exits and no tile pair is freed (the common layer) the buffers are
             # swapped and the next layer starts right behind -- the GPU never waits for the host.
-            ind0n = torch.empty(nact, eng.M, device=dev, dtype=torch.int64)
-            ind1n = torch.empty(nact, eng.N, device=dev, dtype=torch.int64)
-            pr0n, pr1n = torch.empty_like(pr0), torch.empty_like(pr1)
-            l0n = torch.empty(nact, device=dev, dtype=torch.int32)
-            l1n = torch.empty(nact, device=dev, dtype=torch.int32)
+            ind0n, ind1n, pr0n, pr1n, l0n, l1n = spare(nact, eng.M, eng.N)
             C.score_prune_tiles(eng.x, eng.rot, eng.x_alt, eng.rot_alt(), (ind0, ind1), (ind0n, ind1n), (pr0, pr1),
                                 (pr0n, pr1n), (l0, l1), (l0n, l1n), counts, wt, bt, head.weight.reshape(-1), head.bias,
                                 thr, min_match, True, nact, eng.M, eng.N, eng.tp0, eng.tp1, m, n)
